@@ -1,0 +1,217 @@
+/*
+ * rtb200.h — C ABI of librtb200.so, the B200 (sm_100a) ray-tracing hot path that
+ * replaces the renderer library of blink97/raytracing-gpu behind its host surface.
+ *
+ * Every entry point cites the reference interface it stands in for
+ * (paths relative to the reference checkout).  No torch / C++ types cross this
+ * boundary: plain pointers, sizes and POD structs only.
+ *
+ * The scene structs below are layout-compatible with the reference's default
+ * build (LAYOUT_SOA + PARTITIONING_OCTREE, gpu/headers/scene.h:16-170); the
+ * static asserts at the end of this file pin sizes and offsets.
+ */
+#ifndef RTB200_H
+#define RTB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- scene model (ABI types; gpu/headers/scene.h, gpu/headers/vector3.h:7) ---- */
+
+#if defined(__VECTOR_TYPES_H__)
+typedef float3 vector3;                      /* gpu/headers/vector3.h:7 */
+#else
+typedef struct rtb_float3 { float x, y, z; } vector3;
+#endif
+
+#ifndef SCENE_H /* the reference's own scene.h already gives these names */
+#define SCENE_H
+
+enum light_type { AMBIENT, DIRECTIONAL, POINT, SPECULAR };   /* scene.h:9-14 */
+
+struct light {                               /* scene.h:16-23, 28 bytes */
+  enum light_type type;
+  float r, g, b;
+  vector3 v;                                 /* direction (d_light) or position (p_light) */
+};
+
+struct camera {                              /* scene.h:25-32, 48 bytes */
+  int width, height;                         /* already multiplied by `aliasing` at render() */
+  vector3 position, u, v;
+  float fov;                                 /* degrees */
+};
+
+struct triangles_layout {                    /* scene.h:98-107 (SOA) */
+  vector3 *vertex;                           /* 3 consecutive vector3 per triangle */
+  vector3 *normal;
+};
+
+struct scene_objects_additional_data {       /* scene.h:109-114 (SOA) */
+  vector3 *vertex;
+  vector3 *normal;
+};
+
+struct object {                              /* scene.h:119-134, 72 bytes */
+  struct triangles_layout triangles;
+  uint32_t triangle_count;
+  vector3 ka, kd, ks;
+  float ns, ni, nr, d;
+};
+
+struct AABB;
+struct octree;
+
+struct scene {                               /* scene.h:140-170, 120 bytes */
+  struct scene_objects_additional_data objects_data;
+  struct object *objects;
+  size_t object_count;
+  struct light *lights;
+  size_t light_count;
+  struct camera camera;
+  size_t triangle_count;
+  struct AABB *aabbs;                        /* unused by this library (null on host) */
+  struct octree *octree;                     /* unused by this library (null on host) */
+};
+
+#endif /* SCENE_H */
+
+/* ---- errors ---- */
+
+#define RTB_OK            0
+#define RTB_ERR_ARG      -1   /* bad argument / inconsistent scene */
+#define RTB_ERR_CUDA     -2   /* CUDA runtime failure (see rtb_last_error) */
+#define RTB_ERR_NOGPU    -3   /* no usable sm_100 device: there is NO CPU fallback */
+#define RTB_ERR_LIMIT    -4   /* scene exceeds a format limit */
+
+/* Thread-local description of the last failure (replaces the spdlog::error +
+ * exit(1) of gpu/raytracer.cu:21-29; the C++ shim / CLI turns it back into that). */
+const char *rtb_last_error(void);
+
+/* ---- one-shot render: the drop-in for
+ *      void render(const scene&, char*, int, std::ptrdiff_t, int, int)
+ *      gpu/headers/raytracer.h:6, gpu/raytracer.cu:177-253.
+ * `scene` holds HOST pointers; camera.width/height are pre-multiplied by `aliasing`
+ * (gpu/rt.cpp:78-79).  Writes out_h rows of out_w RGBA8 pixels, `stride` bytes apart,
+ * row 0 = top of the image (gpu/rt.cpp:44-47). */
+int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing,
+               ptrdiff_t stride, int out_h, int out_w);
+
+/* ---- persistent scene: replaces to_cuda() (gpu/scene.cu:224-352) and the whole
+ *      create_octree() host pipeline (gpu/partitioning/octree.cu:362-411):
+ *      upload, triangle bounds, Morton codes, radix sort, node emit. ---- */
+
+typedef struct rtb_scene_handle rtb_scene_t;
+
+/* flags for rtb_scene_create */
+#define RTB_BUILD_DEFAULT     0u
+#define RTB_BUILD_NO_TREE     1u   /* skip the hierarchy (brute-force tracer only) */
+
+int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
+                     rtb_scene_t **out);
+void rtb_scene_destroy(rtb_scene_t *h);
+
+/* Replace the camera of a resident scene (fly-through).
+ * width/height pre-multiplied by aliasing, as in render(). */
+int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam);
+
+/* Tracer selection (tests and benches; the default is the hierarchy tracer). */
+#define RTB_TRACER_TREE        0   /* octree traversal (product path) */
+#define RTB_TRACER_BRUTE       1   /* every triangle for every ray: semantic definition,
+                                      gpu/hit.cu:84-114 (PARTITIONING_NONE) */
+
+typedef struct rtb_frame_opts {
+  int aliasing;        /* SSAA factor, 3 in gpu/rt.cpp:67 */
+  int tracer;          /* RTB_TRACER_* */
+  int rank, nranks;    /* interleaved-tile split: this call renders only tiles owned by
+                          `rank` of `nranks`; 0,1 = whole frame */
+  int count_rays;      /* 1: maintain the device ray counters (slower; untimed passes) */
+  int reserved[3];
+} rtb_frame_opts;
+
+/* Render into a HOST buffer (H2D nothing, D2H the frame): timed e2e path. */
+int rtb_scene_render(rtb_scene_t *h, const rtb_frame_opts *opts,
+                     unsigned char *rgba_out, ptrdiff_t stride, int out_h, int out_w);
+
+/* Render into a DEVICE buffer (cudaMalloc'ed or peer-mapped memory, e.g. rank 0's
+ * framebuffer opened over CUDA IPC): only pixels of tiles owned by opts->rank are
+ * written.  `stream` is a cudaStream_t (0 = the library's own stream).  Asynchronous:
+ * call rtb_scene_sync() or synchronise the stream. */
+int rtb_scene_render_device(rtb_scene_t *h, const rtb_frame_opts *opts,
+                            void *d_rgba, ptrdiff_t pitch, int out_h, int out_w,
+                            void *stream);
+int rtb_scene_sync(rtb_scene_t *h);
+
+/* Parity extension (not used by `rt`): per-SAMPLE primary-ray nearest-hit IDs on the
+ * aliasing*out_w x aliasing*out_h sample grid, indexed [py*W' + px] with (px,py) the
+ * kernel's sample coordinates of gpu/raytracer.cu:91-92.  id = global triangle index
+ * in host memory order (objects in file order), -1 = miss.  obj_out may be NULL. */
+int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts,
+                      int32_t *tri_out, int32_t *obj_out, int out_h, int out_w);
+
+/* Closest-hit / any-hit queries for arbitrary rays (host arrays of n rays, 6 floats
+ * each: origin, direction).  Mirrors collide()/collide_dist() (gpu/headers/hit.h:7-8).
+ * tri_out[i] = winning triangle or -1; dist_out[i] = new_dist (0 on miss);
+ * with any_hit != 0 only "occluded or not" is meaningful (tri_out = 0 / -1). */
+int rtb_scene_trace_rays(rtb_scene_t *h, int tracer, int any_hit, const float *rays,
+                         size_t n, int32_t *tri_out, float *dist_out);
+
+typedef struct rtb_stats {
+  uint64_t triangles, objects, lights;
+  uint64_t nodes, leaves, max_depth, max_leaf_tris;
+  uint64_t tree_bytes, triangle_bytes;
+  double upload_ms, build_ms;          /* last rtb_scene_create */
+  double frame_ms;                     /* last render (device time, CUDA events) */
+  uint64_t rays_primary, rays_shadow, rays_bounce;   /* last render with count_rays */
+  uint64_t node_visits, tri_tests;                    /* idem */
+  uint64_t kernel_launches;                           /* kernels launched by last render */
+  uint64_t reserved[4];
+} rtb_stats;
+
+int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);
+
+/* ---- build-pipeline primitives on HOST arrays (upload, run the device kernel,
+ *      download) so the reference's own known-answer vectors can be replayed:
+ *      parallel_radix_sort  gpu/partitioning/sort.h:21-22 (test.cu:308-340),
+ *      shared_prefix_sum    gpu/partitioning/prefix_sum.h:13 (test.cu:288-305). ---- */
+int rtb_radix_sort_pairs_u32(uint32_t *keys, uint32_t *vals, size_t n);
+int rtb_radix_sort_pairs_u64(uint64_t *keys, uint32_t *vals, size_t n);
+int rtb_inclusive_scan_u32(uint32_t *data, size_t n);
+int rtb_inclusive_scan_u64(uint64_t *data, size_t n);
+
+/* Device-resident variants used by the build itself and by micro-benchmarks
+ * (gpu/bench.cu:435-451).  Pointers are device pointers; `stream` a cudaStream_t.
+ * Scratch is allocated internally and cached per call site size. */
+int rtb_dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, size_t n,
+                                 int key_bits, void *stream);
+int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream);
+
+/* Dump the flattened hierarchy for structural tests: nodes (64 B each) and the
+ * leaf-ordered triangle permutation.  Pass NULL buffers to query counts. */
+int rtb_scene_dump_tree(rtb_scene_t *h, void *nodes_out, size_t *n_nodes,
+                        uint32_t *perm_out, size_t *n_tris);
+
+/* Library / device info. */
+int rtb_device_count(void);
+const char *rtb_version(void);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+/* ---- layout pins (SURVEY Appendix D probe of the reference headers) ---- */
+#if defined(__cplusplus)
+static_assert(sizeof(vector3) == 12, "vector3");
+static_assert(sizeof(struct light) == 28 && offsetof(struct light, v) == 16, "light");
+static_assert(sizeof(struct camera) == 48 && offsetof(struct camera, fov) == 44, "camera");
+static_assert(sizeof(struct object) == 72 && offsetof(struct object, triangle_count) == 16 &&
+              offsetof(struct object, ka) == 20 && offsetof(struct object, nr) == 64, "object");
+static_assert(sizeof(struct scene) == 120 && offsetof(struct scene, objects) == 16 &&
+              offsetof(struct scene, camera) == 48 &&
+              offsetof(struct scene, triangle_count) == 96, "scene");
+#endif
+
+#endif /* RTB200_H */
