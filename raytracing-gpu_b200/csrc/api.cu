@@ -1,0 +1,525 @@
+// C ABI of librtb200.so (include/rtb200.h).  Host orchestration only; kernels live in
+// build.cu / sort.cu / trace.cu.  There is NO CPU fallback: without a usable sm_100
+// device every compute entry point returns RTB_ERR_NOGPU.
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+#include "rtb_internal.h"
+#include "scene_store.h"
+
+struct rtb_scene_handle {
+  rtb::SceneStore store;
+};
+
+namespace rtb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+  const char *base = strrchr(file, '/');
+  set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base ? base + 1 : file, line, what);
+  cudaGetLastError();   // clear the sticky flag of non-fatal errors
+  return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? RTB_ERR_NOGPU : RTB_ERR_CUDA;
+}
+
+static int pick_device(int device) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) {
+    cudaGetLastError();
+    set_error("no CUDA device available (%s); librtb200 has no CPU fallback",
+              e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return RTB_ERR_NOGPU;
+  }
+  if (device < 0 || device >= n) { set_error("device %d out of range (0..%d)", device, n - 1); return RTB_ERR_ARG; }
+  cudaDeviceProp p;
+  RTB_CUDA(cudaGetDeviceProperties(&p, device));
+  if (p.major != 10) {
+    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, p.major, p.minor);
+    return RTB_ERR_NOGPU;
+  }
+  RTB_CUDA(cudaSetDevice(device));
+  return RTB_OK;
+}
+
+// host part of render(), gpu/raytracer.cu:178-182
+static DevCamera camera_frame(const struct camera &cam) {
+  auto norm = [](vector3 a) {
+    float r = sqrtf(a.x * a.x + a.y * a.y + a.z * a.z);
+    vector3 o; o.x = a.x / r; o.y = a.y / r; o.z = a.z / r;
+    return o;
+  };
+  const vector3 u = norm(cam.u), v = norm(cam.v);
+  vector3 w;
+  w.x = u.y * v.z - u.z * v.y;
+  w.y = u.z * v.x - u.x * v.z;
+  w.z = u.x * v.y - u.y * v.x;
+  const float L = (float)(cam.width / (2 * tan(cam.fov * M_PI / 360)));
+  DevCamera d;
+  d.u = make_float3(u.x, u.y, u.z);
+  d.v = make_float3(v.x, v.y, v.z);
+  d.pos = make_float3(cam.position.x, cam.position.y, cam.position.z);
+  d.C = make_float3(cam.position.x + L * w.x, cam.position.y + L * w.y, cam.position.z + L * w.z);
+  d.W = cam.width;
+  d.H = cam.height;
+  return d;
+}
+
+static int check_frame(const SceneStore &S, const rtb_frame_opts *o, int out_h, int out_w, rtb_frame_opts *eff) {
+  rtb_frame_opts d;
+  memset(&d, 0, sizeof d);
+  d.aliasing = 3;
+  d.nranks = 1;
+  if (o) d = *o;
+  if (d.nranks < 1) d.nranks = 1;
+  if (d.aliasing < 1 || d.aliasing > 16) { set_error("aliasing %d out of range 1..16", d.aliasing); return RTB_ERR_ARG; }
+  if (d.rank < 0 || d.rank >= d.nranks) { set_error("rank %d not in [0,%d)", d.rank, d.nranks); return RTB_ERR_ARG; }
+  if (out_w <= 0 || out_h <= 0) { set_error("empty output image"); return RTB_ERR_ARG; }
+  if (S.camera.width != out_w * d.aliasing || S.camera.height != out_h * d.aliasing) {
+    set_error("camera is %dx%d but output %dx%d with aliasing %d needs %dx%d (camera width/height must be "
+              "pre-multiplied by aliasing, gpu/rt.cpp:78-79)",
+              S.camera.width, S.camera.height, out_w, out_h, d.aliasing, out_w * d.aliasing, out_h * d.aliasing);
+    return RTB_ERR_ARG;
+  }
+  if (d.tracer != RTB_TRACER_TREE && d.tracer != RTB_TRACER_BRUTE) { set_error("unknown tracer %d", d.tracer); return RTB_ERR_ARG; }
+  if (d.tracer == RTB_TRACER_TREE && !S.has_tree && S.n_tris > (uint32_t)LEAF_MAX) {
+    set_error("scene was created with RTB_BUILD_NO_TREE: only RTB_TRACER_BRUTE is available");
+    return RTB_ERR_ARG;
+  }
+  *eff = d;
+  return RTB_OK;
+}
+
+static int ensure_frame_resources(SceneStore &S) {
+  if (!S.d_tile_counter) RTB_CUDA(cudaMalloc((void **)&S.d_tile_counter, sizeof(unsigned int)));
+  if (!S.d_counters) RTB_CUDA(cudaMalloc((void **)&S.d_counters, 8 * sizeof(unsigned long long)));
+  return RTB_OK;
+}
+
+static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d_out, ptrdiff_t pitch, int out_h,
+                        int out_w, cudaStream_t st) {
+  int rc = ensure_frame_resources(S);
+  if (rc) return rc;
+  FrameArgs fa;
+  fa.cam = camera_frame(S.camera);
+  fa.aliasing = o.aliasing;
+  fa.out_w = out_w;
+  fa.out_h = out_h;
+  fa.rank = o.rank;
+  fa.nranks = o.nranks;
+  fa.out = d_out;
+  fa.pitch = (long long)pitch;
+  fa.tile_counter = S.d_tile_counter;
+  fa.counters = S.d_counters;
+  RTB_CUDA(cudaEventRecord(S.ev0, st));
+  rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches);
+  if (rc) return rc;
+  RTB_CUDA(cudaEventRecord(S.ev1, st));
+  if (o.count_rays)
+    RTB_CUDA(cudaMemcpyAsync(S.counters, S.d_counters, sizeof S.counters, cudaMemcpyDeviceToHost, st));
+  return RTB_OK;
+}
+
+static int finish_frame(SceneStore &S, cudaStream_t st) {
+  RTB_CUDA(cudaStreamSynchronize(st));
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, S.ev0, S.ev1) == cudaSuccess) S.frame_ms = ms;
+  else cudaGetLastError();
+  return RTB_OK;
+}
+
+}  // namespace rtb
+
+using namespace rtb;
+
+extern "C" {
+
+const char *rtb_last_error(void) { return g_err; }
+const char *rtb_version(void) { return "rtb200 0.1 (sm_100a)"; }
+
+int rtb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out) {
+  if (!out) { set_error("out is NULL"); return RTB_ERR_ARG; }
+  *out = nullptr;
+  int rc = pick_device(device);
+  if (rc) return rc;
+  rtb_scene_handle *h = new rtb_scene_handle();
+  SceneStore &S = h->store;
+  S.device = device;
+  cudaError_t e;
+  if ((e = cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)) != cudaSuccess ||
+      (e = cudaEventCreate(&S.ev0)) != cudaSuccess || (e = cudaEventCreate(&S.ev1)) != cudaSuccess) {
+    delete h;
+    return cuda_fail(e, "stream/event creation", __FILE__, __LINE__);
+  }
+  cudaDeviceGetAttribute(&S.sm_count, cudaDevAttrMultiProcessorCount, device);
+  rc = build_scene(scene, flags, &S);
+  if (rc) { delete h; return rc; }
+  *out = h;
+  return RTB_OK;
+}
+
+void rtb_scene_destroy(rtb_scene_t *h) { delete h; }
+
+int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam) {
+  if (!h || !cam) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  h->store.camera = *cam;
+  return RTB_OK;
+}
+
+int rtb_scene_render_device(rtb_scene_t *h, const rtb_frame_opts *opts, void *d_rgba, ptrdiff_t pitch, int out_h,
+                            int out_w, void *stream) {
+  if (!h || !d_rgba) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  rtb_frame_opts o;
+  int rc = check_frame(S, opts, out_h, out_w, &o);
+  if (rc) return rc;
+  if (pitch < (ptrdiff_t)out_w * 4) { set_error("pitch smaller than a row"); return RTB_ERR_ARG; }
+  return render_async(S, o, (unsigned char *)d_rgba, pitch, out_h, out_w, stream ? (cudaStream_t)stream : S.stream);
+}
+
+int rtb_scene_sync(rtb_scene_t *h) {
+  if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  RTB_CUDA(cudaSetDevice(h->store.device));
+  return finish_frame(h->store, h->store.stream);
+}
+
+int rtb_scene_render(rtb_scene_t *h, const rtb_frame_opts *opts, unsigned char *rgba_out, ptrdiff_t stride, int out_h,
+                     int out_w) {
+  if (!h || !rgba_out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  rtb_frame_opts o;
+  int rc = check_frame(S, opts, out_h, out_w, &o);
+  if (rc) return rc;
+  if (stride < (ptrdiff_t)out_w * 4) { set_error("stride smaller than a row"); return RTB_ERR_ARG; }
+  const size_t row = (size_t)out_w * 4, bytes = row * out_h;
+  if (S.d_frame_bytes < bytes) {
+    if (S.d_frame) cudaFree(S.d_frame);
+    S.d_frame = nullptr;
+    S.d_frame_bytes = 0;
+    RTB_CUDA(cudaMalloc((void **)&S.d_frame, bytes));
+    S.d_frame_bytes = bytes;
+  }
+  if (o.nranks > 1) RTB_CUDA(cudaMemsetAsync(S.d_frame, 0, bytes, S.stream));
+  rc = render_async(S, o, S.d_frame, (ptrdiff_t)row, out_h, out_w, S.stream);
+  if (rc) return rc;
+  // D2H: straight into the caller's buffer when it is page-locked, else through our pinned staging
+  cudaPointerAttributes attr;
+  bool pinned = cudaPointerGetAttributes(&attr, rgba_out) == cudaSuccess &&
+                (attr.type == cudaMemoryTypeHost);
+  cudaGetLastError();
+  if (pinned) {
+    RTB_CUDA(cudaMemcpy2DAsync(rgba_out, (size_t)stride, S.d_frame, row, row, out_h, cudaMemcpyDeviceToHost, S.stream));
+    return finish_frame(S, S.stream);
+  }
+  if (S.h_frame_bytes < bytes) {
+    if (S.h_frame) cudaFreeHost(S.h_frame);
+    S.h_frame = nullptr;
+    S.h_frame_bytes = 0;
+    RTB_CUDA(cudaMallocHost((void **)&S.h_frame, bytes));
+    S.h_frame_bytes = bytes;
+  }
+  RTB_CUDA(cudaMemcpyAsync(S.h_frame, S.d_frame, bytes, cudaMemcpyDeviceToHost, S.stream));
+  rc = finish_frame(S, S.stream);
+  if (rc) return rc;
+  for (int y = 0; y < out_h; ++y) memcpy(rgba_out + (size_t)y * stride, S.h_frame + (size_t)y * row, row);
+  return RTB_OK;
+}
+
+int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing, ptrdiff_t stride, int out_h,
+               int out_w) {
+  rtb_scene_t *h = nullptr;
+  int rc = rtb_scene_create(scene, 0, RTB_BUILD_DEFAULT, &h);
+  if (rc) return rc;
+  rtb_frame_opts o;
+  memset(&o, 0, sizeof o);
+  o.aliasing = aliasing;
+  o.nranks = 1;
+  rc = rtb_scene_render(h, &o, rgba_out, stride, out_h, out_w);
+  rtb_scene_destroy(h);
+  return rc;
+}
+
+int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_out, int32_t *obj_out, int out_h,
+                      int out_w) {
+  if (!h || !tri_out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  rtb_frame_opts o;
+  int rc = check_frame(S, opts, out_h, out_w, &o);
+  if (rc) return rc;
+  const size_t n = (size_t)S.camera.width * S.camera.height;
+  int32_t *d_tri = nullptr, *d_obj = nullptr;
+  RTB_CUDA(cudaMalloc((void **)&d_tri, n * 4));
+  if (obj_out && cudaMalloc((void **)&d_obj, n * 4) != cudaSuccess) {
+    cudaFree(d_tri);
+    return cuda_fail(cudaGetLastError(), "cudaMalloc(obj ids)", __FILE__, __LINE__);
+  }
+  rc = launch_hit_ids(S.dev(), camera_frame(S.camera), o.tracer, d_tri, d_obj, S.stream);
+  cudaError_t e = cudaSuccess;
+  if (!rc) {
+    e = cudaMemcpyAsync(tri_out, d_tri, n * 4, cudaMemcpyDeviceToHost, S.stream);
+    if (e == cudaSuccess && obj_out) e = cudaMemcpyAsync(obj_out, d_obj, n * 4, cudaMemcpyDeviceToHost, S.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(S.stream);
+  }
+  cudaFree(d_tri);
+  if (d_obj) cudaFree(d_obj);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "hit-id readback", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_scene_trace_rays(rtb_scene_t *h, int tracer, int any_hit, const float *rays, size_t n, int32_t *tri_out,
+                         float *dist_out) {
+  if (!h || (n && !rays)) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  if (tracer != RTB_TRACER_TREE && tracer != RTB_TRACER_BRUTE) { set_error("unknown tracer %d", tracer); return RTB_ERR_ARG; }
+  if (tracer == RTB_TRACER_TREE && !S.has_tree && S.n_tris > (uint32_t)LEAF_MAX) {
+    set_error("scene was created with RTB_BUILD_NO_TREE");
+    return RTB_ERR_ARG;
+  }
+  if (!n) return RTB_OK;
+  float *d_rays = nullptr, *d_dist = nullptr;
+  int32_t *d_tri = nullptr;
+  cudaError_t e = cudaMalloc((void **)&d_rays, n * 24);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&d_tri, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&d_dist, n * 4);
+  int rc = RTB_OK;
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_rays, rays, n * 24, cudaMemcpyHostToDevice, S.stream);
+  if (e == cudaSuccess) rc = launch_trace_rays(S.dev(), tracer, any_hit, d_rays, n, d_tri, d_dist, S.stream);
+  if (e == cudaSuccess && !rc && tri_out) e = cudaMemcpyAsync(tri_out, d_tri, n * 4, cudaMemcpyDeviceToHost, S.stream);
+  if (e == cudaSuccess && !rc && dist_out) e = cudaMemcpyAsync(dist_out, d_dist, n * 4, cudaMemcpyDeviceToHost, S.stream);
+  if (e == cudaSuccess && !rc) e = cudaStreamSynchronize(S.stream);
+  cudaFree(d_rays); cudaFree(d_tri); cudaFree(d_dist);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "trace_rays", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
+  if (!h || !out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  const SceneStore &S = h->store;
+  memset(out, 0, sizeof *out);
+  out->triangles = S.n_tris; out->objects = S.n_objects; out->lights = S.n_lights;
+  out->nodes = S.n_nodes; out->leaves = S.n_leaves; out->max_depth = (uint64_t)S.height; out->max_leaf_tris = S.max_leaf;
+  out->tree_bytes = (uint64_t)S.n_nodes * 64;
+  out->triangle_bytes = (uint64_t)S.n_tris * 96;
+  out->upload_ms = S.upload_ms; out->build_ms = S.build_ms; out->frame_ms = S.frame_ms;
+  out->rays_primary = S.counters[0]; out->rays_shadow = S.counters[1]; out->rays_bounce = S.counters[2];
+  out->node_visits = S.counters[3]; out->tri_tests = S.counters[4];
+  out->kernel_launches = S.frame_launches;
+  out->reserved[0] = S.build_launches;
+  return RTB_OK;
+}
+
+int rtb_scene_dump_tree(rtb_scene_t *h, void *nodes_out, size_t *n_nodes, uint32_t *perm_out, size_t *n_tris) {
+  if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  if (n_nodes) *n_nodes = S.n_nodes;
+  if (n_tris) *n_tris = S.n_tris;
+  if (nodes_out) RTB_CUDA(cudaMemcpy(nodes_out, S.nodes, (size_t)S.n_nodes * 64, cudaMemcpyDeviceToHost));
+  if (perm_out && S.n_tris) RTB_CUDA(cudaMemcpy(perm_out, S.order, (size_t)S.n_tris * 4, cudaMemcpyDeviceToHost));
+  return RTB_OK;
+}
+
+/* extension: index of the root node in the dumped array */
+int rtb_scene_root(rtb_scene_t *h) { return h ? h->store.root : -1; }
+
+/* extension (tests): box inflation factor of the conservative slab test */
+void rtb_set_margin_k(float k) { set_margin_k(k); }
+
+// ---- bracket timer on the library stream (bench: K frames between two events) ----
+int rtb_scene_timer_start(rtb_scene_t *h) {
+  if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  if (!S.tev0) { RTB_CUDA(cudaEventCreate(&S.tev0)); RTB_CUDA(cudaEventCreate(&S.tev1)); }
+  RTB_CUDA(cudaEventRecord(S.tev0, S.stream));
+  return RTB_OK;
+}
+
+int rtb_scene_timer_stop(rtb_scene_t *h, double *ms_out) {
+  if (!h || !ms_out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  if (!S.tev0) { set_error("timer not started"); return RTB_ERR_ARG; }
+  RTB_CUDA(cudaEventRecord(S.tev1, S.stream));
+  RTB_CUDA(cudaEventSynchronize(S.tev1));
+  float ms = 0;
+  RTB_CUDA(cudaEventElapsedTime(&ms, S.tev0, S.tev1));
+  *ms_out = ms;
+  return RTB_OK;
+}
+
+// ---- page-locked host memory and CUDA IPC helpers (multi-process tile gather) ----
+void *rtb_host_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+  return p;
+}
+void rtb_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int rtb_dev_alloc(int device, size_t bytes, void **out) {
+  if (!out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  int rc = pick_device(device);
+  if (rc) return rc;
+  RTB_CUDA(cudaMalloc(out, bytes ? bytes : 1));
+  return RTB_OK;
+}
+int rtb_dev_free(void *p) { if (p) RTB_CUDA(cudaFree(p)); return RTB_OK; }
+int rtb_dev_memset(void *p, int value, size_t bytes) { RTB_CUDA(cudaMemset(p, value, bytes)); return RTB_OK; }
+int rtb_dev_download(void *dst_host, const void *src_dev, size_t bytes) {
+  RTB_CUDA(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
+  return RTB_OK;
+}
+int rtb_ipc_export(void *d_ptr, unsigned char handle_out[64]) {
+  cudaIpcMemHandle_t hnd;
+  RTB_CUDA(cudaIpcGetMemHandle(&hnd, d_ptr));
+  static_assert(sizeof hnd == 64, "ipc handle size");
+  memcpy(handle_out, &hnd, 64);
+  return RTB_OK;
+}
+int rtb_ipc_open(const unsigned char handle[64], void **out) {
+  cudaIpcMemHandle_t hnd;
+  memcpy(&hnd, handle, 64);
+  RTB_CUDA(cudaIpcOpenMemHandle(out, hnd, cudaIpcMemLazyEnablePeerAccess));
+  return RTB_OK;
+}
+int rtb_ipc_close(void *p) { RTB_CUDA(cudaIpcCloseMemHandle(p)); return RTB_OK; }
+
+// ---- build primitives on host arrays (known-answer replays of gpu/test.cu:288-340) ----
+static int sort_host(uint64_t *keys64, uint32_t *keys32, uint32_t *vals, size_t n, int bits) {
+  int rc = pick_device(0);
+  if (rc) return rc;
+  if (!n) return RTB_OK;
+  std::vector<uint64_t> wide;
+  if (keys32) { wide.resize(n); for (size_t i = 0; i < n; ++i) wide[i] = keys32[i]; }
+  const uint64_t *src = keys32 ? wide.data() : keys64;
+  std::vector<uint32_t> iota;
+  if (!vals) { iota.resize(n); for (size_t i = 0; i < n; ++i) iota[i] = (uint32_t)i; }
+  uint64_t *dk = nullptr, *dk2 = nullptr;
+  uint32_t *dv = nullptr, *dv2 = nullptr, *ds = nullptr;
+  const size_t sw = radix_sort_scratch_words(n);
+  cudaError_t e = cudaMalloc((void **)&dk, n * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&dk2, n * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&dv, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&dv2, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&ds, sw * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(dk, src, n * 8, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(dv, vals ? vals : iota.data(), n * 4, cudaMemcpyHostToDevice);
+  int in_alt = 0;
+  if (e == cudaSuccess) rc = dev_radix_sort_pairs_u64(dk, dv, dk2, dv2, n, bits, ds, sw, 0, &in_alt, nullptr);
+  if (e == cudaSuccess && !rc) {
+    std::vector<uint64_t> back(keys32 ? n : 0);
+    e = cudaMemcpy(keys32 ? back.data() : keys64, in_alt ? dk2 : dk, n * 8, cudaMemcpyDeviceToHost);
+    if (keys32 && e == cudaSuccess) for (size_t i = 0; i < n; ++i) keys32[i] = (uint32_t)back[i];
+    if (e == cudaSuccess && vals) e = cudaMemcpy(vals, in_alt ? dv2 : dv, n * 4, cudaMemcpyDeviceToHost);
+  }
+  cudaFree(dk); cudaFree(dk2); cudaFree(dv); cudaFree(dv2); cudaFree(ds);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "radix sort (host arrays)", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_radix_sort_pairs_u32(uint32_t *keys, uint32_t *vals, size_t n) {
+  if (n && !keys) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  return sort_host(nullptr, keys, vals, n, 32);
+}
+int rtb_radix_sort_pairs_u64(uint64_t *keys, uint32_t *vals, size_t n) {
+  if (n && !keys) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  return sort_host(keys, nullptr, vals, n, 64);
+}
+
+int rtb_inclusive_scan_u32(uint32_t *data, size_t n) {
+  int rc = pick_device(0);
+  if (rc) return rc;
+  if (!n) return RTB_OK;
+  if (!data) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  uint32_t *d = nullptr, *s = nullptr;
+  const size_t sw = scan_scratch_words(n);
+  cudaError_t e = cudaMalloc((void **)&d, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&s, sw * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(d, data, n * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) rc = dev_exclusive_scan_u32(d, n, s, sw, true, 0, nullptr);
+  if (e == cudaSuccess && !rc) e = cudaMemcpy(data, d, n * 4, cudaMemcpyDeviceToHost);
+  cudaFree(d); cudaFree(s);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "scan (host arrays)", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_inclusive_scan_u64(uint64_t *data, size_t n) {
+  int rc = pick_device(0);
+  if (rc) return rc;
+  if (!n) return RTB_OK;
+  if (!data) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  uint64_t *d = nullptr, *s = nullptr;
+  const size_t sw = scan_scratch_words(n);
+  cudaError_t e = cudaMalloc((void **)&d, n * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&s, sw * 8);
+  if (e == cudaSuccess) e = cudaMemcpy(d, data, n * 8, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) rc = dev_inclusive_scan_u64(d, n, s, sw, 0);
+  if (e == cudaSuccess && !rc) e = cudaMemcpy(data, d, n * 8, cudaMemcpyDeviceToHost);
+  cudaFree(d); cudaFree(s);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "scan (host arrays)", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, size_t n, int key_bits, void *stream) {
+  if (!n) return RTB_OK;
+  if (!d_keys || !d_vals) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  uint64_t *dk2 = nullptr;
+  uint32_t *dv2 = nullptr, *ds = nullptr;
+  const size_t sw = radix_sort_scratch_words(n);
+  cudaError_t e = cudaMalloc((void **)&dk2, n * 8);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&dv2, n * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&ds, sw * 4);
+  int rc = RTB_OK, in_alt = 0;
+  if (e == cudaSuccess) rc = dev_radix_sort_pairs_u64(d_keys, d_vals, dk2, dv2, n, key_bits, ds, sw, st, &in_alt, nullptr);
+  if (e == cudaSuccess && !rc && in_alt) {
+    e = cudaMemcpyAsync(d_keys, dk2, n * 8, cudaMemcpyDeviceToDevice, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_vals, dv2, n * 4, cudaMemcpyDeviceToDevice, st);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(dk2); cudaFree(dv2); cudaFree(ds);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "device radix sort", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream) {
+  if (!n) return RTB_OK;
+  if (!d_data) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  uint32_t *s = nullptr;
+  const size_t sw = scan_scratch_words(n);
+  RTB_CUDA(cudaMalloc((void **)&s, sw * 4));
+  int rc = dev_exclusive_scan_u32(d_data, n, s, sw, true, st, nullptr);
+  cudaError_t e = cudaStreamSynchronize(st);
+  cudaFree(s);
+  if (rc) return rc;
+  if (e != cudaSuccess) return cuda_fail(e, "device scan", __FILE__, __LINE__);
+  return RTB_OK;
+}
+
+}  // extern "C"

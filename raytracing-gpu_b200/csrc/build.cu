@@ -1,0 +1,491 @@
+// Device-side hierarchy build over TRIANGLES.
+//
+// Replaces the reference's object-level pipeline (gpu/partitioning/octree.cu:362-411:
+// compute_bounding_box -> find_scene_scale -> position_object -> parallel_radix_sort ->
+// nodes_difference_array -> shared_prefix_sum -> create_octree, with blocking copies,
+// per-step cudaMalloc and three cross-block races) by:
+//   k_bounds      triangle boxes -> scene box (warp shuffles + ordered-int atomics, race-free)
+//   k_morton      63-bit Morton code of the box centre (21 bits per axis: the octree cell
+//                 path of the triangle, 21 levels x 3 bits, top level most significant)
+//   radix sort    sort.cu (key + index payload)
+//   k_permute     triangles into leaf order as float4 streams (v0|id, e1|obj, e2; n0,n1,n2)
+//   k_emit        ONE bottom-up pass over the sorted codes: every leaf climbs towards the
+//                 root, the second thread to reach a node merges the two child boxes and
+//                 goes on (Apetrei-style agglomeration; the tree is the Morton radix tree,
+//                 i.e. the octree with each level split into its three binary cuts)
+//   k_compact     subtrees of <= LEAF_MAX triangles become leaves; surviving nodes are
+//                 written to the flat 64-byte node array with remapped child references
+// The result is deterministic: topology depends only on the sorted keys, boxes are exact
+// min/max of vertex coordinates.
+#include <string.h>
+#include <vector>
+#include "rtb_internal.h"
+#include "rtb_math.cuh"
+#include "scene_store.h"
+
+namespace rtb {
+
+namespace {
+
+constexpr int BT = 256;
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, d));
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int d = 16; d; d >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, d));
+  return v;
+}
+
+__device__ __forceinline__ void tri_box(const float *raw_v, uint32_t i, V3 &lo, V3 &hi) {
+  const float *p = raw_v + 9ull * i;
+  float x0 = p[0], y0 = p[1], z0 = p[2], x1 = p[3], y1 = p[4], z1 = p[5], x2 = p[6], y2 = p[7], z2 = p[8];
+  lo = mk(fminf(x0, fminf(x1, x2)), fminf(y0, fminf(y1, y2)), fminf(z0, fminf(z1, z2)));
+  hi = mk(fmaxf(x0, fmaxf(x1, x2)), fmaxf(y0, fmaxf(y1, y2)), fmaxf(z0, fmaxf(z1, z2)));
+}
+
+// bounds[0..2] = min (ordered-uint), bounds[3..5] = max.  Initialised by the host to
+// 0xffffffff / 0 before the launch, so there is no in-kernel init to race with.
+__global__ void __launch_bounds__(BT) k_bounds(const float *raw_v, uint32_t n, uint32_t *bounds) {
+  __shared__ float red[6][BT / 32];
+  const float INF = __int_as_float(0x7f800000);
+  V3 lo = mk(INF, INF, INF), hi = mk(-INF, -INF, -INF);
+  for (uint32_t i = blockIdx.x * BT + threadIdx.x; i < n; i += gridDim.x * BT) {
+    V3 a, b;
+    tri_box(raw_v, i, a, b);
+    lo = mk(fminf(lo.x, a.x), fminf(lo.y, a.y), fminf(lo.z, a.z));
+    hi = mk(fmaxf(hi.x, b.x), fmaxf(hi.y, b.y), fmaxf(hi.z, b.z));
+  }
+  lo = mk(warp_min(lo.x), warp_min(lo.y), warp_min(lo.z));
+  hi = mk(warp_max(hi.x), warp_max(hi.y), warp_max(hi.z));
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    red[0][warp] = lo.x; red[1][warp] = lo.y; red[2][warp] = lo.z;
+    red[3][warp] = hi.x; red[4][warp] = hi.y; red[5][warp] = hi.z;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float v = red[threadIdx.x][0];
+    for (int w = 1; w < BT / 32; ++w) v = threadIdx.x < 3 ? fminf(v, red[threadIdx.x][w]) : fmaxf(v, red[threadIdx.x][w]);
+    if (threadIdx.x < 3) atomicMin(&bounds[threadIdx.x], f2ord(v));
+    else atomicMax(&bounds[threadIdx.x], f2ord(v));
+  }
+}
+
+__device__ __forceinline__ uint64_t spread21(uint32_t v) {
+  uint64_t x = v & 0x1fffffu;
+  x = (x | x << 32) & 0x1f00000000ffffull;
+  x = (x | x << 16) & 0x1f0000ff0000ffull;
+  x = (x | x << 8) & 0x100f00f00f00f00full;
+  x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+  x = (x | x << 2) & 0x1249249249249249ull;
+  return x;
+}
+
+__global__ void __launch_bounds__(BT) k_morton(const float *raw_v, uint32_t n, const uint32_t *bounds,
+                                               uint64_t *keys, uint32_t *vals) {
+  const uint32_t i = blockIdx.x * BT + threadIdx.x;
+  if (i >= n) return;
+  const V3 smin = mk(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
+  const V3 smax = mk(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
+  V3 lo, hi;
+  tri_box(raw_v, i, lo, hi);
+  const float S = 2097152.0f;   // 2^21 cells per axis
+  float ex = smax.x - smin.x, ey = smax.y - smin.y, ez = smax.z - smin.z;
+  float cx = 0.5f * lo.x + 0.5f * hi.x, cy = 0.5f * lo.y + 0.5f * hi.y, cz = 0.5f * lo.z + 0.5f * hi.z;
+  float fx = ex > 0 ? (cx - smin.x) / ex * S : 0.0f;
+  float fy = ey > 0 ? (cy - smin.y) / ey * S : 0.0f;
+  float fz = ez > 0 ? (cz - smin.z) / ez * S : 0.0f;
+  uint32_t qx = (uint32_t)fminf(fmaxf(fx, 0.0f), S - 1.0f);
+  uint32_t qy = (uint32_t)fminf(fmaxf(fy, 0.0f), S - 1.0f);
+  uint32_t qz = (uint32_t)fminf(fmaxf(fz, 0.0f), S - 1.0f);
+  keys[i] = spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
+  vals[i] = i;
+}
+
+// Identity order (RTB_BUILD_NO_TREE): slot == global id.
+__global__ void __launch_bounds__(BT) k_iota(uint32_t *vals, uint32_t n) {
+  const uint32_t i = blockIdx.x * BT + threadIdx.x;
+  if (i < n) vals[i] = i;
+}
+
+__device__ __forceinline__ uint32_t object_of(const uint32_t *obj_first, uint32_t n_obj, uint32_t tri) {
+  // largest o with obj_first[o] <= tri  (obj_first has n_obj + 1 entries, ascending)
+  uint32_t lo = 0, hi = n_obj;
+  while (hi - lo > 1) {
+    uint32_t mid = (lo + hi) >> 1;
+    if (obj_first[mid] <= tri) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+__global__ void __launch_bounds__(BT) k_permute(const float *raw_v, const float *raw_n, const uint32_t *order,
+                                                uint32_t n, const uint32_t *obj_first, uint32_t n_obj,
+                                                float4 *v0, float4 *e1, float4 *e2, float4 *n0, float4 *n1,
+                                                float4 *n2) {
+  const uint32_t s = blockIdx.x * BT + threadIdx.x;
+  if (s >= n) return;
+  const uint32_t i = order[s];
+  const float *p = raw_v + 9ull * i;
+  const V3 a = mk(p[0], p[1], p[2]), b = mk(p[3], p[4], p[5]), c = mk(p[6], p[7], p[8]);
+  const V3 ab = vsub(b, a), ac = vsub(c, a);   // edge1/edge2 of gpu/hit.cu:20-21, same subtraction
+  v0[s] = make_float4(a.x, a.y, a.z, __uint_as_float(i));
+  e1[s] = make_float4(ab.x, ab.y, ab.z, __uint_as_float(object_of(obj_first, n_obj, i)));
+  e2[s] = make_float4(ac.x, ac.y, ac.z, 0.0f);
+  const float *q = raw_n + 9ull * i;
+  const V3 na = vnorm(mk(q[0], q[1], q[2])), nb = vnorm(mk(q[3], q[4], q[5])), nc = vnorm(mk(q[6], q[7], q[8]));
+  n0[s] = make_float4(na.x, na.y, na.z, 0.0f);
+  n1[s] = make_float4(nb.x, nb.y, nb.z, 0.0f);
+  n2[s] = make_float4(nc.x, nc.y, nc.z, 0.0f);
+}
+
+// "How different are sorted neighbours j and j+1": position of the highest differing key
+// bit (+64), or of the highest differing index bit when the keys are equal.
+__device__ __forceinline__ int delta(const uint64_t *keys, uint32_t j) {
+  const uint64_t x = keys[j] ^ keys[j + 1];
+  if (x) return 128 - __clzll((long long)x);
+  return 32 - __clz((int)(j ^ (j + 1)));
+}
+
+__device__ __forceinline__ int leaf_ref(uint32_t first, uint32_t count) { return ~(int)((first << 3) | count); }
+
+struct RawNode {           // same 64-byte layout as the final node
+  float4 q0, q1, q2;
+  int ref0, ref1, lo, cnt;
+};
+
+__device__ __forceinline__ void store_child(RawNode *nd, int side, V3 lo, V3 hi, int ref) {
+  float *f = reinterpret_cast<float *>(nd);
+  // q0/q1 hold x and y of child 0/1; q2 holds z of both
+  float *qxy = f + 4 * side;
+  qxy[0] = lo.x; qxy[1] = hi.x; qxy[2] = lo.y; qxy[3] = hi.y;
+  f[8 + 2 * side] = lo.z;
+  f[9 + 2 * side] = hi.z;
+  (&nd->ref0)[side] = ref;
+}
+__device__ __forceinline__ void load_child(const volatile RawNode *nd, int side, V3 &lo, V3 &hi) {
+  const volatile float *f = reinterpret_cast<const volatile float *>(nd);
+  const volatile float *qxy = f + 4 * side;
+  lo.x = qxy[0]; hi.x = qxy[1]; lo.y = qxy[2]; hi.y = qxy[3];
+  lo.z = f[8 + 2 * side];
+  hi.z = f[9 + 2 * side];
+}
+
+// One thread per sorted triangle.  visit[j] (initialised to -1) receives the range bound
+// of the first child to arrive at inner node j; the second child continues upwards.
+__global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
+                                             uint32_t n, RawNode *raw, int *visit, int *child_height,
+                                             int *root_info /* [0]=raw root, [1]=height */) {
+  const uint32_t i = blockIdx.x * BT + threadIdx.x;
+  if (i >= n) return;
+  V3 lo, hi;
+  tri_box(raw_v, order[i], lo, hi);
+  uint32_t l = i, r = i;
+  int cur = -1;       // raw inner index of the node we stand on (-1: still the single triangle)
+  int height = 0;     // inner nodes on the longest path below (collapsed subtrees count 0)
+  for (;;) {
+    const uint32_t cnt = r - l + 1;
+    if (cnt == n) { root_info[0] = cur; root_info[1] = height; return; }
+    const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
+    const int my_h = cnt <= (uint32_t)LEAF_MAX ? 0 : height;
+    int parent, side;
+    if (l == 0 || (r != n - 1 && delta(keys, r) < delta(keys, l - 1))) { parent = (int)r; side = 0; }
+    else { parent = (int)l - 1; side = 1; }
+    store_child(&raw[parent], side, lo, hi, my_ref);
+    child_height[2 * parent + side] = my_h;
+    __threadfence();
+    const int other = atomicExch(&visit[parent], side == 0 ? (int)l : (int)r);
+    if (other < 0) return;                       // first to arrive: the sibling will carry on
+    __threadfence();
+    V3 slo, shi;
+    load_child(&raw[parent], side ^ 1, slo, shi);
+    const int oh = ((volatile int *)child_height)[2 * parent + (side ^ 1)];
+    lo = mk(fminf(lo.x, slo.x), fminf(lo.y, slo.y), fminf(lo.z, slo.z));
+    hi = mk(fmaxf(hi.x, shi.x), fmaxf(hi.y, shi.y), fmaxf(hi.z, shi.z));
+    if (side == 0) r = (uint32_t)other; else l = (uint32_t)other;
+    raw[parent].lo = (int)l;
+    raw[parent].cnt = (int)(r - l + 1);
+    height = (my_h > oh ? my_h : oh) + 1;
+    cur = parent;
+  }
+}
+
+// live[j] = 1 when raw node j survives (its range is larger than a leaf)
+__global__ void __launch_bounds__(BT) k_live(const RawNode *raw, uint32_t n_inner, uint32_t *live) {
+  const uint32_t j = blockIdx.x * BT + threadIdx.x;
+  if (j < n_inner) live[j] = raw[j].cnt > LEAF_MAX ? 1u : 0u;
+}
+
+// new_index = exclusive scan of live.  stats: [0] leaves, [1] max leaf size
+__global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
+                                                float4 *nodes, unsigned int *stats) {
+  const uint32_t j = blockIdx.x * BT + threadIdx.x;
+  if (j >= n_inner) return;
+  RawNode nd = raw[j];
+  if (nd.cnt <= LEAF_MAX) return;
+  unsigned leaves = 0, maxleaf = 0;
+  if (nd.ref0 >= 0) nd.ref0 = (int)new_index[nd.ref0]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref0 & 7)); }
+  if (nd.ref1 >= 0) nd.ref1 = (int)new_index[nd.ref1]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref1 & 7)); }
+  float4 *dst = nodes + 4ull * new_index[j];
+  dst[0] = nd.q0;
+  dst[1] = nd.q1;
+  dst[2] = nd.q2;
+  dst[3] = make_float4(__int_as_float(nd.ref0), __int_as_float(nd.ref1), __int_as_float(nd.lo), __int_as_float(nd.cnt));
+  if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
+}
+
+// Scenes of at most LEAF_MAX triangles (and brute-force-only scenes): one node whose first
+// child is a leaf over everything, boxed by the scene bounds, second child empty.
+__global__ void k_single_node(const uint32_t *bounds, uint32_t n, float4 *nodes) {
+  const float INF = __int_as_float(0x7f800000);
+  float lx = INF, ly = INF, lz = INF, hx = -INF, hy = -INF, hz = -INF;
+  if (n) {
+    lx = ord2f(bounds[0]); ly = ord2f(bounds[1]); lz = ord2f(bounds[2]);
+    hx = ord2f(bounds[3]); hy = ord2f(bounds[4]); hz = ord2f(bounds[5]);
+  }
+  nodes[0] = make_float4(lx, hx, ly, hy);
+  nodes[1] = make_float4(INF, -INF, INF, -INF);
+  nodes[2] = make_float4(lz, hz, INF, -INF);
+  nodes[3] = make_float4(__int_as_float(leaf_ref(0, n)), __int_as_float(leaf_ref(0, 0)), __int_as_float(0),
+                         __int_as_float((int)n));
+}
+
+double ms_between(cudaEvent_t a, cudaEvent_t b) {
+  float ms = 0;
+  cudaEventElapsedTime(&ms, a, b);
+  return ms;
+}
+
+uint32_t pack_host_color(float r, float g, float b) {
+  // init_color, gpu/colors.cu:3-21 (host build uses -ffp-contract=off)
+  auto q = [](float x) -> uint32_t {
+    x = x * 255;
+    if (x > 255) x = 255;
+    if (x < 0) x = 0;
+    if (x != x) return 0u;
+    return (uint32_t)(uint8_t)x;
+  };
+  return q(r) | (q(g) << 8) | (q(b) << 16) | 0xff000000u;
+}
+float bits_to_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+
+}  // namespace
+
+SceneStore::~SceneStore() { release(); }
+
+void SceneStore::release() {
+  if (device >= 0) cudaSetDevice(device);
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_frame, d_tile_counter, d_counters};
+  for (void *p : ptrs) if (p) cudaFree(p);
+  v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
+  order = nullptr; d_frame = nullptr; d_tile_counter = nullptr; d_counters = nullptr;
+  if (h_frame) { cudaFreeHost(h_frame); h_frame = nullptr; }
+  if (ev0) { cudaEventDestroy(ev0); ev0 = nullptr; }
+  if (ev1) { cudaEventDestroy(ev1); ev1 = nullptr; }
+  if (tev0) { cudaEventDestroy(tev0); tev0 = nullptr; }
+  if (tev1) { cudaEventDestroy(tev1); tev1 = nullptr; }
+  if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+}
+
+#define CK(call) do { int rc__ = (call); if (rc__) return rc__; } while (0)
+
+template <typename T>
+static int dev_alloc(T **p, size_t count) {
+  *p = nullptr;
+  RTB_CUDA(cudaMalloc((void **)p, (count ? count : 1) * sizeof(T)));
+  return RTB_OK;
+}
+
+struct Temp {   // build-time scratch, freed when build_scene returns
+  std::vector<void *> ptrs;
+  ~Temp() { for (void *p : ptrs) cudaFree(p); }
+  template <typename T> int alloc(T **p, size_t count) {
+    int rc = dev_alloc(p, count);
+    if (!rc) ptrs.push_back(*p);
+    return rc;
+  }
+};
+
+int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
+  if (!hs) { set_error("scene is NULL"); return RTB_ERR_ARG; }
+  const size_t n_obj = hs->object_count, n_light = hs->light_count;
+  if (n_obj && !hs->objects) { set_error("object_count > 0 but objects is NULL"); return RTB_ERR_ARG; }
+  if (n_light && !hs->lights) { set_error("light_count > 0 but lights is NULL"); return RTB_ERR_ARG; }
+  std::vector<uint32_t> first(n_obj + 1, 0);
+  size_t total = 0;
+  for (size_t o = 0; o < n_obj; ++o) {
+    first[o] = (uint32_t)total;
+    total += hs->objects[o].triangle_count;
+    if (hs->objects[o].triangle_count && (!hs->objects[o].triangles.vertex || !hs->objects[o].triangles.normal)) {
+      set_error("object %zu has triangles but NULL vertex/normal arrays", o);
+      return RTB_ERR_ARG;
+    }
+    if (total >= (1ull << 28)) { set_error("more than 2^28-1 triangles"); return RTB_ERR_LIMIT; }
+  }
+  first[n_obj] = (uint32_t)total;
+  if (hs->triangle_count != total) {
+    set_error("scene.triangle_count (%zu) != sum of object triangle counts (%zu)", hs->triangle_count, total);
+    return RTB_ERR_ARG;
+  }
+  const uint32_t n = (uint32_t)total;
+  cudaStream_t st = S->stream;
+  Temp tmp;
+  cudaEvent_t e_up0 = S->ev0, e_up1 = S->ev1;
+  cudaEvent_t e_b1 = nullptr;
+  RTB_CUDA(cudaEventCreate(&e_b1));
+  struct EvGuard { cudaEvent_t e; ~EvGuard() { cudaEventDestroy(e); } } evg{e_b1};
+
+  // ---- upload (to_cuda, gpu/scene.cu:224-352): raw float3 arrays, object table, lights ----
+  RTB_CUDA(cudaEventRecord(e_up0, st));
+  float *raw_v = nullptr, *raw_n = nullptr;
+  uint32_t *d_first = nullptr;
+  CK(tmp.alloc(&raw_v, 9ull * n));
+  CK(tmp.alloc(&raw_n, 9ull * n));
+  CK(tmp.alloc(&d_first, n_obj + 1));
+  // objects whose arrays are adjacent in host memory (the SoA scene) go up in one copy
+  for (size_t o = 0; o < n_obj;) {
+    size_t e = o;
+    const vector3 *pv = hs->objects[o].triangles.vertex, *pn = hs->objects[o].triangles.normal;
+    size_t tri = hs->objects[o].triangle_count;
+    while (e + 1 < n_obj && hs->objects[e + 1].triangles.vertex == pv + 3 * tri &&
+           hs->objects[e + 1].triangles.normal == pn + 3 * tri) {
+      ++e;
+      tri += hs->objects[e].triangle_count;
+    }
+    if (tri) {
+      RTB_CUDA(cudaMemcpyAsync(raw_v + 9ull * first[o], pv, 36ull * tri, cudaMemcpyHostToDevice, st));
+      RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * first[o], pn, 36ull * tri, cudaMemcpyHostToDevice, st));
+    }
+    o = e + 1;
+  }
+  RTB_CUDA(cudaMemcpyAsync(d_first, first.data(), (n_obj + 1) * 4, cudaMemcpyHostToDevice, st));
+  std::vector<float> mat(8 * (n_obj ? n_obj : 1), 0.0f);
+  for (size_t o = 0; o < n_obj; ++o) {
+    const struct object &ob = hs->objects[o];
+    float *m = &mat[8 * o];
+    m[0] = bits_to_float(pack_host_color(ob.ka.x, ob.ka.y, ob.ka.z));
+    m[1] = bits_to_float(pack_host_color(ob.kd.x, ob.kd.y, ob.kd.z));
+    m[2] = bits_to_float(pack_host_color(ob.ks.x, ob.ks.y, ob.ks.z));
+    m[3] = ob.ns;
+    m[4] = ob.nr;
+  }
+  std::vector<float> lig(8 * (n_light ? n_light : 1), 0.0f);
+  for (size_t i = 0; i < n_light; ++i) {
+    const struct light &l = hs->lights[i];
+    float *m = &lig[8 * i];
+    m[0] = bits_to_float((uint32_t)l.type);
+    m[1] = bits_to_float(pack_host_color(l.r, l.g, l.b));
+    m[4] = l.v.x; m[5] = l.v.y; m[6] = l.v.z;
+  }
+  CK(dev_alloc(&S->materials, 2 * (n_obj ? n_obj : 1)));
+  CK(dev_alloc(&S->lights, 2 * (n_light ? n_light : 1)));
+  RTB_CUDA(cudaMemcpyAsync(S->materials, mat.data(), mat.size() * 4, cudaMemcpyHostToDevice, st));
+  RTB_CUDA(cudaMemcpyAsync(S->lights, lig.data(), lig.size() * 4, cudaMemcpyHostToDevice, st));
+  RTB_CUDA(cudaEventRecord(e_up1, st));
+
+  // ---- bounds ----
+  uint32_t *d_bounds = nullptr;
+  CK(tmp.alloc(&d_bounds, 8));
+  const uint32_t init_bounds[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};
+  RTB_CUDA(cudaMemcpyAsync(d_bounds, init_bounds, sizeof init_bounds, cudaMemcpyHostToDevice, st));
+  unsigned long long launches = 0;
+  if (n) {
+    unsigned g = (n + BT - 1) / BT;
+    if (g > 148u * 8u) g = 148u * 8u;
+    k_bounds<<<g, BT, 0, st>>>(raw_v, n, d_bounds);
+    ++launches;
+  }
+
+  CK(dev_alloc(&S->v0, n)); CK(dev_alloc(&S->e1, n)); CK(dev_alloc(&S->e2, n));
+  CK(dev_alloc(&S->n0, n)); CK(dev_alloc(&S->n1, n)); CK(dev_alloc(&S->n2, n));
+  CK(dev_alloc(&S->order, n));
+
+  const bool tree = !(flags & RTB_BUILD_NO_TREE) && n > (uint32_t)LEAF_MAX;
+  const unsigned gN = (n + BT - 1) / BT;
+  uint64_t *keys = nullptr;
+  if (tree) {
+    uint64_t *keys_a = nullptr, *keys_b = nullptr;
+    uint32_t *vals_b = nullptr, *scratch = nullptr;
+    const size_t sw = radix_sort_scratch_words(n);
+    CK(tmp.alloc(&keys_a, n)); CK(tmp.alloc(&keys_b, n)); CK(tmp.alloc(&vals_b, n)); CK(tmp.alloc(&scratch, sw));
+    k_morton<<<gN, BT, 0, st>>>(raw_v, n, d_bounds, keys_a, S->order);
+    ++launches;
+    int in_alt = 0;
+    CK(dev_radix_sort_pairs_u64(keys_a, S->order, keys_b, vals_b, n, MORTON_BITS, scratch, sw, st, &in_alt, &launches));
+    keys = keys_a;
+    if (in_alt) {
+      keys = keys_b;
+      RTB_CUDA(cudaMemcpyAsync(S->order, vals_b, 4ull * n, cudaMemcpyDeviceToDevice, st));
+    }
+  } else if (n) {
+    k_iota<<<gN, BT, 0, st>>>(S->order, n);
+    ++launches;
+  }
+  if (n) {
+    k_permute<<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2, S->n0,
+                                 S->n1, S->n2);
+    ++launches;
+  }
+
+  S->n_nodes = 1; S->n_leaves = n ? 1 : 0; S->max_leaf = n; S->height = 1; S->root = 0;
+  if (tree) {
+    const uint32_t n_inner = n - 1;
+    RawNode *raw = nullptr;
+    int *visit = nullptr, *child_h = nullptr, *root_info = nullptr;
+    uint32_t *live = nullptr, *scan_scratch = nullptr;
+    unsigned int *d_stats = nullptr;
+    const size_t ssw = scan_scratch_words(n_inner + 1);
+    CK(tmp.alloc(&raw, n_inner)); CK(tmp.alloc(&visit, n_inner)); CK(tmp.alloc(&child_h, 2ull * n_inner));
+    CK(tmp.alloc(&root_info, 2)); CK(tmp.alloc(&live, n_inner + 1)); CK(tmp.alloc(&scan_scratch, ssw));
+    CK(tmp.alloc(&d_stats, 2));
+    RTB_CUDA(cudaMemsetAsync(visit, 0xff, 4ull * n_inner, st));
+    RTB_CUDA(cudaMemsetAsync(raw, 0, sizeof(RawNode) * (size_t)n_inner, st));
+    RTB_CUDA(cudaMemsetAsync(d_stats, 0, 8, st));
+    RTB_CUDA(cudaMemsetAsync(live, 0, 4ull * (n_inner + 1), st));
+    k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info);
+    k_live<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live);
+    launches += 2;
+    CK(dev_exclusive_scan_u32(live, n_inner + 1, scan_scratch, ssw, false, st, &launches));
+    uint32_t n_live = 0;
+    int h_root[2] = {0, 0};
+    RTB_CUDA(cudaMemcpyAsync(&n_live, live + n_inner, 4, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaMemcpyAsync(h_root, root_info, 8, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    if (n_live == 0 || h_root[0] < 0) { set_error("hierarchy build produced no root"); return RTB_ERR_CUDA; }
+    if (h_root[1] > STACK_MAX) { set_error("hierarchy depth %d exceeds %d", h_root[1], STACK_MAX); return RTB_ERR_LIMIT; }
+    CK(dev_alloc(&S->nodes, 4ull * n_live));
+    k_compact<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, S->nodes, d_stats);
+    ++launches;
+    uint32_t new_root = 0;
+    unsigned int h_stats[2] = {0, 0};
+    RTB_CUDA(cudaMemcpyAsync(&new_root, live + h_root[0], 4, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaMemcpyAsync(h_stats, d_stats, 8, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    S->n_nodes = n_live; S->root = (int)new_root; S->height = h_root[1];
+    S->n_leaves = h_stats[0]; S->max_leaf = h_stats[1];
+  } else {
+    CK(dev_alloc(&S->nodes, 4));
+    k_single_node<<<1, 1, 0, st>>>(d_bounds, n, S->nodes);
+    ++launches;
+  }
+  uint32_t h_bounds[8];
+  RTB_CUDA(cudaEventRecord(e_b1, st));
+  RTB_CUDA(cudaMemcpyAsync(h_bounds, d_bounds, sizeof h_bounds, cudaMemcpyDeviceToHost, st));
+  RTB_CUDA(cudaStreamSynchronize(st));
+  RTB_CUDA(cudaGetLastError());
+  float amax = 0;
+  if (n) for (int k = 0; k < 6; ++k) { float f = ord2f(h_bounds[k]); f = f < 0 ? -f : f; if (f > amax) amax = f; }
+  S->abs_max = amax;
+  S->n_tris = n; S->n_objects = (uint32_t)n_obj; S->n_lights = (uint32_t)n_light;
+  S->has_tree = tree;
+  S->upload_ms = ms_between(e_up0, e_up1);
+  S->build_ms = ms_between(e_up1, e_b1);
+  S->build_launches = launches;
+  S->camera = hs->camera;
+  return RTB_OK;
+}
+
+}  // namespace rtb

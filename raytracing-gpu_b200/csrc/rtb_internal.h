@@ -1,0 +1,88 @@
+// Internal declarations shared by the translation units of librtb200.so.
+// Nothing here is part of the ABI (include/rtb200.h is).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include "rtb200.h"
+
+namespace rtb {
+
+// ---- error plumbing (rtb_last_error) ----
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+#define RTB_CUDA(call)                                                        \
+  do {                                                                        \
+    cudaError_t e__ = (call);                                                 \
+    if (e__ != cudaSuccess) return ::rtb::cuda_fail(e__, #call, __FILE__, __LINE__); \
+  } while (0)
+
+// ---- hierarchy format ----
+// One node = 64 bytes = 4 float4 (two children with full float boxes):
+//   q0 = (c0.min.x, c0.max.x, c0.min.y, c0.max.y)
+//   q1 = (c1.min.x, c1.max.x, c1.min.y, c1.max.y)
+//   q2 = (c0.min.z, c0.max.z, c1.min.z, c1.max.z)
+//   q3 = (as_float(ref0), as_float(ref1), as_float(first slot of range), as_float(slot count))
+// ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX.
+// An empty child is a leaf with count 0 and an inverted box (+inf, -inf).
+constexpr int LEAF_MAX = 4;
+constexpr int STACK_MAX = 96;        // inner-node depth limit (63 Morton bits + 32 index tie-break bits)
+constexpr int MORTON_BITS = 63;      // 21 bits per axis
+
+struct DevScene {
+  // triangles in leaf (Morton) order, three float4 streams (SoA):
+  //   v0 = (vertex0.xyz, as_float(global triangle id in host order))
+  //   e1 = (vertex1 - vertex0, as_float(object index))
+  //   e2 = (vertex2 - vertex0, 0)
+  const float4 *v0, *e1, *e2;
+  // unit vertex normals (normalize() applied once at build: gpu/hit.cu:15-17), same order
+  const float4 *n0, *n1, *n2;
+  const float4 *nodes;      // 4 float4 per node
+  int root;                 // index of the root node
+  uint32_t n_tris;
+  uint32_t n_objects, n_lights;
+  const float4 *materials;  // 3 float4 per object: (ka_col, kd_col, ks_col as packed RGBA8 bits; ns) (nr,0,0,0) ...
+  const float4 *lights;     // 2 float4 per light: (type, packed colour, 0, 0) (v.xyz, 0)
+  float abs_max;            // largest |coordinate| of the scene bounds (conservative-margin scale)
+  float margin_k;           // box inflation, in float spacings at abs_max + |origin| (trace.cu)
+};
+
+struct DevCamera {
+  float3 u, v, C, pos;      // gpu/raytracer.cu:178-182 (host part of render())
+  int W, H;                 // sample grid (already multiplied by aliasing)
+};
+
+struct FrameArgs {
+  DevCamera cam;
+  int aliasing;
+  int out_w, out_h;
+  int rank, nranks;
+  unsigned char *out;       // device (or peer-mapped) RGBA8, row 0 = top
+  long long pitch;
+  unsigned int *tile_counter;
+  unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
+};
+
+// ---- device-side build (build.cu / sort.cu) ----
+int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_keys_alt, uint32_t *d_vals_alt,
+                             size_t n, int key_bits, uint32_t *d_scratch, size_t scratch_words,
+                             cudaStream_t st, int *result_in_alt, unsigned long long *launches);
+size_t radix_sort_scratch_words(size_t n);
+int dev_exclusive_scan_u32(uint32_t *d_data, size_t n, uint32_t *d_scratch, size_t scratch_words, bool inclusive,
+                           cudaStream_t st, unsigned long long *launches);
+int dev_inclusive_scan_u64(uint64_t *d_data, size_t n, uint64_t *d_scratch, size_t scratch_words, cudaStream_t st);
+size_t scan_scratch_words(size_t n);
+
+// ---- frame kernels (trace.cu) ----
+int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
+                 unsigned long long *launches);
+int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
+                   cudaStream_t st);
+int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,
+                      float *d_dist, cudaStream_t st);
+void set_margin_k(float k);   // conservative-box scale factor (tests only)
+float get_margin_k();
+
+}  // namespace rtb

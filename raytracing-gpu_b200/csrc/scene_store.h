@@ -1,0 +1,49 @@
+// The resident scene behind rtb_scene_t: every device allocation the library owns.
+#pragma once
+#include "rtb_internal.h"
+
+namespace rtb {
+
+struct SceneStore {
+  int device = -1;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;     // around the last frame kernel / upload
+  cudaEvent_t tev0 = nullptr, tev1 = nullptr;   // bracket timer (rtb_scene_timer_*)
+  int sm_count = 148;
+
+  float4 *v0 = nullptr, *e1 = nullptr, *e2 = nullptr, *n0 = nullptr, *n1 = nullptr, *n2 = nullptr;
+  float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
+  uint32_t *order = nullptr;            // slot -> global triangle id
+  uint32_t n_tris = 0, n_objects = 0, n_lights = 0;
+  uint32_t n_nodes = 0, n_leaves = 0, max_leaf = 0;
+  int root = 0, height = 0;
+  bool has_tree = false;
+  float abs_max = 0;
+  struct camera camera;                 // current camera (sample-grid resolution)
+
+  // frame resources (grown on demand)
+  unsigned char *d_frame = nullptr;
+  size_t d_frame_bytes = 0;
+  unsigned char *h_frame = nullptr;     // pinned staging for the D2H copy
+  size_t h_frame_bytes = 0;
+  unsigned int *d_tile_counter = nullptr;
+  unsigned long long *d_counters = nullptr;
+
+  double upload_ms = 0, build_ms = 0, frame_ms = 0;
+  unsigned long long build_launches = 0, frame_launches = 0;
+  unsigned long long counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+  ~SceneStore();
+  void release();
+  DevScene dev() const {
+    DevScene d;
+    d.v0 = v0; d.e1 = e1; d.e2 = e2; d.n0 = n0; d.n1 = n1; d.n2 = n2;
+    d.nodes = nodes; d.root = root; d.n_tris = n_tris; d.n_objects = n_objects; d.n_lights = n_lights;
+    d.materials = materials; d.lights = lights; d.abs_max = abs_max; d.margin_k = get_margin_k();
+    return d;
+  }
+};
+
+int build_scene(const struct scene *hs, unsigned flags, SceneStore *S);
+
+}  // namespace rtb

@@ -1,0 +1,435 @@
+// Frame kernels: persistent warps pull 8x4-pixel tiles, trace every sample of the tile
+// (primary ray, shadow rays, reflection chain) and resolve the SSAA box filter in shared
+// memory, so the high-resolution framebuffer and the downscale pass of the reference
+// (gpu/raytracer.cu:87-129 raytrace, :49-85 downscale, :177-253 render) never exist.
+//
+// Semantics follow SURVEY Appendix A exactly:
+//   primary rays      gpu/raytracer.cu:91-110
+//   bounce loop       gpu/raytracer.cu:107-122, trace :32-47, ray_bounce gpu/ray.cu:16-25
+//   ray/triangle      gpu/hit.cu:8-48     nearest hit  gpu/hit.cu:50-78, :84-114
+//   shadow rays       gpu/light.cu:29-36, gpu/hit.cu:241-253 (any candidate on the ray)
+//   shading           gpu/light.cu:12-27, :50-127      colours  gpu/colors.cu:3-47
+// Nearest hit = lexicographic minimum of (new_dist, global triangle id), which equals
+// the reference's "first strict minimum in iteration order" and does not depend on the
+// traversal order.  The hierarchy only culls: every box test is conservative.
+#include "rtb_internal.h"
+#include "rtb_math.cuh"
+
+namespace rtb {
+
+namespace {
+
+constexpr float INF = __builtin_huge_valf();
+
+struct Counters { unsigned primary, shadow, bounce, nodes, tris; };
+
+struct Best {
+  float dist;   // new_dist of the winner, INF when none
+  int id;       // global triangle id (host order)
+  int slot;     // position in the leaf-ordered streams
+};
+
+// gpu/hit.cu:20-41 + :66-67 acceptance of one triangle; dist = new_dist of hit.cu:66.
+__device__ __forceinline__ bool tri_candidate(const V3 o, const V3 d, const float4 a4, const float4 b4,
+                                              const float4 c4, float &dist) {
+  const float EPS = 0.0000001f;
+  const V3 v0 = mk(a4), e1 = mk(b4), e2 = mk(c4);
+  const V3 h = vcross(d, e2);
+  const float a = vdot(e1, h);
+  if (a > -EPS && a < EPS) return false;
+  const float f = 1 / a;
+  const V3 s = vsub(o, v0);
+  const float u = f * vdot(s, h);
+  if (u < 0.0f || u > 1.0f) return false;
+  const V3 q = vcross(s, e1);
+  const float v = f * vdot(d, q);
+  if (v < 0.0f || u + v > 1.0f) return false;
+  const float t = f * vdot(e2, q);
+  if (!(t > EPS)) return false;
+  const V3 out = vadd(o, vscale(vnorm(d), t * vlen(d)));
+  dist = vlen(vsub(out, o));
+  return dist > 0.01f;
+}
+
+// Hit record of the winner: point (hit.cu:39-41) and interpolated normal (hit.cu:42-44).
+__device__ __forceinline__ void hit_record(const DevScene &sc, const V3 o, const V3 d, int slot, V3 &P, V3 &N) {
+  const V3 v0 = mk(__ldg(sc.v0 + slot)), e1 = mk(__ldg(sc.e1 + slot)), e2 = mk(__ldg(sc.e2 + slot));
+  const V3 h = vcross(d, e2);
+  const float a = vdot(e1, h);
+  const float f = 1 / a;
+  const V3 s = vsub(o, v0);
+  const float u = f * vdot(s, h);
+  const V3 q = vcross(s, e1);
+  const float v = f * vdot(d, q);
+  const float t = f * vdot(e2, q);
+  P = vadd(o, vscale(vnorm(d), t * vlen(d)));
+  const V3 n0 = mk(__ldg(sc.n0 + slot)), n1 = mk(__ldg(sc.n1 + slot)), n2 = mk(__ldg(sc.n2 + slot));
+  N = vadd(vadd(vscale(n0, 1 - u - v), vscale(n1, u)), vscale(n2, v));
+}
+
+template <bool ANY>
+__device__ __forceinline__ bool consider(const DevScene &sc, const V3 o, const V3 d, int slot, Best &best) {
+  const float4 a4 = __ldg(sc.v0 + slot), b4 = __ldg(sc.e1 + slot), c4 = __ldg(sc.e2 + slot);
+  float dist;
+  if (!tri_candidate(o, d, a4, b4, c4, dist)) return false;
+  if (ANY) return true;
+  const int id = __float_as_int(a4.w);
+  if (dist < best.dist || (dist == best.dist && id < best.id)) {
+    best.dist = dist;
+    best.id = id;
+    best.slot = slot;
+    return true;
+  }
+  return false;
+}
+
+// Every triangle for every ray: the semantic definition (gpu/hit.cu:84-114, PARTITIONING_NONE).
+template <bool ANY, bool COUNT>
+__device__ bool trace_brute(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
+  best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
+  for (uint32_t s = 0; s < sc.n_tris; ++s) {
+    if (COUNT) ++c.tris;
+    if (consider<ANY>(sc, o, d, (int)s, best) && ANY) return true;
+  }
+  return best.slot >= 0;
+}
+
+// Conservative slab test.  The box is inflated by eps on every side; eps is a multiple of
+// the float spacing at the largest coordinate the triangle test can involve, so a ray
+// that the (rounded) Moeller-Trumbore arithmetic accepts is never culled.
+struct Slabs { float ix, iy, iz, ax, ay, az, bx, by, bz; };
+
+__device__ __forceinline__ float safe_rcp(float x) {
+  const float tiny = 1e-30f;
+  return 1.0f / (fabsf(x) > tiny ? x : copysignf(tiny, x));
+}
+
+__device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
+  Slabs s;
+  s.ix = safe_rcp(d.x); s.iy = safe_rcp(d.y); s.iz = safe_rcp(d.z);
+  s.ax = (o.x + eps) * s.ix; s.ay = (o.y + eps) * s.iy; s.az = (o.z + eps) * s.iz;   // pairs with box min
+  s.bx = (o.x - eps) * s.ix; s.by = (o.y - eps) * s.iy; s.bz = (o.z - eps) * s.iz;   // pairs with box max
+  return s;
+}
+
+__device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, float loy, float hiy, float loz,
+                                         float hiz, float tmax, float &tn) {
+  const float x0 = __fmaf_rn(lox, s.ix, -s.ax), x1 = __fmaf_rn(hix, s.ix, -s.bx);
+  const float y0 = __fmaf_rn(loy, s.iy, -s.ay), y1 = __fmaf_rn(hiy, s.iy, -s.by);
+  const float z0 = __fmaf_rn(loz, s.iz, -s.az), z1 = __fmaf_rn(hiz, s.iz, -s.bz);
+  tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+  const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+  return tn <= tf;
+}
+
+template <bool ANY, bool COUNT>
+__device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
+  best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
+  const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
+  const float eps = sc.margin_k * 1.1920929e-7f * amax;
+  const Slabs sl = make_slabs(o, d, eps);
+  // distance -> ray parameter, rounded up
+  const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
+  float tmax = INF;
+  int stack[STACK_MAX];
+  int sp = 0;
+  int cur = sc.root;
+  for (;;) {
+    if (cur >= 0) {
+      if (COUNT) ++c.nodes;
+      const float4 *np = sc.nodes + 4ll * cur;
+      const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+      float tn0, tn1;
+      const bool h0 = slab_hit(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
+      const bool h1 = slab_hit(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
+      const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
+      if (h0 && h1) {
+        const bool far0 = tn1 < tn0;
+        cur = far0 ? r1 : r0;
+        stack[sp++] = far0 ? r0 : r1;
+      } else if (h0) cur = r0;
+      else if (h1) cur = r1;
+      else {
+        if (!sp) break;
+        cur = stack[--sp];
+      }
+    } else {
+      const uint32_t packed = (uint32_t)~cur;
+      const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
+      for (int k = 0; k < cnt; ++k) {
+        if (COUNT) ++c.tris;
+        if (consider<ANY>(sc, o, d, first + k, best)) {
+          if (ANY) return true;
+          tmax = (best.dist * 1.0001f + eps) * inv_len;
+        }
+      }
+      if (!sp) break;
+      cur = stack[--sp];
+    }
+  }
+  return best.slot >= 0;
+}
+
+template <int TRACER, bool ANY, bool COUNT>
+__device__ __forceinline__ bool trace(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
+  if (TRACER == RTB_TRACER_BRUTE) return trace_brute<ANY, COUNT>(sc, o, d, best, c);
+  return trace_tree<ANY, COUNT>(sc, o, d, best, c);
+}
+
+// gpu/light.cu:12-27
+__device__ __forceinline__ uint32_t apply_specular(uint32_t color, const V3 inc_o, const V3 inc_d, const V3 P,
+                                                   const V3 N, uint32_t ks_col, float ns) {
+  V3 V = vsub(inc_o, P);
+  V3 R = vsub(inc_d, vscale(N, 2 * vdot(N, inc_d)));
+  R = vnorm(R);
+  V = vnorm(V);
+  const float dt = vdot(R, V);
+  const float Ls = powf(dt > 0.0f ? dt : 0.0f, ns);
+  return color_add(color, color_mul(ks_col, Ls));
+}
+
+// gpu/light.cu:50-127
+template <int TRACER, bool COUNT>
+__device__ uint32_t apply_light(const DevScene &sc, int obj, const V3 P, const V3 Nrm, Counters &c) {
+  const float4 m0 = __ldg(sc.materials + 2 * obj);
+  const uint32_t ka = __float_as_uint(m0.x), kd = __float_as_uint(m0.y), ks = __float_as_uint(m0.z);
+  const float ns = m0.w;
+  uint32_t color = init_color(0, 0, 0);
+  for (uint32_t i = 0; i < sc.n_lights; ++i) {
+    const float4 l0 = __ldg(sc.lights + 2 * i), l1 = __ldg(sc.lights + 2 * i + 1);
+    const int type = __float_as_int(l0.x);
+    const uint32_t lcol = __float_as_uint(l0.y);
+    const V3 lv = mk(l1);
+    if (type == AMBIENT) {
+      color = color_add(color, color_mults(lcol, ka));
+    } else if (type == DIRECTIONAL) {
+      const V3 L = vscale(lv, -1);
+      Best b;
+      if (COUNT) ++c.shadow;
+      if (!trace<TRACER, true, COUNT>(sc, P, L, b, c)) {
+        uint32_t t = color_mults(lcol, kd);
+        t = color_mul(t, vdot(L, Nrm));
+        t = apply_specular(t, vadd(P, vscale(lv, -10)), lv, P, Nrm, ks, ns);
+        color = color_add(color, t);
+      }
+    } else if (type == POINT) {
+      const V3 L = vscale(lv, -1);
+      V3 N = Nrm;
+      if (vdot(L, N) < 0) N = vscale(N, -1);
+      const V3 dir = vsub(lv, P);
+      const float dist = vlen(vsub(lv, P));
+      Best b;
+      if (COUNT) ++c.shadow;
+      if (!trace<TRACER, true, COUNT>(sc, P, dir, b, c)) {
+        uint32_t t = color_mults(lcol, kd);
+        t = color_mul(t, vdot(L, N) * 1 / dist);
+        t = apply_specular(t, vadd(P, vscale(dir, -10)), dir, P, Nrm, ks, ns);
+        color = color_add(color, t);
+      }
+    }
+  }
+  return color;
+}
+
+__device__ __forceinline__ void primary_ray(const DevCamera &cam, int px, int py, V3 &o, V3 &d) {
+  const V3 ui = vscale(mk(cam.u), (float)(px - cam.W / 2));
+  const V3 vj = vscale(mk(cam.v), (float)(py - cam.H / 2));
+  o = vadd(vadd(mk(cam.C), ui), vj);
+  d = vnorm(vsub(mk(cam.pos), o));
+}
+
+// raytrace kernel body (gpu/raytracer.cu:87-129) for one sample
+template <int TRACER, bool COUNT>
+__device__ uint32_t shade_sample(const DevScene &sc, const DevCamera &cam, int px, int py, Counters &c) {
+  V3 o, d;
+  primary_ray(cam, px, py, o, d);
+  float nr_ = 1, r = 1;
+  int budget = 10;
+  uint32_t color = init_color(0, 0, 0);
+  bool first = true;
+  do {
+    if (COUNT) { if (first) ++c.primary; else ++c.bounce; }
+    first = false;
+    Best b;
+    uint32_t tc;
+    if (trace<TRACER, false, COUNT>(sc, o, d, b, c)) {
+      V3 P, N;
+      hit_record(sc, o, d, b.slot, P, N);
+      const int obj = __float_as_int(__ldg(sc.e1 + b.slot).w);
+      tc = apply_light<TRACER, COUNT>(sc, obj, P, N, c);
+      r = __ldg(sc.materials + 2 * obj + 1).x;
+      if (r > 0) {
+        d = vsub(d, vscale(N, 2 * vdot(N, d)));
+        o = P;
+      }
+    } else {
+      r = 0;
+      tc = init_color(0, 0, 0);
+    }
+    tc = color_mul(tc, nr_);
+    color = color_add(color, tc);
+    nr_ *= r;
+  } while (nr_ > 0.01f && budget-- > 0);
+  return color;
+}
+
+constexpr int FRAME_THREADS = 128;
+constexpr int FRAME_WARPS = FRAME_THREADS / 32;
+
+// Warp tiles: 8x4 output pixels.  32 warp tiles (4 across, 8 down) make one 32x32-pixel
+// rank tile; rank tile (Tx,Ty) belongs to rank (Tx + 3*Ty) mod nranks.
+template <int TRACER, bool COUNT>
+__global__ void __launch_bounds__(FRAME_THREADS) k_frame(const DevScene sc, const FrameArgs fa) {
+  extern __shared__ uint32_t s_cols[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int a = fa.aliasing;
+  const int tw = 8 * a;                          // samples per tile row
+  uint32_t *tile = s_cols + (size_t)warp * 32 * a * a;
+  const int nTx = (fa.out_w + 31) / 32, nTy = (fa.out_h + 31) / 32;
+  const unsigned total = (unsigned)nTx * (unsigned)nTy * 32u;
+  Counters c = {0, 0, 0, 0, 0};
+  for (;;) {
+    unsigned t = 0;
+    if (lane == 0) t = atomicAdd(fa.tile_counter, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    if (t >= total) break;
+    const int T = (int)(t >> 5), sub = (int)(t & 31u);
+    const int Tx = T % nTx, Ty = T / nTx;
+    if (fa.nranks > 1 && (Tx + 3 * Ty) % fa.nranks != fa.rank) continue;
+    const int lx0 = Tx * 32 + (sub & 3) * 8, ly0 = Ty * 32 + (sub >> 2) * 4;
+    if (lx0 >= fa.out_w || ly0 >= fa.out_h) continue;
+    for (int q = 0; q < a * a; ++q) {
+      const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
+      const int px = a * lx0 + sx, py = a * ly0 + sy;
+      uint32_t col = 0;
+      if (px < fa.cam.W && py < fa.cam.H) col = shade_sample<TRACER, COUNT>(sc, fa.cam, px, py, c);
+      tile[sy * tw + sx] = col;
+    }
+    __syncwarp();
+    // downscale kernel body (gpu/raytracer.cu:49-85) for this lane's output pixel
+    const int lx = lx0 + (lane & 7), ly = ly0 + (lane >> 3);
+    if (lx < fa.out_w && ly < fa.out_h) {
+      float r = 0, g = 0, b = 0;
+      for (int j = 0; j < a; ++j)
+        for (int i = 0; i < a; ++i) {
+          const uint32_t col = tile[(a * (lane >> 3) + j) * tw + a * (lane & 7) + i];
+          r += (float)ch_r(col);
+          g += (float)ch_g(col);
+          b += (float)ch_b(col);
+        }
+      const float ali2 = 255.0f * (float)a * (float)a;
+      r /= ali2;
+      g /= ali2;
+      b /= ali2;
+      const uint32_t e = init_color(r, g, b);
+      unsigned char *dst = fa.out + (long long)(fa.out_h - ly - 1) * fa.pitch + 4ll * (fa.out_w - lx - 1);
+      *reinterpret_cast<uint32_t *>(dst) = e;
+    }
+    __syncwarp();
+  }
+  if (COUNT) {
+    unsigned v[5] = {c.primary, c.shadow, c.bounce, c.nodes, c.tris};
+#pragma unroll
+    for (int k = 0; k < 5; ++k) {
+      unsigned long long s = v[k];
+#pragma unroll
+      for (int dlt = 16; dlt; dlt >>= 1) s += __shfl_xor_sync(0xffffffffu, s, dlt);
+      if (lane == 0 && s) atomicAdd(fa.counters + k, s);
+    }
+  }
+}
+
+template <int TRACER>
+__global__ void __launch_bounds__(128) k_hit_ids(const DevScene sc, const DevCamera cam, int32_t *tri, int32_t *obj) {
+  // 8x4 sample blocks per warp, like the frame kernel
+  const int lane = threadIdx.x & 31;
+  const long long w = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  const int bw = (cam.W + 7) / 8;
+  const int bx = (int)(w % bw), by = (int)(w / bw);
+  const int px = bx * 8 + (lane & 7), py = by * 4 + (lane >> 3);
+  if (px >= cam.W || py >= cam.H) return;
+  V3 o, d;
+  primary_ray(cam, px, py, o, d);
+  Best b;
+  Counters c = {0, 0, 0, 0, 0};
+  const bool hit = trace<TRACER, false, false>(sc, o, d, b, c);
+  const size_t k = (size_t)py * cam.W + px;
+  tri[k] = hit ? b.id : -1;
+  if (obj) obj[k] = hit ? __float_as_int(__ldg(sc.e1 + b.slot).w) : -1;
+}
+
+template <int TRACER, bool ANY>
+__global__ void __launch_bounds__(128) k_trace_rays(const DevScene sc, const float *rays, size_t n, int32_t *tri,
+                                                    float *dist) {
+  const size_t i = (size_t)blockIdx.x * 128 + threadIdx.x;
+  if (i >= n) return;
+  const V3 o = mk(rays[6 * i], rays[6 * i + 1], rays[6 * i + 2]);
+  const V3 d = mk(rays[6 * i + 3], rays[6 * i + 4], rays[6 * i + 5]);
+  Best b;
+  Counters c = {0, 0, 0, 0, 0};
+  const bool hit = trace<TRACER, ANY, false>(sc, o, d, b, c);
+  if (tri) tri[i] = hit ? (ANY ? 0 : b.id) : -1;
+  if (dist) dist[i] = (hit && !ANY) ? b.dist : 0.0f;
+}
+
+float g_margin_k = 24.0f;
+
+}  // namespace
+
+void set_margin_k(float k) { g_margin_k = k; }
+float get_margin_k() { return g_margin_k; }
+
+template <int TRACER, bool COUNT>
+static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
+  const size_t smem = (size_t)FRAME_WARPS * 32 * fa.aliasing * fa.aliasing * sizeof(uint32_t);
+  auto kern = k_frame<TRACER, COUNT>;
+  if (smem > 48 * 1024) RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RTB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FRAME_THREADS, smem));
+  if (per_sm < 1) per_sm = 1;
+  kern<<<sm_count * per_sm, FRAME_THREADS, smem, st>>>(sc, fa);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
+                 unsigned long long *launches) {
+  if (fa.aliasing < 1 || fa.aliasing > 16) { set_error("aliasing must be in 1..16"); return RTB_ERR_ARG; }
+  RTB_CUDA(cudaMemsetAsync(fa.tile_counter, 0, sizeof(unsigned int), st));
+  if (count) RTB_CUDA(cudaMemsetAsync(fa.counters, 0, 8 * sizeof(unsigned long long), st));
+  if (launches) *launches = 1;
+  if (tracer == RTB_TRACER_BRUTE)
+    return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
+                 : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);
+  return count ? launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st)
+               : launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
+}
+
+int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
+                   cudaStream_t st) {
+  const long long bw = (cam.W + 7) / 8, bh = (cam.H + 3) / 4;
+  const long long warps = bw * bh;
+  const unsigned blocks = (unsigned)((warps + 3) / 4);
+  if (!blocks) return RTB_OK;
+  if (tracer == RTB_TRACER_BRUTE) k_hit_ids<RTB_TRACER_BRUTE><<<blocks, 128, 0, st>>>(sc, cam, d_tri, d_obj);
+  else k_hit_ids<RTB_TRACER_TREE><<<blocks, 128, 0, st>>>(sc, cam, d_tri, d_obj);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,
+                      float *d_dist, cudaStream_t st) {
+  if (!n) return RTB_OK;
+  const unsigned blocks = (unsigned)((n + 127) / 128);
+  if (tracer == RTB_TRACER_BRUTE) {
+    if (any_hit) k_trace_rays<RTB_TRACER_BRUTE, true><<<blocks, 128, 0, st>>>(sc, d_rays, n, d_tri, d_dist);
+    else k_trace_rays<RTB_TRACER_BRUTE, false><<<blocks, 128, 0, st>>>(sc, d_rays, n, d_tri, d_dist);
+  } else {
+    if (any_hit) k_trace_rays<RTB_TRACER_TREE, true><<<blocks, 128, 0, st>>>(sc, d_rays, n, d_tri, d_dist);
+    else k_trace_rays<RTB_TRACER_TREE, false><<<blocks, 128, 0, st>>>(sc, d_rays, n, d_tri, d_dist);
+  }
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+}  // namespace rtb
