@@ -103,21 +103,26 @@ int refcpu_collide(void *h, const float *rays, size_t n, float *hit_out) {
 }
 
 /* cpu/raytracer.c:19-34 */
-static struct color cpu_trace(struct scene scene, struct ray ray, float coef) {
+/* rays[0] += 1 per collide() issued here (primary / reflection), rays[1] += 1 per shadow
+ * ray apply_light casts (one per DIRECTIONAL / POINT light, cpu/light.c:50-110) */
+static struct color cpu_trace(struct scene scene, struct ray ray, float coef, uint64_t *rays) {
   if (coef < 0.01)
     return init_color(0, 0, 0);
   struct object obj;
+  rays[0]++;
   struct ray new_ray = collide(scene, ray, &obj);
   if (!vector3_is_zero(new_ray.direction)) {
+    for (size_t i = 0; i < scene.light_count; i++)
+      if (scene.lights[i].type == DIRECTIONAL || scene.lights[i].type == POINT) rays[1]++;
     struct color object = apply_light(scene, obj, new_ray);
     struct ray reflection_ray = ray_bounce(ray, new_ray);
-    struct color reflection = cpu_trace(scene, reflection_ray, obj.nr * coef);
+    struct color reflection = cpu_trace(scene, reflection_ray, obj.nr * coef, rays);
     return color_add(reflection, color_mul(object, coef));
   }
   return init_color(0, 0, 0);
 }
 
-struct job { struct scene *s; const float *xy; size_t begin, end; float *rgb; struct vector3 u, v, C; };
+struct job { struct scene *s; const float *xy; size_t begin, end; float *rgb; struct vector3 u, v, C; uint64_t rays[2]; };
 
 static void *worker(void *p) {
   struct job *j = p;
@@ -129,7 +134,7 @@ static void *worker(void *p) {
     struct ray ray;
     ray.origin = point;
     ray.direction = vector3_normalize(vector3_sub(j->s->camera.position, point));
-    struct color c = cpu_trace(*j->s, ray, 1);
+    struct color c = cpu_trace(*j->s, ray, 1, j->rays);
     j->rgb[3 * i] = c.r; j->rgb[3 * i + 1] = c.g; j->rgb[3 * i + 2] = c.b;
   }
   return NULL;
@@ -137,7 +142,7 @@ static void *worker(void *p) {
 
 /* xy: n (k,l) image-plane coordinates in the CPU renderer's convention
  * (cpu/raytracer.c:50-58: pixel offsets from the image centre, step 0.5). */
-int refcpu_trace_samples(void *h, const float *xy, size_t n, float *rgb_out, int nthreads) {
+int refcpu_trace_samples(void *h, const float *xy, size_t n, float *rgb_out, int nthreads, uint64_t *rays_out) {
   struct scene *s = h;
   if (nthreads < 1) nthreads = 1;
   if (nthreads > 256) nthreads = 256;
@@ -152,8 +157,13 @@ int refcpu_trace_samples(void *h, const float *xy, size_t n, float *rgb_out, int
     jobs[t].s = s; jobs[t].xy = xy; jobs[t].rgb = rgb_out; jobs[t].u = u; jobs[t].v = v; jobs[t].C = C;
     jobs[t].begin = n * (size_t)t / (size_t)nthreads;
     jobs[t].end = n * (size_t)(t + 1) / (size_t)nthreads;
+    jobs[t].rays[0] = jobs[t].rays[1] = 0;
     pthread_create(&tid[t], NULL, worker, &jobs[t]);
   }
   for (int t = 0; t < nthreads; t++) pthread_join(tid[t], NULL);
+  if (rays_out) {
+    rays_out[0] = rays_out[1] = 0;
+    for (int t = 0; t < nthreads; t++) { rays_out[0] += jobs[t].rays[0]; rays_out[1] += jobs[t].rays[1]; }
+  }
   return 0;
 }

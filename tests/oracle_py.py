@@ -66,7 +66,7 @@ def ref_lib(name):
         L.refcpu_scene_create.argtypes = [C.c_void_p]
         L.refcpu_scene_destroy.argtypes = [C.c_void_p]
         L.refcpu_collide.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
-        L.refcpu_trace_samples.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int]
+        L.refcpu_trace_samples.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p]
     return L
 
 
