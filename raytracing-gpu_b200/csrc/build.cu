@@ -94,11 +94,13 @@ __global__ void __launch_bounds__(BT) k_morton(const float *raw_v, uint32_t n, c
   V3 lo, hi;
   tri_box(raw_v, i, lo, hi);
   const float S = 2097152.0f;   // 2^21 cells per axis
-  float ex = smax.x - smin.x, ey = smax.y - smin.y, ez = smax.z - smin.z;
-  float cx = 0.5f * lo.x + 0.5f * hi.x, cy = 0.5f * lo.y + 0.5f * hi.y, cz = 0.5f * lo.z + 0.5f * hi.z;
-  float fx = ex > 0 ? (cx - smin.x) / ex * S : 0.0f;
-  float fy = ey > 0 ? (cy - smin.y) / ey * S : 0.0f;
-  float fz = ez > 0 ? (cz - smin.z) / ez * S : 0.0f;
+  // cubic cells: one scale for the three axes (the scene box's longest side), so a code
+  // prefix is an octree cell and flat scenes do not waste their top splits on a thin axis
+  const float ext = fmaxf(fmaxf(smax.x - smin.x, smax.y - smin.y), smax.z - smin.z);
+  const float cx = 0.5f * lo.x + 0.5f * hi.x, cy = 0.5f * lo.y + 0.5f * hi.y, cz = 0.5f * lo.z + 0.5f * hi.z;
+  const float fx = ext > 0 ? (cx - smin.x) / ext * S : 0.0f;
+  const float fy = ext > 0 ? (cy - smin.y) / ext * S : 0.0f;
+  const float fz = ext > 0 ? (cz - smin.z) / ext * S : 0.0f;
   uint32_t qx = (uint32_t)fminf(fmaxf(fx, 0.0f), S - 1.0f);
   uint32_t qy = (uint32_t)fminf(fmaxf(fy, 0.0f), S - 1.0f);
   uint32_t qz = (uint32_t)fminf(fmaxf(fz, 0.0f), S - 1.0f);

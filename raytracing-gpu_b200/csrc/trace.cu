@@ -122,6 +122,15 @@ __device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, f
   return tn <= tf;
 }
 
+#ifndef RTB_LOOP_SHAPE
+#define RTB_LOOP_SHAPE 0
+#endif
+constexpr int TRAVERSAL_DONE = (int)0x80000000;   // stack sentinel: not a valid leaf reference
+
+// "while-while" traversal: every lane first descends inner nodes until it holds a leaf
+// (or has nothing left), then the warp tests triangles together.  Keeping the two phases
+// apart keeps the lanes of a warp in the same code at the same time; with a single
+// if-inner-else-leaf loop the triangle code ran at 7.5 of 32 lanes (profiles/r1_v1).
 template <bool ANY, bool COUNT>
 __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
   best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
@@ -131,11 +140,16 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
   // distance -> ray parameter, rounded up
   const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
   float tmax = INF;
-  int stack[STACK_MAX];
-  int sp = 0;
+  int stack[STACK_MAX + 1];
+  stack[0] = TRAVERSAL_DONE;
+  int sp = 1;
   int cur = sc.root;
   for (;;) {
+#if RTB_LOOP_SHAPE == 1   /* if-if: one node OR one leaf per trip */
     if (cur >= 0) {
+#else                     /* while-while */
+    while (cur >= 0) {
+#endif
       if (COUNT) ++c.nodes;
       const float4 *np = sc.nodes + 4ll * cur;
       const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
@@ -149,23 +163,22 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
         stack[sp++] = far0 ? r0 : r1;
       } else if (h0) cur = r0;
       else if (h1) cur = r1;
-      else {
-        if (!sp) break;
-        cur = stack[--sp];
-      }
-    } else {
-      const uint32_t packed = (uint32_t)~cur;
-      const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
-      for (int k = 0; k < cnt; ++k) {
-        if (COUNT) ++c.tris;
-        if (consider<ANY>(sc, o, d, first + k, best)) {
-          if (ANY) return true;
-          tmax = (best.dist * 1.0001f + eps) * inv_len;
-        }
-      }
-      if (!sp) break;
-      cur = stack[--sp];
+      else cur = stack[--sp];
+#if RTB_LOOP_SHAPE == 1
+      continue;
+#endif
     }
+    if (cur == TRAVERSAL_DONE) break;
+    const uint32_t packed = (uint32_t)~cur;
+    const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
+    for (int k = 0; k < cnt; ++k) {
+      if (COUNT) ++c.tris;
+      if (consider<ANY>(sc, o, d, first + k, best)) {
+        if (ANY) return true;
+        tmax = (best.dist * 1.0001f + eps) * inv_len;
+      }
+    }
+    cur = stack[--sp];
   }
   return best.slot >= 0;
 }

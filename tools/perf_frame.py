@@ -1,0 +1,41 @@
+"""Quick iteration probe (GPU box): frame-kernel time on the C5 terrain + frame checksum.
+usage: python tools/perf_frame.py [--grid 2237] [--frames 5] [--k 24,8,2] [--ncu]"""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "raytracing-gpu_b200"))
+import pyrtb  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--grid", type=int, default=2237)
+ap.add_argument("--frames", type=int, default=5)
+ap.add_argument("--k", default="")
+ap.add_argument("--w", type=int, default=3840)
+ap.add_argument("--h", type=int, default=2160)
+ap.add_argument("--count", action="store_true")
+a = ap.parse_args()
+hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
+ds = pyrtb.DeviceScene(hs, 3)
+st = ds.stats()
+print("build %.2f ms upload %.2f ms nodes %d depth %d" % (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"]))
+ks = [float(x) for x in a.k.split(",")] if a.k else [None]
+for k in ks:
+    if k is not None:
+        pyrtb.lib().rtb_set_margin_k(k)
+    img = ds.render()
+    t = []
+    for _ in range(a.frames):
+        img = ds.render()
+        t.append(ds.stats()["frame_ms"])
+    line = "K=%s frame ms: min %.2f median %.2f  checksum %d" % (k, min(t), float(np.median(t)), int(img.astype(np.uint64).sum()))
+    if a.count:
+        ds.render(count=True)
+        s = ds.stats()
+        rays = s["rays_primary"] + s["rays_shadow"] + s["rays_bounce"]
+        line += "  rays %d nodes/ray %.2f tris/ray %.2f" % (rays, s["node_visits"] / rays, s["tri_tests"] / rays)
+    print(line, flush=True)
+ds.close()
