@@ -27,7 +27,10 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 //   q3 = (as_float(ref0), as_float(ref1), as_float(first slot of range), as_float(slot count))
 // ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX.
 // An empty child is a leaf with count 0 and an inverted box (+inf, -inf).
-constexpr int LEAF_MAX = 4;
+#ifndef RTB_LEAF_MAX
+#define RTB_LEAF_MAX 4
+#endif
+constexpr int LEAF_MAX = RTB_LEAF_MAX;
 constexpr int STACK_MAX = 96;        // inner-node depth limit (63 Morton bits + 32 index tie-break bits)
 constexpr int MORTON_BITS = 63;      // 21 bits per axis
 

@@ -291,8 +291,11 @@ constexpr int FRAME_WARPS = FRAME_THREADS / 32;
 
 // Warp tiles: 8x4 output pixels.  32 warp tiles (4 across, 8 down) make one 32x32-pixel
 // rank tile; rank tile (Tx,Ty) belongs to rank (Tx + 3*Ty) mod nranks.
+#ifndef RTB_FRAME_MINBLOCKS
+#define RTB_FRAME_MINBLOCKS 8
+#endif
 template <int TRACER, bool COUNT>
-__global__ void __launch_bounds__(FRAME_THREADS) k_frame(const DevScene sc, const FrameArgs fa) {
+__global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
   extern __shared__ uint32_t s_cols[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = fa.aliasing;

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librtb200.so")
+LIB_PATH = os.environ.get("RTB200_LIB") or os.path.join(_HERE, "librtb200.so")   # env override: A/B builds in tools/
 
 AMBIENT, DIRECTIONAL, POINT = 0, 1, 2
 TRACER_TREE, TRACER_BRUTE = 0, 1
