@@ -54,6 +54,14 @@ inline void write_png(const std::byte *buffer, int width, int height, int stride
 void render(const scene &scene, char *buffer, int aliasing, std::ptrdiff_t stride,
             int pre_h, int pre_w);
 
+/* Synthetic benchmark scene of BASELINE.json configs[4], built through empty_scene /
+ * add_object_to_scene / get_vertex / get_normal: a grid x grid tessellated height field
+ * (2*grid^2 triangles, 16 objects, ambient + directional + point light).  grid = 2237
+ * gives 10 008 338 triangles.  width/height: camera resolution (not multiplied by aliasing). */
+extern "C" int rtb_synth_terrain(struct scene *out, int grid, uint64_t seed, int width, int height);
+/* Scene -> .svati text that parser() reads back to the identical memory image. */
+extern "C" int rtb_write_svati(const struct scene *scene, const char *path, int width, int height);
+
 /* The body of main() in gpu/rt.cpp:54-97 as a callable (used by the `rt` binary). */
 extern "C" int rtb_cli_main(int argc, char **argv);
 

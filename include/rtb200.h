@@ -194,6 +194,32 @@ int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream);
 int rtb_scene_dump_tree(rtb_scene_t *h, void *nodes_out, size_t *n_nodes,
                         uint32_t *perm_out, size_t *n_tris);
 
+/* Index of the root node inside the array rtb_scene_dump_tree returns. */
+int rtb_scene_root(rtb_scene_t *h);
+
+/* Bracket timer on the library stream: CUDA events around everything queued between
+ * start and stop (bench: K frames back to back).  stop synchronises and returns ms. */
+int rtb_scene_timer_start(rtb_scene_t *h);
+int rtb_scene_timer_stop(rtb_scene_t *h, double *ms_out);
+
+/* Box-inflation factor of the conservative slab test, in float spacings at
+ * |ray origin| + |scene| (DESIGN.md "conservative culling").  Tests and probes only. */
+void rtb_set_margin_k(float k);
+
+/* Page-locked host memory (a frame buffer the D2H copy can target directly) and plain
+ * device buffers / CUDA-IPC handles for the multi-process tile gather: rank 0 exports
+ * its frame, the other ranks open it and pass the mapped pointer to
+ * rtb_scene_render_device, so their tiles travel as NVLink peer stores. */
+void *rtb_host_alloc(size_t bytes);
+void rtb_host_free(void *p);
+int rtb_dev_alloc(int device, size_t bytes, void **out);
+int rtb_dev_free(void *p);
+int rtb_dev_memset(void *p, int value, size_t bytes);
+int rtb_dev_download(void *dst_host, const void *src_dev, size_t bytes);
+int rtb_ipc_export(void *d_ptr, unsigned char handle_out[64]);
+int rtb_ipc_open(const unsigned char handle[64], void **out);
+int rtb_ipc_close(void *p);
+
 /* Library / device info. */
 int rtb_device_count(void);
 const char *rtb_version(void);
