@@ -123,13 +123,19 @@ int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam);
 #define RTB_TRACER_BRUTE       1   /* every triangle for every ray: semantic definition,
                                       gpu/hit.cu:84-114 (PARTITIONING_NONE) */
 
+#define RTB_KERNEL_PER_SAMPLE  0
+#define RTB_KERNEL_WAVEFRONT   1
+
 typedef struct rtb_frame_opts {
   int aliasing;        /* SSAA factor, 3 in gpu/rt.cpp:67 */
   int tracer;          /* RTB_TRACER_* */
   int rank, nranks;    /* interleaved-tile split: this call renders only tiles owned by
                           `rank` of `nranks`; 0,1 = whole frame */
   int count_rays;      /* 1: maintain the device ray counters (slower; untimed passes) */
-  int reserved[3];
+  int frame_kernel;    /* RTB_KERNEL_*: 0 = persistent-warp per-sample kernel (default, fastest measured);
+                          1 = staged wavefront kernel with in-warp ray queues (tree tracer, <= 32
+                          shadow-casting lights, aliasing <= 6; same bytes out) */
+  int reserved[2];
 } rtb_frame_opts;
 
 /* Render into a HOST buffer (H2D nothing, D2H the frame): timed e2e path. */

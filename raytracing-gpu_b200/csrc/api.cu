@@ -120,6 +120,21 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.pitch = (long long)pitch;
   fa.tile_counter = S.d_tile_counter;
   fa.counters = S.d_counters;
+  fa.bounce_scratch = nullptr;
+  fa.n_shadow_lights = S.n_shadow_lights;
+  memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
+  if (o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
+      S.n_lights <= 255) {
+    const size_t need = wave_scratch_floats(o.aliasing, S.sm_count);
+    if (S.d_bounce_floats < need) {
+      if (S.d_bounce) cudaFree(S.d_bounce);
+      S.d_bounce = nullptr;
+      S.d_bounce_floats = 0;
+      RTB_CUDA(cudaMalloc((void **)&S.d_bounce, need * sizeof(float)));
+      S.d_bounce_floats = need;
+    }
+    fa.bounce_scratch = S.d_bounce;
+  }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches);
   if (rc) return rc;
@@ -177,6 +192,11 @@ void rtb_scene_destroy(rtb_scene_t *h) { delete h; }
 
 int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam) {
   if (!h || !cam) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  if (camera_origin_radius(*cam) > h->store.origin_radius) {
+    set_error("camera puts ray origins %.0f units out, the hierarchy was padded for %.0f: create the scene again "
+              "with this camera", camera_origin_radius(*cam), h->store.origin_radius);
+    return RTB_ERR_LIMIT;
+  }
   h->store.camera = *cam;
   return RTB_OK;
 }

@@ -17,6 +17,8 @@
 //                 written to the flat 64-byte node array with remapped child references
 // The result is deterministic: topology depends only on the sorted keys, boxes are exact
 // min/max of vertex coordinates.
+#include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <vector>
 #include "rtb_internal.h"
@@ -178,13 +180,51 @@ __device__ __forceinline__ void load_child(const volatile RawNode *nd, int side,
 
 // One thread per sorted triangle.  visit[j] (initialised to -1) receives the range bound
 // of the first child to arrive at inner node j; the second child continues upwards.
+// Sliver padding.  The rounded Moeller-Trumbore test accepts rays that pass within
+// delta ~ few * 2^-24 * |origin - vertex| of a triangle's edges; beyond a corner of
+// interior angle theta that region reaches delta / sin(theta/2) past the vertex, which for
+// needle triangles exceeds the uniform ray-time margin (tests/golden island_smooth has a
+// 2.4-degree needle: 1 of 4.67 M samples was culled before this).  Leaf boxes of triangles
+// whose sharpest corner gives 1/sin(theta/2) > SLIVER_KAPPA0 are therefore grown by
+// pad_unit * kappa, pad_unit = SLIVER_K * 2^-23 * (largest |coordinate| a ray origin or the
+// scene can have); inner boxes inherit it through the union.
+constexpr float SLIVER_KAPPA0 = 4.0f;
+constexpr float SLIVER_K = 6.0f;
+
+__device__ __forceinline__ float sliver_kappa(const float *raw_v, uint32_t i, float &longest) {
+  const float *p = raw_v + 9ull * i;
+  const V3 a = mk(p[0], p[1], p[2]), b = mk(p[3], p[4], p[5]), c = mk(p[6], p[7], p[8]);
+  const V3 ab = vsub(b, a), bc = vsub(c, b), ca = vsub(a, c);
+  const float lab = vlen(ab), lbc = vlen(bc), lca = vlen(ca);
+  longest = fmaxf(fmaxf(lab, lbc), lca);
+  if (!(lab > 0) || !(lbc > 0) || !(lca > 0)) return 0.0f;   // two equal vertices: a == 0 exactly, never accepted
+  // cos of the interior angles at a, b, c
+  const float ca_ = -vdot(ab, ca) / (lab * lca), cb_ = -vdot(ab, bc) / (lab * lbc), cc_ = -vdot(bc, ca) / (lbc * lca);
+  const float cmax = fminf(fmaxf(fmaxf(ca_, cb_), cc_), 1.0f);
+  const float s = sqrtf(fmaxf(0.5f * (1.0f - cmax), 1e-12f));   // sin(theta_min / 2)
+  return fminf(1.0f / s, 1.0e4f);
+}
+
 __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
                                              uint32_t n, RawNode *raw, int *visit, int *child_height,
-                                             int *root_info /* [0]=raw root, [1]=height */) {
+                                             int *root_info /* [0]=raw root, [1]=height */,
+                                             const uint32_t *bounds, float origin_radius) {
   const uint32_t i = blockIdx.x * BT + threadIdx.x;
   if (i >= n) return;
   V3 lo, hi;
   tri_box(raw_v, order[i], lo, hi);
+  {
+    float longest = 0;
+    const float kappa = sliver_kappa(raw_v, order[i], longest);
+    if (kappa > SLIVER_KAPPA0) {
+      float amax = 0;
+      for (int k = 0; k < 6; ++k) amax = fmaxf(amax, fabsf(ord2f(bounds[k])));
+      // the u,v <= 1 tests keep accepted rays within about one edge length of the triangle
+      const float pad = fminf(SLIVER_K * 1.1920929e-7f * (amax + origin_radius) * kappa, longest);
+      lo = mk(lo.x - pad, lo.y - pad, lo.z - pad);
+      hi = mk(hi.x + pad, hi.y + pad, hi.z + pad);
+    }
+  }
   uint32_t l = i, r = i;
   int cur = -1;       // raw inner index of the node we stand on (-1: still the single triangle)
   int height = 0;     // inner nodes on the longest path below (collapsed subtrees count 0)
@@ -280,10 +320,10 @@ SceneStore::~SceneStore() { release(); }
 
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_frame, d_tile_counter, d_counters};
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_frame, d_tile_counter, d_counters, d_bounce};
   for (void *p : ptrs) if (p) cudaFree(p);
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
-  order = nullptr; d_frame = nullptr; d_tile_counter = nullptr; d_counters = nullptr;
+  order = nullptr; d_frame = nullptr; d_tile_counter = nullptr; d_counters = nullptr; d_bounce = nullptr;
   if (h_frame) { cudaFreeHost(h_frame); h_frame = nullptr; }
   if (ev0) { cudaEventDestroy(ev0); ev0 = nullptr; }
   if (ev1) { cudaEventDestroy(ev1); ev1 = nullptr; }
@@ -311,6 +351,14 @@ struct Temp {   // build-time scratch, freed when build_scene returns
   }
 };
 
+// How far from the world origin a primary-ray origin of this camera can be: the image plane
+// lies L = W'/(2 tan(fov/2)) behind the camera (gpu/raytracer.cu:181-182).
+float camera_origin_radius(const struct camera &cm) {
+  const double L = cm.fov > 0 && cm.fov < 360 ? cm.width / (2 * tan(cm.fov * M_PI / 360)) : 0;
+  const double pm = fmax(fmax(fabs(cm.position.x), fabs(cm.position.y)), fabs(cm.position.z));
+  return (float)(pm + fabs(L) + 0.5 * (abs(cm.width) + abs(cm.height)));
+}
+
 int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   if (!hs) { set_error("scene is NULL"); return RTB_ERR_ARG; }
   const size_t n_obj = hs->object_count, n_light = hs->light_count;
@@ -334,6 +382,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   }
   const uint32_t n = (uint32_t)total;
   cudaStream_t st = S->stream;
+  S->origin_radius = 2.0f * camera_origin_radius(hs->camera);   // x2 head-room for camera moves
   Temp tmp;
   cudaEvent_t e_up0 = S->ev0, e_up1 = S->ev1;
   cudaEvent_t e_b1 = nullptr;
@@ -447,7 +496,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     RTB_CUDA(cudaMemsetAsync(raw, 0, sizeof(RawNode) * (size_t)n_inner, st));
     RTB_CUDA(cudaMemsetAsync(d_stats, 0, 8, st));
     RTB_CUDA(cudaMemsetAsync(live, 0, 4ull * (n_inner + 1), st));
-    k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info);
+    k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info, d_bounds, S->origin_radius);
     k_live<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live);
     launches += 2;
     CK(dev_exclusive_scan_u32(live, n_inner + 1, scan_scratch, ssw, false, st, &launches));
@@ -487,6 +536,12 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   S->build_ms = ms_between(e_up1, e_b1);
   S->build_launches = launches;
   S->camera = hs->camera;
+  S->n_shadow_lights = 0;
+  for (size_t i = 0; i < n_light; ++i)
+    if (hs->lights[i].type == DIRECTIONAL || hs->lights[i].type == POINT) {
+      if (S->n_shadow_lights < 32) S->shadow_light[S->n_shadow_lights] = (unsigned char)i;
+      ++S->n_shadow_lights;
+    }
   return RTB_OK;
 }
 

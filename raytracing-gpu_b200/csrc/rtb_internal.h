@@ -66,7 +66,14 @@ struct FrameArgs {
   long long pitch;
   unsigned int *tile_counter;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
+  // wavefront kernel only
+  float *bounce_scratch;          // per resident warp: 7 x S floats (origin, direction, nr_ of reflected rays)
+  int n_shadow_lights;            // DIRECTIONAL + POINT lights (<= 32 for the wavefront kernel)
+  unsigned char shadow_light[32]; // their indices in the light array, file order
 };
+
+constexpr int WAVE_MAX_ALIASING = 6;      // shared-memory budget of the wavefront kernel
+size_t wave_scratch_floats(int aliasing, int sm_count);   // size of FrameArgs::bounce_scratch
 
 // ---- device-side build (build.cu / sort.cu) ----
 int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_keys_alt, uint32_t *d_vals_alt,

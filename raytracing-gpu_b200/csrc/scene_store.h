@@ -19,6 +19,7 @@ struct SceneStore {
   int root = 0, height = 0;
   bool has_tree = false;
   float abs_max = 0;
+  float origin_radius = 0;              // ray-origin radius the sliver padding was built for (build.cu)
   struct camera camera;                 // current camera (sample-grid resolution)
 
   // frame resources (grown on demand)
@@ -28,6 +29,10 @@ struct SceneStore {
   size_t h_frame_bytes = 0;
   unsigned int *d_tile_counter = nullptr;
   unsigned long long *d_counters = nullptr;
+  float *d_bounce = nullptr;            // wavefront kernel: reflected-ray scratch
+  size_t d_bounce_floats = 0;
+  int n_shadow_lights = 0;              // DIRECTIONAL + POINT lights
+  unsigned char shadow_light[32] = {0};
 
   double upload_ms = 0, build_ms = 0, frame_ms = 0;
   unsigned long long build_launches = 0, frame_launches = 0;
@@ -45,5 +50,6 @@ struct SceneStore {
 };
 
 int build_scene(const struct scene *hs, unsigned flags, SceneStore *S);
+float camera_origin_radius(const struct camera &cm);
 
 }  // namespace rtb

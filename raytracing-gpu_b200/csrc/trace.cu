@@ -388,6 +388,8 @@ __global__ void __launch_bounds__(128) k_trace_rays(const DevScene sc, const flo
   if (dist) dist[i] = (hit && !ANY) ? b.dist : 0.0f;
 }
 
+#include "wave.cuh"
+
 float g_margin_k = 24.0f;
 
 }  // namespace
@@ -408,12 +410,36 @@ static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count,
   return RTB_OK;
 }
 
+constexpr int WAVE_MAX_BLOCKS_PER_SM = 16;
+
+size_t wave_scratch_floats(int aliasing, int sm_count) {
+  return (size_t)sm_count * WAVE_MAX_BLOCKS_PER_SM * WAVE_WARPS * 7 * 32 * aliasing * aliasing;
+}
+
+template <bool COUNT>
+static int launch_wave_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
+  const size_t smem = (size_t)WAVE_WARPS * 16 * 32 * fa.aliasing * fa.aliasing;
+  auto kern = k_frame_wave<COUNT>;
+  if (smem > 48 * 1024) RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;
+  RTB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, WAVE_THREADS, smem));
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > WAVE_MAX_BLOCKS_PER_SM) per_sm = WAVE_MAX_BLOCKS_PER_SM;
+  kern<<<sm_count * per_sm, WAVE_THREADS, smem, st>>>(sc, fa);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches) {
   if (fa.aliasing < 1 || fa.aliasing > 16) { set_error("aliasing must be in 1..16"); return RTB_ERR_ARG; }
   RTB_CUDA(cudaMemsetAsync(fa.tile_counter, 0, sizeof(unsigned int), st));
   if (count) RTB_CUDA(cudaMemsetAsync(fa.counters, 0, 8 * sizeof(unsigned long long), st));
   if (launches) *launches = 1;
+  // RTB_KERNEL_WAVEFRONT was requested and is applicable (api.cu sets bounce_scratch only then);
+  // everything else runs the persistent-warp per-sample kernel, the faster of the two
+  if (tracer == RTB_TRACER_TREE && fa.bounce_scratch && fa.n_shadow_lights <= 32 && fa.aliasing <= WAVE_MAX_ALIASING)
+    return count ? launch_wave_t<true>(sc, fa, sm_count, st) : launch_wave_t<false>(sc, fa, sm_count, st);
   if (tracer == RTB_TRACER_BRUTE)
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);

@@ -321,6 +321,7 @@ class DeviceScene:
     def __init__(self, hs, aliasing=3, device=0, flags=BUILD_DEFAULT):
         self.h = C.c_void_p()
         self.aliasing = aliasing
+        self.frame_kernel = 0
         self.out_w, self.out_h = hs.width, hs.height
         s = hs.scaled(aliasing)
         _check(lib().rtb_scene_create(C.byref(s), device, flags, C.byref(self.h)))
@@ -328,6 +329,7 @@ class DeviceScene:
     def _opts(self, tracer, rank, nranks, count):
         o = FrameOpts()
         o.aliasing, o.tracer, o.rank, o.nranks, o.count_rays = self.aliasing, tracer, rank, nranks, int(count)
+        o.reserved[0] = self.frame_kernel     # 0: per-sample kernel (product path), 1: wavefront kernel
         return o
 
     def set_camera(self, cam_struct):

@@ -17,9 +17,11 @@ ap.add_argument("--k", default="")
 ap.add_argument("--w", type=int, default=3840)
 ap.add_argument("--h", type=int, default=2160)
 ap.add_argument("--count", action="store_true")
+ap.add_argument("--wave", action="store_true")
 a = ap.parse_args()
 hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
 ds = pyrtb.DeviceScene(hs, 3)
+ds.frame_kernel = int(a.wave)
 st = ds.stats()
 print("build %.2f ms upload %.2f ms nodes %d depth %d" % (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"]))
 ks = [float(x) for x in a.k.split(",")] if a.k else [None]
