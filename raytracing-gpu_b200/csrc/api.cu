@@ -5,6 +5,7 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <mutex>
 #include <vector>
 #include "rtb_internal.h"
 #include "scene_store.h"
@@ -41,10 +42,11 @@ static int pick_device(int device) {
     return RTB_ERR_NOGPU;
   }
   if (device < 0 || device >= n) { set_error("device %d out of range (0..%d)", device, n - 1); return RTB_ERR_ARG; }
-  cudaDeviceProp p;
-  RTB_CUDA(cudaGetDeviceProperties(&p, device));
-  if (p.major != 10) {
-    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, p.major, p.minor);
+  int major = 0, minor = 0;   // (cudaGetDeviceProperties costs ~2 ms per call; attributes are cheap)
+  RTB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+  RTB_CUDA(cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, device));
+  if (major != 10) {
+    set_error("device %d is sm_%d%d; this library is built for sm_100a only", device, major, minor);
     return RTB_ERR_NOGPU;
   }
   RTB_CUDA(cudaSetDevice(device));
@@ -152,6 +154,77 @@ static int finish_frame(SceneStore &S, cudaStream_t st) {
   return RTB_OK;
 }
 
+// ---- per-device cache: what a scene handle needs besides the scene itself ----
+struct FrameCtx {
+  int device, sm_count;
+  cudaStream_t stream;
+  cudaEvent_t ev0, ev1, tev0, tev1;
+  unsigned char *d_frame, *h_frame;
+  size_t d_frame_bytes, h_frame_bytes;
+  unsigned int *d_tile_counter;
+  unsigned long long *d_counters;
+  float *d_bounce;
+  size_t d_bounce_floats;
+};
+static std::mutex g_ctx_mu;
+static std::vector<FrameCtx> g_ctx_pool;
+static std::vector<int> g_pool_tuned;   // devices whose memory pool keeps freed blocks
+
+int acquire_frame_ctx(int device, SceneStore &S) {
+  {
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    bool tuned = false;
+    for (int d : g_pool_tuned) tuned |= d == device;
+    if (!tuned) {
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        unsigned long long keep = ~0ull;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+      cudaGetLastError();
+      g_pool_tuned.push_back(device);
+    }
+    for (size_t i = 0; i < g_ctx_pool.size(); ++i)
+      if (g_ctx_pool[i].device == device) {
+        const FrameCtx c = g_ctx_pool[i];
+        g_ctx_pool.erase(g_ctx_pool.begin() + i);
+        S.sm_count = c.sm_count; S.stream = c.stream; S.ev0 = c.ev0; S.ev1 = c.ev1; S.tev0 = c.tev0; S.tev1 = c.tev1;
+        S.d_frame = c.d_frame; S.h_frame = c.h_frame; S.d_frame_bytes = c.d_frame_bytes; S.h_frame_bytes = c.h_frame_bytes;
+        S.d_tile_counter = c.d_tile_counter; S.d_counters = c.d_counters; S.d_bounce = c.d_bounce;
+        S.d_bounce_floats = c.d_bounce_floats;
+        return RTB_OK;
+      }
+  }
+  RTB_CUDA(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking));
+  RTB_CUDA(cudaEventCreate(&S.ev0));
+  RTB_CUDA(cudaEventCreate(&S.ev1));
+  RTB_CUDA(cudaEventCreate(&S.tev0));
+  RTB_CUDA(cudaEventCreate(&S.tev1));
+  cudaDeviceGetAttribute(&S.sm_count, cudaDevAttrMultiProcessorCount, device);
+  return RTB_OK;
+}
+
+void recycle_frame_ctx(SceneStore &S) {
+  if (!S.stream) return;
+  FrameCtx c;
+  c.device = S.device; c.sm_count = S.sm_count; c.stream = S.stream; c.ev0 = S.ev0; c.ev1 = S.ev1; c.tev0 = S.tev0;
+  c.tev1 = S.tev1; c.d_frame = S.d_frame; c.h_frame = S.h_frame; c.d_frame_bytes = S.d_frame_bytes;
+  c.h_frame_bytes = S.h_frame_bytes; c.d_tile_counter = S.d_tile_counter; c.d_counters = S.d_counters;
+  c.d_bounce = S.d_bounce; c.d_bounce_floats = S.d_bounce_floats;
+  S.stream = nullptr; S.ev0 = S.ev1 = S.tev0 = S.tev1 = nullptr; S.d_frame = S.h_frame = nullptr;
+  S.d_frame_bytes = S.h_frame_bytes = 0; S.d_tile_counter = nullptr; S.d_counters = nullptr; S.d_bounce = nullptr;
+  S.d_bounce_floats = 0;
+  std::lock_guard<std::mutex> lk(g_ctx_mu);
+  if (g_ctx_pool.size() < 16) { g_ctx_pool.push_back(c); return; }
+  if (c.d_frame) cudaFree(c.d_frame);
+  if (c.h_frame) cudaFreeHost(c.h_frame);
+  if (c.d_tile_counter) cudaFree(c.d_tile_counter);
+  if (c.d_counters) cudaFree(c.d_counters);
+  if (c.d_bounce) cudaFree(c.d_bounce);
+  cudaEventDestroy(c.ev0); cudaEventDestroy(c.ev1); cudaEventDestroy(c.tev0); cudaEventDestroy(c.tev1);
+  cudaStreamDestroy(c.stream);
+}
+
 }  // namespace rtb
 
 using namespace rtb;
@@ -175,13 +248,8 @@ int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_
   rtb_scene_handle *h = new rtb_scene_handle();
   SceneStore &S = h->store;
   S.device = device;
-  cudaError_t e;
-  if ((e = cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)) != cudaSuccess ||
-      (e = cudaEventCreate(&S.ev0)) != cudaSuccess || (e = cudaEventCreate(&S.ev1)) != cudaSuccess) {
-    delete h;
-    return cuda_fail(e, "stream/event creation", __FILE__, __LINE__);
-  }
-  cudaDeviceGetAttribute(&S.sm_count, cudaDevAttrMultiProcessorCount, device);
+  rc = acquire_frame_ctx(device, S);
+  if (rc) { delete h; return rc; }
   rc = build_scene(scene, flags, &S);
   if (rc) { delete h; return rc; }
   *out = h;
@@ -371,7 +439,6 @@ int rtb_scene_timer_start(rtb_scene_t *h) {
   if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
   SceneStore &S = h->store;
   RTB_CUDA(cudaSetDevice(S.device));
-  if (!S.tev0) { RTB_CUDA(cudaEventCreate(&S.tev0)); RTB_CUDA(cudaEventCreate(&S.tev1)); }
   RTB_CUDA(cudaEventRecord(S.tev0, S.stream));
   return RTB_OK;
 }

@@ -318,32 +318,34 @@ float bits_to_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
 
 SceneStore::~SceneStore() { release(); }
 
+// Scene arrays come from the device's stream-ordered memory pool (cudaMallocAsync; api.cu
+// raises its release threshold), so a one-shot render() does not pay ~20 cudaMalloc/cudaFree
+// round trips per call the way the reference does (gpu/scene.cu:236-308, octree.cu:367-411).
+// Stream, events and frame buffers go back to a per-device cache (recycle_frame_ctx).
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_frame, d_tile_counter, d_counters, d_bounce};
-  for (void *p : ptrs) if (p) cudaFree(p);
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order};
+  for (void *p : ptrs) if (p) cudaFreeAsync(p, stream);
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
-  order = nullptr; d_frame = nullptr; d_tile_counter = nullptr; d_counters = nullptr; d_bounce = nullptr;
-  if (h_frame) { cudaFreeHost(h_frame); h_frame = nullptr; }
-  if (ev0) { cudaEventDestroy(ev0); ev0 = nullptr; }
-  if (ev1) { cudaEventDestroy(ev1); ev1 = nullptr; }
-  if (tev0) { cudaEventDestroy(tev0); tev0 = nullptr; }
-  if (tev1) { cudaEventDestroy(tev1); tev1 = nullptr; }
-  if (stream) { cudaStreamDestroy(stream); stream = nullptr; }
+  order = nullptr;
+  if (stream) cudaStreamSynchronize(stream);
+  recycle_frame_ctx(*this);
 }
 
 #define CK(call) do { int rc__ = (call); if (rc__) return rc__; } while (0)
 
+static thread_local cudaStream_t tl_alloc_stream = nullptr;   // set by build_scene
+
 template <typename T>
 static int dev_alloc(T **p, size_t count) {
   *p = nullptr;
-  RTB_CUDA(cudaMalloc((void **)p, (count ? count : 1) * sizeof(T)));
+  RTB_CUDA(cudaMallocAsync((void **)p, (count ? count : 1) * sizeof(T), tl_alloc_stream));
   return RTB_OK;
 }
 
-struct Temp {   // build-time scratch, freed when build_scene returns
+struct Temp {   // build-time scratch, freed (stream-ordered) when build_scene returns
   std::vector<void *> ptrs;
-  ~Temp() { for (void *p : ptrs) cudaFree(p); }
+  ~Temp() { for (void *p : ptrs) cudaFreeAsync(p, tl_alloc_stream); }
   template <typename T> int alloc(T **p, size_t count) {
     int rc = dev_alloc(p, count);
     if (!rc) ptrs.push_back(*p);
@@ -382,6 +384,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   }
   const uint32_t n = (uint32_t)total;
   cudaStream_t st = S->stream;
+  tl_alloc_stream = st;
   S->origin_radius = 2.0f * camera_origin_radius(hs->camera);   // x2 head-room for camera moves
   Temp tmp;
   cudaEvent_t e_up0 = S->ev0, e_up1 = S->ev1;

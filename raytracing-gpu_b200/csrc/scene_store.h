@@ -50,6 +50,9 @@ struct SceneStore {
 };
 
 int build_scene(const struct scene *hs, unsigned flags, SceneStore *S);
+// per-device cache of stream, events and frame buffers (api.cu)
+int acquire_frame_ctx(int device, SceneStore &S);
+void recycle_frame_ctx(SceneStore &S);
 float camera_origin_radius(const struct camera &cm);
 
 }  // namespace rtb

@@ -223,3 +223,51 @@ def test_build_is_deterministic_and_structurally_sound(gpu):
     finally:
         a.close()
         b.close()
+
+
+def test_rt_cli_end_to_end(gpu, tmp_path):
+    """rt file.svati output.png (gpu/rt.cpp:54-97): parse -> render -> PNG, and the .ppm variant."""
+    import os
+    import subprocess
+    from PIL import Image
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    rt = os.path.join(root, "raytracing-gpu_b200", "rt")
+    for name in ("cube", "dir-light-shadows"):
+        hs, z = load_golden(name)
+        svati, png = str(tmp_path / (name + ".svati")), str(tmp_path / (name + ".png"))
+        hs.write_svati(svati)
+        r = subprocess.run([rt, svati, png], capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        assert "Using structure of arrays (SOA) layout" in r.stdout and "lancement." in r.stdout and "done.." in r.stdout
+        img = np.asarray(Image.open(png).convert("RGBA"))
+        assert rgb_report(img, z["rgba"])[0] <= RGB_TOL_FRACTION and img.shape == z["rgba"].shape
+    ppm = str(tmp_path / "cube.ppm")
+    assert subprocess.run([rt, str(tmp_path / "cube.svati"), ppm], capture_output=True, timeout=300).returncode == 0
+    tok = open(ppm).read().split()
+    assert tok[:4] == ["P3", "512", "512", "255"]
+    body = np.array(tok[4:], dtype=np.int32).reshape(512, 512, 3)
+    assert np.array_equal(body, load_golden("cube")[1]["rgba"][..., :3])
+
+
+def test_set_camera_and_limit(gpu):
+    import ctypes as C
+    hs, z = load_golden("cube")
+    ds = pyrtb.DeviceScene(hs, 3)
+    try:
+        a = ds.render()
+        cam = pyrtb.Camera()
+        C.memmove(C.byref(cam), C.byref(hs.scaled(3).camera), C.sizeof(pyrtb.Camera))
+        cam.position.x += 0.5
+        ds.set_camera(cam)
+        b = ds.render()
+        assert not np.array_equal(a, b)
+        hs2 = pyrtb.HostScene.from_arrays(z["vertex"], z["normal"], z["tri_counts"], z["materials"], z["lights"], z["camera"])
+        hs2.s.camera.position.x += 0.5
+        want = oracle_py.orc_render(hs2, 3, want_ids=False)["rgba"]
+        assert rgb_report(b, want)[0] <= RGB_TOL_FRACTION
+        cam.position.x = 1e7      # far outside what the hierarchy was padded for
+        with pytest.raises(pyrtb.RtbError) as e:
+            ds.set_camera(cam)
+        assert e.value.code == pyrtb.RTB_ERR_LIMIT
+    finally:
+        ds.close()
