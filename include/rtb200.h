@@ -218,6 +218,11 @@ void rtb_set_margin_k(float k);
  * rtb_scene_render_device, so their tiles travel as NVLink peer stores. */
 void *rtb_host_alloc(size_t bytes);
 void rtb_host_free(void *p);
+/* Allocator behind empty_scene/add_object_to_scene (gpu/scene.cu:146-218): vertex and normal
+ * arrays of 1 MiB or more are page-locked when a device is present, so render()'s upload is a
+ * direct DMA; falls back to malloc.  rtb_scene_mem_free accepts either kind. */
+void *rtb_scene_mem_alloc(size_t bytes);
+void rtb_scene_mem_free(void *p);
 int rtb_dev_alloc(int device, size_t bytes, void **out);
 int rtb_dev_free(void *p);
 int rtb_dev_memset(void *p, int value, size_t bytes);

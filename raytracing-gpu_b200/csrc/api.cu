@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <mutex>
 #include <vector>
@@ -454,6 +455,35 @@ int rtb_scene_timer_stop(rtb_scene_t *h, double *ms_out) {
   RTB_CUDA(cudaEventElapsedTime(&ms, S.tev0, S.tev1));
   *ms_out = ms;
   return RTB_OK;
+}
+
+// ---- bulk memory of the host scene container (host/scene.cpp): pinned when a device exists ----
+static std::mutex g_pin_mu;
+static std::vector<void *> g_pinned;
+
+void *rtb_scene_mem_alloc(size_t bytes) {
+  void *p = nullptr;
+  if (bytes >= (1u << 20) && cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    g_pinned.push_back(p);
+    return p;
+  }
+  cudaGetLastError();
+  return malloc(bytes);
+}
+
+void rtb_scene_mem_free(void *p) {
+  if (!p) return;
+  {
+    std::lock_guard<std::mutex> lk(g_pin_mu);
+    for (size_t i = 0; i < g_pinned.size(); ++i)
+      if (g_pinned[i] == p) {
+        g_pinned.erase(g_pinned.begin() + i);
+        cudaFreeHost(p);
+        return;
+      }
+  }
+  free(p);
 }
 
 // ---- page-locked host memory and CUDA IPC helpers (multi-process tile gather) ----

@@ -9,7 +9,26 @@
 #include <cstring>
 #include "rt_host.h"
 
+// Vertex / normal arrays are the bulk of what render() uploads.  When the library that
+// hosts this file also provides page-locked allocation (librtb200.so: api.cu), the arrays
+// live in pinned memory and the upload runs at PCIe speed instead of being staged by the
+// driver; the host-only build (librt_host.so) has no such hook and uses malloc.
+extern "C" void *rtb_scene_mem_alloc(size_t bytes) __attribute__((weak));
+extern "C" void rtb_scene_mem_free(void *p) __attribute__((weak));
+
 namespace {
+
+void *bulk_alloc(size_t bytes) { return rtb_scene_mem_alloc ? rtb_scene_mem_alloc(bytes) : std::malloc(bytes); }
+void bulk_free(void *p) {
+  if (rtb_scene_mem_free) rtb_scene_mem_free(p);
+  else std::free(p);
+}
+vector3 *bulk_grow(vector3 *old, size_t old_count, size_t new_count) {
+  vector3 *p = static_cast<vector3 *>(bulk_alloc(new_count * sizeof(vector3)));
+  if (old && p) std::memcpy(p, old, old_count * sizeof(vector3));
+  if (old) bulk_free(old);
+  return p;
+}
 
 size_t capacity_for(size_t triangles) {
   size_t cap = 1024;
@@ -41,9 +60,9 @@ struct object *add_object_to_scene(struct scene *s, uint32_t nb_triangles) {
   const bool grow = s->objects_data.vertex == nullptr ||
                     capacity_for(new_total) != capacity_for(old_total);
   if (grow) {
-    const size_t bytes = capacity_for(new_total) * 3 * sizeof(vector3);
-    s->objects_data.vertex = static_cast<vector3 *>(std::realloc(s->objects_data.vertex, bytes));
-    s->objects_data.normal = static_cast<vector3 *>(std::realloc(s->objects_data.normal, bytes));
+    const size_t count = capacity_for(new_total) * 3;
+    s->objects_data.vertex = bulk_grow(s->objects_data.vertex, 3 * old_total, count);
+    s->objects_data.normal = bulk_grow(s->objects_data.normal, 3 * old_total, count);
   }
   // objects[] grows by powers of two as well
   size_t ocap = 16;
@@ -69,8 +88,8 @@ vector3 *get_normal(const struct triangles_layout t, uint32_t i) { return t.norm
 
 void free_scene(struct scene *s) {
   if (!s) return;
-  std::free(s->objects_data.vertex);
-  std::free(s->objects_data.normal);
+  if (s->objects_data.vertex) bulk_free(s->objects_data.vertex);
+  if (s->objects_data.normal) bulk_free(s->objects_data.normal);
   std::free(s->objects);
   std::free(s->lights);
   std::memset(s, 0, sizeof *s);
