@@ -25,10 +25,10 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 //   q1 = (c1.min.x, c1.max.x, c1.min.y, c1.max.y)
 //   q2 = (c0.min.z, c0.max.z, c1.min.z, c1.max.z)
 //   q3 = (as_float(ref0), as_float(ref1), as_float(first slot of range), as_float(slot count))
-// ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX.
+// ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX (3).
 // An empty child is a leaf with count 0 and an inverted box (+inf, -inf).
 #ifndef RTB_LEAF_MAX
-#define RTB_LEAF_MAX 4
+#define RTB_LEAF_MAX 3   /* C5, speculative traversal: 2: 43.4  3: 43.3  4: 43.9  6: 45.0 ms */
 #endif
 constexpr int LEAF_MAX = RTB_LEAF_MAX;
 constexpr int STACK_MAX = 96;        // inner-node depth limit (63 Morton bits + 32 index tie-break bits)

@@ -112,18 +112,21 @@ __device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
   return s;
 }
 
+// USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound)
+template <bool USE_TMAX = true>
 __device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, float loy, float hiy, float loz,
                                          float hiz, float tmax, float &tn) {
   const float x0 = __fmaf_rn(lox, s.ix, -s.ax), x1 = __fmaf_rn(hix, s.ix, -s.bx);
   const float y0 = __fmaf_rn(loy, s.iy, -s.ay), y1 = __fmaf_rn(hiy, s.iy, -s.by);
   const float z0 = __fmaf_rn(loz, s.iz, -s.az), z1 = __fmaf_rn(hiz, s.iz, -s.bz);
   tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-  const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+  const float tf = USE_TMAX ? fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax))
+                            : fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
   return tn <= tf;
 }
 
 #ifndef RTB_LOOP_SHAPE
-#define RTB_LOOP_SHAPE 0
+#define RTB_LOOP_SHAPE 2
 #endif
 constexpr int TRAVERSAL_DONE = (int)0x80000000;   // stack sentinel: not a valid leaf reference
 
@@ -131,6 +134,9 @@ constexpr int TRAVERSAL_DONE = (int)0x80000000;   // stack sentinel: not a valid
 // (or has nothing left), then the warp tests triangles together.  Keeping the two phases
 // apart keeps the lanes of a warp in the same code at the same time; with a single
 // if-inner-else-leaf loop the triangle code ran at 7.5 of 32 lanes (profiles/r1_v1).
+// Default shape 2 adds Aila-Laine style speculation: a lane that reaches its first leaf
+// keeps it aside and goes on descending until every lane of the warp holds one
+// (C5: 46.8 -> 44.5 ms).  Shapes 0 (plain while-while) and 1 (if-if) remain for A/B builds.
 template <bool ANY, bool COUNT>
 __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
   best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
@@ -144,6 +150,53 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
   stack[0] = TRAVERSAL_DONE;
   int sp = 1;
   int cur = sc.root;
+#if RTB_LOOP_SHAPE == 2   /* while-while with one postponed leaf (speculative traversal) */
+  int pending = 0;        // leaf references are negative, 0 = none held
+  for (;;) {
+    while (cur >= 0) {
+      if (COUNT) ++c.nodes;
+      const float4 *np = sc.nodes + 4ll * cur;
+      const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
+      float tn0, tn1;
+      const bool h0 = slab_hit<!ANY>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
+      const bool h1 = slab_hit<!ANY>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
+      const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
+      if (h0 && h1) {
+        // shadow rays only ask "anything?": no near-first ordering (42.7 vs 43.9 ms on C5)
+#ifdef RTB_ANY_ORDERED
+        const bool far0 = tn1 < tn0;
+#else
+        const bool far0 = ANY ? false : tn1 < tn0;
+#endif
+        cur = far0 ? r1 : r0;
+        stack[sp++] = far0 ? r0 : r1;
+      } else if (h0) cur = r0;
+      else if (h1) cur = r1;
+      else cur = stack[--sp];
+      if (cur < 0 && cur != TRAVERSAL_DONE && pending == 0) {   // first leaf: keep it, go on
+        pending = cur;
+        cur = stack[--sp];
+      }
+      if (!__any_sync(__activemask(), pending == 0)) break;     // every lane here holds a leaf
+    }
+    while (pending != 0 || (cur < 0 && cur != TRAVERSAL_DONE)) {
+      int leaf;
+      if (pending != 0) { leaf = pending; pending = 0; }
+      else { leaf = cur; cur = stack[--sp]; }
+      const uint32_t packed = (uint32_t)~leaf;
+      const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
+      for (int k = 0; k < cnt; ++k) {
+        if (COUNT) ++c.tris;
+        if (consider<ANY>(sc, o, d, first + k, best)) {
+          if (ANY) return true;
+          tmax = (best.dist * 1.0001f + eps) * inv_len;
+        }
+      }
+    }
+    if (cur == TRAVERSAL_DONE) break;
+  }
+  return best.slot >= 0;
+#else
   for (;;) {
 #if RTB_LOOP_SHAPE == 1   /* if-if: one node OR one leaf per trip */
     if (cur >= 0) {
@@ -181,6 +234,7 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
     cur = stack[--sp];
   }
   return best.slot >= 0;
+#endif
 }
 
 template <int TRACER, bool ANY, bool COUNT>
