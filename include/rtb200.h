@@ -190,7 +190,8 @@ int rtb_inclusive_scan_u64(uint64_t *data, size_t n);
 
 /* Device-resident variants used by the build itself and by micro-benchmarks
  * (gpu/bench.cu:435-451).  Pointers are device pointers; `stream` a cudaStream_t.
- * Scratch is allocated internally and cached per call site size. */
+ * Scratch comes from the stream-ordered memory pool on `stream`; the calls are asynchronous:
+ * results are ready in stream order (synchronise the stream before reading them on the host). */
 int rtb_dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, size_t n,
                                  int key_bits, void *stream);
 int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream);

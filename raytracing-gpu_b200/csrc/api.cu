@@ -171,20 +171,23 @@ static std::mutex g_ctx_mu;
 static std::vector<FrameCtx> g_ctx_pool;
 static std::vector<int> g_pool_tuned;   // devices whose memory pool keeps freed blocks
 
+// cudaMallocAsync's default pool hands freed blocks back to the driver at every
+// synchronisation unless told to keep them; keeping them makes scratch allocation ~1 us.
+static void tune_pool_locked(int device) {
+  for (int d : g_pool_tuned) if (d == device) return;
+  cudaMemPool_t pool;
+  if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+    unsigned long long keep = ~0ull;
+    cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  }
+  cudaGetLastError();
+  g_pool_tuned.push_back(device);
+}
+
 int acquire_frame_ctx(int device, SceneStore &S) {
   {
     std::lock_guard<std::mutex> lk(g_ctx_mu);
-    bool tuned = false;
-    for (int d : g_pool_tuned) tuned |= d == device;
-    if (!tuned) {
-      cudaMemPool_t pool;
-      if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-        unsigned long long keep = ~0ull;
-        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-      }
-      cudaGetLastError();
-      g_pool_tuned.push_back(device);
-    }
+    tune_pool_locked(device);
     for (size_t i = 0; i < g_ctx_pool.size(); ++i)
       if (g_ctx_pool[i].device == device) {
         const FrameCtx c = g_ctx_pool[i];
@@ -601,24 +604,36 @@ int rtb_inclusive_scan_u64(uint64_t *data, size_t n) {
   return RTB_OK;
 }
 
+// Scratch comes from the stream-ordered pool on the caller's stream: no device-wide
+// synchronisation, and after the first call of a given size no driver allocation either.
+static int pool_scratch(void **p, size_t bytes, cudaStream_t st) {
+  int device = 0;
+  RTB_CUDA(cudaGetDevice(&device));
+  { std::lock_guard<std::mutex> lk(g_ctx_mu); tune_pool_locked(device); }
+  RTB_CUDA(cudaMallocAsync(p, bytes, st));
+  return RTB_OK;
+}
+
 int rtb_dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, size_t n, int key_bits, void *stream) {
   if (!n) return RTB_OK;
   if (!d_keys || !d_vals) { set_error("NULL argument"); return RTB_ERR_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
-  uint64_t *dk2 = nullptr;
-  uint32_t *dv2 = nullptr, *ds = nullptr;
   const size_t sw = radix_sort_scratch_words(n);
-  cudaError_t e = cudaMalloc((void **)&dk2, n * 8);
-  if (e == cudaSuccess) e = cudaMalloc((void **)&dv2, n * 4);
-  if (e == cudaSuccess) e = cudaMalloc((void **)&ds, sw * 4);
-  int rc = RTB_OK, in_alt = 0;
-  if (e == cudaSuccess) rc = dev_radix_sort_pairs_u64(d_keys, d_vals, dk2, dv2, n, key_bits, ds, sw, st, &in_alt, nullptr);
-  if (e == cudaSuccess && !rc && in_alt) {
+  // one block: alternate keys | alternate values | histogram scratch
+  const size_t off_v = (n * 8 + 255) & ~(size_t)255, off_s = (off_v + n * 4 + 255) & ~(size_t)255;
+  unsigned char *blk = nullptr;
+  int rc = pool_scratch((void **)&blk, off_s + sw * 4, st);
+  if (rc) return rc;
+  uint64_t *dk2 = (uint64_t *)blk;
+  uint32_t *dv2 = (uint32_t *)(blk + off_v), *ds = (uint32_t *)(blk + off_s);
+  int in_alt = 0;
+  rc = dev_radix_sort_pairs_u64(d_keys, d_vals, dk2, dv2, n, key_bits, ds, sw, st, &in_alt, nullptr);
+  cudaError_t e = cudaSuccess;
+  if (!rc && in_alt) {
     e = cudaMemcpyAsync(d_keys, dk2, n * 8, cudaMemcpyDeviceToDevice, st);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_vals, dv2, n * 4, cudaMemcpyDeviceToDevice, st);
   }
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(dk2); cudaFree(dv2); cudaFree(ds);
+  cudaFreeAsync(blk, st);
   if (rc) return rc;
   if (e != cudaSuccess) return cuda_fail(e, "device radix sort", __FILE__, __LINE__);
   return RTB_OK;
@@ -630,13 +645,11 @@ int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream) {
   cudaStream_t st = (cudaStream_t)stream;
   uint32_t *s = nullptr;
   const size_t sw = scan_scratch_words(n);
-  RTB_CUDA(cudaMalloc((void **)&s, sw * 4));
-  int rc = dev_exclusive_scan_u32(d_data, n, s, sw, true, st, nullptr);
-  cudaError_t e = cudaStreamSynchronize(st);
-  cudaFree(s);
+  int rc = pool_scratch((void **)&s, (sw ? sw : 1) * 4, st);
   if (rc) return rc;
-  if (e != cudaSuccess) return cuda_fail(e, "device scan", __FILE__, __LINE__);
-  return RTB_OK;
+  rc = dev_exclusive_scan_u32(d_data, n, s, sw, true, st, nullptr);
+  cudaFreeAsync(s, st);
+  return rc;
 }
 
 }  // extern "C"

@@ -261,6 +261,20 @@ __global__ void __launch_bounds__(BT) k_live(const RawNode *raw, uint32_t n_inne
   if (j < n_inner) live[j] = raw[j].cnt > LEAF_MAX ? 1u : 0u;
 }
 
+// (min, max) pairs -> (centre, half extent) pairs, the half extent rounded outwards so
+// that [c - h, c + h] contains [min, max].  An inverted (empty) box becomes h = -inf.
+__device__ __forceinline__ void centre_half(float lo, float hi, float &c, float &h) {
+  if (!(lo <= hi)) { c = 0.0f; h = -__int_as_float(0x7f800000); return; }
+  c = 0.5f * lo + 0.5f * hi;
+  h = fmaxf(hi - c, c - lo) * 1.000001f;
+}
+__device__ __forceinline__ float4 to_centre_half(float4 q) {
+  float4 r;
+  centre_half(q.x, q.y, r.x, r.y);
+  centre_half(q.z, q.w, r.z, r.w);
+  return r;
+}
+
 // new_index = exclusive scan of live.  stats: [0] leaves, [1] max leaf size
 __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
                                                 float4 *nodes, unsigned int *stats) {
@@ -272,9 +286,15 @@ __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_i
   if (nd.ref0 >= 0) nd.ref0 = (int)new_index[nd.ref0]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref0 & 7)); }
   if (nd.ref1 >= 0) nd.ref1 = (int)new_index[nd.ref1]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref1 & 7)); }
   float4 *dst = nodes + 4ull * new_index[j];
+#if RTB_NODE_CH
+  dst[0] = to_centre_half(nd.q0);
+  dst[1] = to_centre_half(nd.q1);
+  dst[2] = to_centre_half(nd.q2);
+#else
   dst[0] = nd.q0;
   dst[1] = nd.q1;
   dst[2] = nd.q2;
+#endif
   dst[3] = make_float4(__int_as_float(nd.ref0), __int_as_float(nd.ref1), __int_as_float(nd.lo), __int_as_float(nd.cnt));
   if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
 }
@@ -288,9 +308,15 @@ __global__ void k_single_node(const uint32_t *bounds, uint32_t n, float4 *nodes)
     lx = ord2f(bounds[0]); ly = ord2f(bounds[1]); lz = ord2f(bounds[2]);
     hx = ord2f(bounds[3]); hy = ord2f(bounds[4]); hz = ord2f(bounds[5]);
   }
+#if RTB_NODE_CH
+  nodes[0] = to_centre_half(make_float4(lx, hx, ly, hy));
+  nodes[1] = to_centre_half(make_float4(INF, -INF, INF, -INF));
+  nodes[2] = to_centre_half(make_float4(lz, hz, INF, -INF));
+#else
   nodes[0] = make_float4(lx, hx, ly, hy);
   nodes[1] = make_float4(INF, -INF, INF, -INF);
   nodes[2] = make_float4(lz, hz, INF, -INF);
+#endif
   nodes[3] = make_float4(__int_as_float(leaf_ref(0, n)), __int_as_float(leaf_ref(0, 0)), __int_as_float(0),
                          __int_as_float((int)n));
 }

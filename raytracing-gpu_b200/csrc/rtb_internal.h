@@ -27,6 +27,12 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 //   q3 = (as_float(ref0), as_float(ref1), as_float(first slot of range), as_float(slot count))
 // ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX (3).
 // An empty child is a leaf with count 0 and an inverted box (+inf, -inf).
+// A/B option RTB_NODE_CH=1 stores every (min, max) pair above as (centre, half extent), half
+// extent rounded outwards (build.cu centre_half): 12 FFMA + 4 FMNMX per box instead of
+// 6 FFMA + 10 FMNMX.  Measured slower on C5 (43.05 vs 42.04 ms), so min/max is the default.
+#ifndef RTB_NODE_CH
+#define RTB_NODE_CH 0
+#endif
 #ifndef RTB_LEAF_MAX
 #define RTB_LEAF_MAX 3   /* C5, speculative traversal: 2: 43.4  3: 43.3  4: 43.9  6: 45.0 ms */
 #endif

@@ -2,7 +2,7 @@
 built for sm_100) next to librtb200 on the shipped scenes: wall time of the drop-in call
 render() (upload + partitioning build + frame + download, what the reference API offers) and
 pixel differences of both against the un-fused semantic definition (tests/golden).
-usage: python tools/ref_gpu_compare.py [--scale S] [scene ...]     (one subprocess per scene, with a timeout)"""
+usage: python tests/reports/ref_gpu_compare.py [--scale S] [scene ...]     (one subprocess per scene, with a timeout)"""
 import argparse
 import ctypes as C
 import os
@@ -12,9 +12,9 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, os.path.join(ROOT, "raytracing-gpu_b200"))
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))  # util.py
 
 
 def one(name, scale):
