@@ -180,29 +180,112 @@ __device__ __forceinline__ void load_child(const volatile RawNode *nd, int side,
 
 // One thread per sorted triangle.  visit[j] (initialised to -1) receives the range bound
 // of the first child to arrive at inner node j; the second child continues upwards.
-// Sliver padding.  The rounded Moeller-Trumbore test accepts rays that pass within
-// delta ~ few * 2^-24 * |origin - vertex| of a triangle's edges; beyond a corner of
-// interior angle theta that region reaches delta / sin(theta/2) past the vertex, which for
-// needle triangles exceeds the uniform ray-time margin (tests/golden island_smooth has a
-// 2.4-degree needle: 1 of 4.67 M samples was culled before this).  Leaf boxes of triangles
-// whose sharpest corner gives 1/sin(theta/2) > SLIVER_KAPPA0 are therefore grown by
-// pad_unit * kappa, pad_unit = SLIVER_K * 2^-23 * (largest |coordinate| a ray origin or the
-// scene can have); inner boxes inherit it through the union.
+// Needle padding.  In ray space (the plane perpendicular to the ray) the rounded
+// Moeller-Trumbore test is "inside three half-planes", each edge line displaced by the rounding
+// noise: u = s.(d x e2) / a is |d| |e2'| dist(ray, line of e2) / a, and the numerator is
+// computed with an absolute error of c 2^-24 |s| |d x e2| (c about 3..10), so the lines of e1
+// and e2 move by delta = c 2^-24 |s|, |s| = |origin - vertex0|, whatever the triangle.  The
+// third edge is tested as u + v <= 1: u and v carry delta / (their height), which moves that
+// line by delta (|e1| + |e2|) / |e3|: 47 delta for the 2.4-degree needle of
+// tests/golden island_smooth, whose short edge is the one opposite vertex 0 (the sample that
+// found this: accepted 0.033 from the triangle, 1 wrong id in 4.67 M before the padding).
+// Distances in ray space are 3D distances between ray and triangle, so the cure is an isotropic
+// pad of the leaf box by pad_unit (|e1| + |e2|) / |e3| when that ratio exceeds SLIVER_KAPPA0
+// (the ray-time margin of trace.cu, 48 2^-24 (|o| + |scene|), covers the rest).  Displaced
+// lines meet delta / sin(theta) beyond a corner of interior angle theta: corners sharper than
+// 1 / sin(theta/2) > SLIVER_KAPPA0 get that spike added to the box (direction-aware, so a
+// needle's box stays thin).  pad_unit = SLIVER_K 2^-23 (|scene| + origin_radius), i.e.
+// c = 2 SLIVER_K = 6 at the largest |s| the scene handle accepts; pads are capped at the
+// longest edge and inherited by inner boxes through the union.  What no finite pad covers:
+// triangles seen edge-on (a -> 0), accepted by the reference arithmetic anywhere in their
+// plane.
 constexpr float SLIVER_KAPPA0 = 4.0f;
-constexpr float SLIVER_K = 6.0f;
+#ifndef RTB_SLIVER_K
+#define RTB_SLIVER_K 3.0f
+#endif
+constexpr float SLIVER_K = RTB_SLIVER_K;
+#ifndef RTB_SLIVER_MODE
+#define RTB_SLIVER_MODE 5   /* 0: none, 1: isotropic by the sharpest corner, 2: corner spikes, 3: spikes of the
+                               sharpest corner at every corner, 5 (product): third-edge slop + corner spikes */
+#endif
 
-__device__ __forceinline__ float sliver_kappa(const float *raw_v, uint32_t i, float &longest) {
+// 1 / sin(theta / 2) for the corner between unit-length-normalised edges (cosine given)
+__device__ __forceinline__ float corner_kappa(float cosine) {
+  const float c = fminf(cosine, 1.0f);
+  return fminf(1.0f / sqrtf(fmaxf(0.5f * (1.0f - c), 1e-12f)), 1.0e4f);
+}
+
+__device__ __forceinline__ void grow(V3 &lo, V3 &hi, const V3 p) {
+  lo = mk(fminf(lo.x, p.x), fminf(lo.y, p.y), fminf(lo.z, p.z));
+  hi = mk(fmaxf(hi.x, p.x), fmaxf(hi.y, p.y), fmaxf(hi.z, p.z));
+}
+
+// Grows [lo, hi] (the triangle's box).  pad_unit = SLIVER_K * 2^-23 * scale.
+// Corner spikes: at a corner v with unit edge directions a, b and interior angle theta, edge
+// lines pushed out by delta_a, delta_b <= delta meet at v - (delta_b a + delta_a b) / sin(theta),
+// inside the parallelogram v - m (s a + t b), s, t in [0, 1], m = delta / sin(theta)
+// <= pad_unit * kappa / 2.  That spike is added to the box with m = pad_unit * kappa.
+__device__ __forceinline__ void sliver_pad(const float *raw_v, uint32_t i, float pad_unit, V3 &lo, V3 &hi) {
+#if RTB_SLIVER_MODE == 0
+  return;
+#else
   const float *p = raw_v + 9ull * i;
-  const V3 a = mk(p[0], p[1], p[2]), b = mk(p[3], p[4], p[5]), c = mk(p[6], p[7], p[8]);
-  const V3 ab = vsub(b, a), bc = vsub(c, b), ca = vsub(a, c);
+  const V3 v[3] = {mk(p[0], p[1], p[2]), mk(p[3], p[4], p[5]), mk(p[6], p[7], p[8])};
+  const V3 ab = vsub(v[1], v[0]), bc = vsub(v[2], v[1]), ca = vsub(v[0], v[2]);
   const float lab = vlen(ab), lbc = vlen(bc), lca = vlen(ca);
-  longest = fmaxf(fmaxf(lab, lbc), lca);
-  if (!(lab > 0) || !(lbc > 0) || !(lca > 0)) return 0.0f;   // two equal vertices: a == 0 exactly, never accepted
-  // cos of the interior angles at a, b, c
-  const float ca_ = -vdot(ab, ca) / (lab * lca), cb_ = -vdot(ab, bc) / (lab * lbc), cc_ = -vdot(bc, ca) / (lbc * lca);
-  const float cmax = fminf(fmaxf(fmaxf(ca_, cb_), cc_), 1.0f);
-  const float s = sqrtf(fmaxf(0.5f * (1.0f - cmax), 1e-12f));   // sin(theta_min / 2)
-  return fminf(1.0f / s, 1.0e4f);
+  if (!(lab > 0) || !(lbc > 0) || !(lca > 0)) return;   // two equal vertices: a == 0 exactly, never accepted
+  const float longest = fmaxf(fmaxf(lab, lbc), lca);
+  // unit edge directions leaving each corner, and the corner cosines
+  const V3 d_ab = vscale(ab, 1.0f / lab), d_bc = vscale(bc, 1.0f / lbc), d_ca = vscale(ca, 1.0f / lca);
+  const V3 out0[2] = {d_ab, vscale(d_ca, -1.0f)};       // from a: towards b, towards c
+  const V3 out1[2] = {d_bc, vscale(d_ab, -1.0f)};       // from b: towards c, towards a
+  const V3 out2[2] = {d_ca, vscale(d_bc, -1.0f)};       // from c: towards a, towards b
+  const float kap[3] = {corner_kappa(vdot(out0[0], out0[1])), corner_kappa(vdot(out1[0], out1[1])),
+                        corner_kappa(vdot(out2[0], out2[1]))};
+#if RTB_SLIVER_MODE == 1
+  const float kappa = fmaxf(fmaxf(kap[0], kap[1]), kap[2]);
+  if (kappa > SLIVER_KAPPA0) {
+    // the u,v <= 1 tests keep accepted rays within about one edge length of the triangle
+    const float pad = fminf(pad_unit * kappa, longest);
+    lo = mk(lo.x - pad, lo.y - pad, lo.z - pad);
+    hi = mk(hi.x + pad, hi.y + pad, hi.z + pad);
+  }
+#else
+  const V3 *outs[3] = {out0, out1, out2};
+#if RTB_SLIVER_MODE == 5
+  // u + v <= 1 is the edge opposite vertex 0; u and v carry an absolute error of
+  // delta / (height over their edge) each, so that edge line is pushed out by
+  // delta * (|e1| + |e2|) / |e3| in ray space: large when the SHORT edge of a needle is the
+  // one opposite vertex 0.  A distance in ray space is a distance in 3D between ray and
+  // triangle, whatever the incidence: isotropic pad.
+  {
+    const float ratio = (lab + lca) / lbc;
+    if (ratio > SLIVER_KAPPA0) {
+      const float pad = fminf(pad_unit * ratio, longest);
+      lo = mk(lo.x - pad, lo.y - pad, lo.z - pad);
+      hi = mk(hi.x + pad, hi.y + pad, hi.z + pad);
+    }
+  }
+#endif
+#if RTB_SLIVER_MODE == 3   /* every corner gets the spike of the sharpest one */
+  const float kmax = fmaxf(fmaxf(kap[0], kap[1]), kap[2]);
+#endif
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+#if RTB_SLIVER_MODE == 3
+    if (!(kmax > SLIVER_KAPPA0)) continue;
+    const float m = fminf(pad_unit * kmax, longest);
+#else
+    if (!(kap[c] > SLIVER_KAPPA0)) continue;
+    const float m = fminf(pad_unit * kap[c], longest);
+#endif
+    const V3 sa = vscale(outs[c][0], m), sb = vscale(outs[c][1], m);
+    grow(lo, hi, vsub(v[c], sa));
+    grow(lo, hi, vsub(v[c], sb));
+    grow(lo, hi, vsub(vsub(v[c], sa), sb));
+  }
+#endif
+#endif
 }
 
 __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
@@ -214,16 +297,9 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
   V3 lo, hi;
   tri_box(raw_v, order[i], lo, hi);
   {
-    float longest = 0;
-    const float kappa = sliver_kappa(raw_v, order[i], longest);
-    if (kappa > SLIVER_KAPPA0) {
-      float amax = 0;
-      for (int k = 0; k < 6; ++k) amax = fmaxf(amax, fabsf(ord2f(bounds[k])));
-      // the u,v <= 1 tests keep accepted rays within about one edge length of the triangle
-      const float pad = fminf(SLIVER_K * 1.1920929e-7f * (amax + origin_radius) * kappa, longest);
-      lo = mk(lo.x - pad, lo.y - pad, lo.z - pad);
-      hi = mk(hi.x + pad, hi.y + pad, hi.z + pad);
-    }
+    float amax = 0;
+    for (int k = 0; k < 6; ++k) amax = fmaxf(amax, fabsf(ord2f(bounds[k])));
+    sliver_pad(raw_v, order[i], SLIVER_K * 1.1920929e-7f * (amax + origin_radius), lo, hi);
   }
   uint32_t l = i, r = i;
   int cur = -1;       // raw inner index of the node we stand on (-1: still the single triangle)
@@ -261,10 +337,13 @@ __global__ void __launch_bounds__(BT) k_live(const RawNode *raw, uint32_t n_inne
   if (j < n_inner) live[j] = raw[j].cnt > LEAF_MAX ? 1u : 0u;
 }
 
+#if RTB_NODE_CH
 // (min, max) pairs -> (centre, half extent) pairs, the half extent rounded outwards so
 // that [c - h, c + h] contains [min, max].  An inverted (empty) box becomes h = -inf.
 __device__ __forceinline__ void centre_half(float lo, float hi, float &c, float &h) {
-  if (!(lo <= hi)) { c = 0.0f; h = -__int_as_float(0x7f800000); return; }
+  const float inf = __int_as_float(0x7f800000);
+  if (!(lo <= hi)) { c = 0.0f; h = -inf; return; }
+  if (lo == -inf || hi == inf) { c = 0.0f; h = inf; return; }
   c = 0.5f * lo + 0.5f * hi;
   h = fmaxf(hi - c, c - lo) * 1.000001f;
 }
@@ -274,6 +353,7 @@ __device__ __forceinline__ float4 to_centre_half(float4 q) {
   centre_half(q.z, q.w, r.z, r.w);
   return r;
 }
+#endif
 
 // new_index = exclusive scan of live.  stats: [0] leaves, [1] max leaf size
 __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
@@ -300,14 +380,12 @@ __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_i
 }
 
 // Scenes of at most LEAF_MAX triangles (and brute-force-only scenes): one node whose first
-// child is a leaf over everything, boxed by the scene bounds, second child empty.
-__global__ void k_single_node(const uint32_t *bounds, uint32_t n, float4 *nodes) {
+// child is a leaf over everything with an unbounded box (nothing to cull, so nothing to pad),
+// second child empty.
+__global__ void k_single_node(uint32_t n, float4 *nodes) {
   const float INF = __int_as_float(0x7f800000);
   float lx = INF, ly = INF, lz = INF, hx = -INF, hy = -INF, hz = -INF;
-  if (n) {
-    lx = ord2f(bounds[0]); ly = ord2f(bounds[1]); lz = ord2f(bounds[2]);
-    hx = ord2f(bounds[3]); hy = ord2f(bounds[4]); hz = ord2f(bounds[5]);
-  }
+  if (n) { lx = ly = lz = -INF; hx = hy = hz = INF; }
 #if RTB_NODE_CH
   nodes[0] = to_centre_half(make_float4(lx, hx, ly, hy));
   nodes[1] = to_centre_half(make_float4(INF, -INF, INF, -INF));
@@ -548,7 +626,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     S->n_leaves = h_stats[0]; S->max_leaf = h_stats[1];
   } else {
     CK(dev_alloc(&S->nodes, 4));
-    k_single_node<<<1, 1, 0, st>>>(d_bounds, n, S->nodes);
+    k_single_node<<<1, 1, 0, st>>>(n, S->nodes);
     ++launches;
   }
   uint32_t h_bounds[8];

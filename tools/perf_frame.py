@@ -18,8 +18,14 @@ ap.add_argument("--w", type=int, default=3840)
 ap.add_argument("--h", type=int, default=2160)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--wave", action="store_true")
+ap.add_argument("--scene", default=None, help="golden scene name instead of the terrain (rendered at --w x --h)")
 a = ap.parse_args()
-hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
+if a.scene:
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from util import load_golden
+    hs = load_golden(a.scene)[0].with_resolution(a.w, a.h)
+else:
+    hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
 ds = pyrtb.DeviceScene(hs, 3)
 ds.frame_kernel = int(a.wave)
 st = ds.stats()
