@@ -213,6 +213,11 @@ int rtb_scene_timer_stop(rtb_scene_t *h, double *ms_out);
  * |ray origin| + |scene| (DESIGN.md "conservative culling").  Tests and probes only. */
 void rtb_set_margin_k(float k);
 
+/* Longest-first scheduling of the frame's work items from the previous frame's measured
+ * costs (resident scenes, from the third frame of a handle on).  On by default; 0 turns it
+ * off for A/B measurements.  The frame's bytes do not depend on it. */
+void rtb_set_schedule(int on);
+
 /* Page-locked host memory (a frame buffer the D2H copy can target directly) and plain
  * device buffers / CUDA-IPC handles for the multi-process tile gather: rank 0 exports
  * its frame, the other ranks open it and pass the mapped pointer to

@@ -102,6 +102,8 @@ static int check_frame(const SceneStore &S, const rtb_frame_opts *o, int out_h, 
   return RTB_OK;
 }
 
+static bool g_schedule = true;   // rtb_set_schedule (tests, A/B)
+
 static int ensure_frame_resources(SceneStore &S) {
   if (!S.d_tile_counter) RTB_CUDA(cudaMalloc((void **)&S.d_tile_counter, sizeof(unsigned int)));
   if (!S.d_counters) RTB_CUDA(cudaMalloc((void **)&S.d_counters, 8 * sizeof(unsigned long long)));
@@ -123,6 +125,8 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.pitch = (long long)pitch;
   fa.tile_counter = S.d_tile_counter;
   fa.counters = S.d_counters;
+  fa.item_order = nullptr;
+  fa.item_cost = nullptr;
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
@@ -138,10 +142,60 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     }
     fa.bounce_scratch = S.d_bounce;
   }
+  // Longest-first scheduling.  Warps take work items from an atomic counter; near the end of
+  // the frame the slowest item in flight sets the tail (one item is 1/55 of a warp's frame at
+  // 4K on one GPU, 1/7 on eight).  The second frame of a handle (and the first after every
+  // camera change) records each item's cost; a 2-pass radix sort of the 16-bit costs on the
+  // same stream gives the order the following frames use.  A one-shot render never gets here.
+  const bool schedule = g_schedule && !fa.bounce_scratch && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
+                        S.frames_done >= 1;
+  bool record = false;
+  uint64_t *sk = nullptr, *sk2 = nullptr;
+  uint32_t *sv = nullptr, *sv2 = nullptr, *ss = nullptr;
+  size_t ssw = 0;
+  unsigned n_items = 0;
+  if (schedule) {
+    n_items = frame_item_count(out_w, out_h, o.nranks);
+    const int key[5] = {o.rank, o.nranks, out_w, out_h, o.aliasing};
+    const size_t cap = ((size_t)n_items + 255) & ~(size_t)255;
+    if (S.sched_items < cap) {
+      if (S.d_sched) cudaFreeAsync(S.d_sched, st);
+      S.d_sched = nullptr; S.d_item_order = nullptr; S.sched_items = 0;
+      const size_t bytes = cap * (2 + 8 + 8 + 4 + 4) + radix_sort_scratch_words(cap) * 4 + 1024;
+      RTB_CUDA(cudaMallocAsync((void **)&S.d_sched, bytes, st));
+      S.sched_items = cap;
+    }
+    if (memcmp(key, S.sched_key, sizeof key) != 0) {
+      memcpy(S.sched_key, key, sizeof key);
+      S.d_item_order = nullptr;
+    }
+    const size_t c = S.sched_items;
+    sk = (uint64_t *)S.d_sched; sk2 = sk + c;
+    sv = (uint32_t *)(sk2 + c); sv2 = sv + c;
+    ss = sv2 + c;
+    ssw = radix_sort_scratch_words(c);
+    unsigned short *cost = (unsigned short *)(ss + ssw + 64);
+    record = !S.d_item_order || S.order_camera_gen != S.camera_gen;
+    fa.item_order = S.d_item_order;
+    if (record) {
+      // the current order (if any) lives in sv or sv2 and is read by this frame: the new one is
+      // sorted after the frame on the same stream, so overwriting either is safe
+      RTB_CUDA(cudaMemsetAsync(cost, 0, (size_t)n_items * 2, st));
+      fa.item_cost = cost;
+    }
+  }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches);
   if (rc) return rc;
   RTB_CUDA(cudaEventRecord(S.ev1, st));
+  if (record) {
+    int in_alt = 0;
+    rc = launch_item_order(fa.item_cost, n_items, sk, sv, sk2, sv2, ss, ssw, st, &in_alt);
+    if (rc) return rc;
+    S.d_item_order = in_alt ? sv2 : sv;
+    S.order_camera_gen = S.camera_gen;
+  }
+  ++S.frames_done;
   if (o.count_rays)
     RTB_CUDA(cudaMemcpyAsync(S.counters, S.d_counters, sizeof S.counters, cudaMemcpyDeviceToHost, st));
   return RTB_OK;
@@ -270,6 +324,7 @@ int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam) {
     return RTB_ERR_LIMIT;
   }
   h->store.camera = *cam;
+  ++h->store.camera_gen;
   return RTB_OK;
 }
 
@@ -437,6 +492,7 @@ int rtb_scene_root(rtb_scene_t *h) { return h ? h->store.root : -1; }
 
 /* extension (tests): box inflation factor of the conservative slab test */
 void rtb_set_margin_k(float k) { set_margin_k(k); }
+void rtb_set_schedule(int on) { g_schedule = on != 0; }
 
 // ---- bracket timer on the library stream (bench: K frames between two events) ----
 int rtb_scene_timer_start(rtb_scene_t *h) {

@@ -428,10 +428,11 @@ SceneStore::~SceneStore() { release(); }
 // Stream, events and frame buffers go back to a per-device cache (recycle_frame_ctx).
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order};
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_sched};
   for (void *p : ptrs) if (p) cudaFreeAsync(p, stream);
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
   order = nullptr;
+  d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);
   recycle_frame_ctx(*this);
 }

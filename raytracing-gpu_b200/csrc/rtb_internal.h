@@ -71,6 +71,10 @@ struct FrameArgs {
   unsigned char *out;       // device (or peer-mapped) RGBA8, row 0 = top
   long long pitch;
   unsigned int *tile_counter;
+  // work-item scheduling (trace.cu frame_item): order to take the items in (nullptr = 0,1,2,..)
+  // and where to leave each item's cost, in 64-cycle units (nullptr = not recorded)
+  const unsigned int *item_order;
+  unsigned short *item_cost;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
   // wavefront kernel only
   float *bounce_scratch;          // per resident warp: 7 x S floats (origin, direction, nr_ of reflected rays)
@@ -94,6 +98,10 @@ size_t scan_scratch_words(size_t n);
 // ---- frame kernels (trace.cu) ----
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches);
+unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
+int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
+                      uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
+                      cudaStream_t st, int *result_in_alt);
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
                    cudaStream_t st);
 int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,

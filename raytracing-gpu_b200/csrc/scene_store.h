@@ -34,6 +34,13 @@ struct SceneStore {
   int n_shadow_lights = 0;              // DIRECTIONAL + POINT lights
   unsigned char shadow_light[32] = {0};
 
+  // longest-first scheduling of the frame's work items (api.cu render_async)
+  unsigned char *d_sched = nullptr;     // one block: cost | keys | keys alt | vals | vals alt | sort scratch
+  size_t sched_items = 0;               // capacity, in items
+  const unsigned int *d_item_order = nullptr;   // inside d_sched; nullptr = no order yet
+  int sched_key[5] = {-1, -1, -1, -1, -1};      // rank, nranks, out_w, out_h, aliasing the order is for
+  unsigned long long camera_gen = 0, order_camera_gen = ~0ull, frames_done = 0;
+
   double upload_ms = 0, build_ms = 0, frame_ms = 0;
   unsigned long long build_launches = 0, frame_launches = 0;
   unsigned long long counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};

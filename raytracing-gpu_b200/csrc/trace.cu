@@ -378,6 +378,36 @@ __device__ uint32_t shade_sample(const DevScene &sc, const DevCamera &cam, int p
 constexpr int FRAME_THREADS = 128;
 constexpr int FRAME_WARPS = FRAME_THREADS / 32;
 
+// ---- work items of a frame ----
+// A work item is one warp tile (8x4 output pixels) of a rank tile this rank owns.  Rank tile
+// (Tx,Ty) belongs to rank (Tx + 3*Ty) mod N, so in tile row Ty this rank owns the columns
+// Tx0(Ty) + N*j; rows are padded to J = ceil(nTx / N) slots (a slot past the row end is an
+// empty item).  Only owned tiles are enumerated: one atomic per item, whatever N is.
+#ifndef RTB_RANK_TILE
+#define RTB_RANK_TILE 32      /* rank tile edge in output pixels (multiple of 8) */
+#endif
+constexpr int RANK_TILE = RTB_RANK_TILE;
+constexpr int RT_WX = RANK_TILE / 8, RT_WY = RANK_TILE / 4, RT_ITEMS = RT_WX * RT_WY;   // warp tiles per rank tile
+
+__device__ __forceinline__ unsigned frame_items(const FrameArgs &fa) {
+  const int nTx = (fa.out_w + RANK_TILE - 1) / RANK_TILE, nTy = (fa.out_h + RANK_TILE - 1) / RANK_TILE;
+  const int J = (nTx + fa.nranks - 1) / fa.nranks;
+  return (unsigned)J * (unsigned)nTy * (unsigned)RT_ITEMS;
+}
+__device__ __forceinline__ bool frame_item(const FrameArgs &fa, unsigned item, int &lx0, int &ly0) {
+  const int nTx = (fa.out_w + RANK_TILE - 1) / RANK_TILE;
+  const int N = fa.nranks;
+  const int J = (nTx + N - 1) / N;
+  const int T = (int)(item / RT_ITEMS), sub = (int)(item % RT_ITEMS);
+  const int Ty = T / J, j = T - Ty * J;
+  int tx0 = (fa.rank - 3 * Ty) % N;
+  if (tx0 < 0) tx0 += N;
+  const int Tx = tx0 + N * j;
+  lx0 = Tx * RANK_TILE + (sub % RT_WX) * 8;
+  ly0 = Ty * RANK_TILE + (sub / RT_WX) * 4;
+  return lx0 < fa.out_w && ly0 < fa.out_h;
+}
+
 // Warp tiles: 8x4 output pixels.  32 warp tiles (4 across, 8 down) make one 32x32-pixel
 // rank tile; rank tile (Tx,Ty) belongs to rank (Tx + 3*Ty) mod nranks.
 #ifndef RTB_FRAME_MINBLOCKS
@@ -386,23 +416,23 @@ constexpr int FRAME_WARPS = FRAME_THREADS / 32;
 template <int TRACER, bool COUNT>
 __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
   extern __shared__ uint32_t s_cols[];
+  __shared__ long long s_begin[FRAME_WARPS];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = fa.aliasing;
   const int tw = 8 * a;                          // samples per tile row
   uint32_t *tile = s_cols + (size_t)warp * 32 * a * a;
-  const int nTx = (fa.out_w + 31) / 32, nTy = (fa.out_h + 31) / 32;
-  const unsigned total = (unsigned)nTx * (unsigned)nTy * 32u;
+  const unsigned total = frame_items(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
     unsigned t = 0;
     if (lane == 0) t = atomicAdd(fa.tile_counter, 1u);
     t = __shfl_sync(0xffffffffu, t, 0);
     if (t >= total) break;
-    const int T = (int)(t >> 5), sub = (int)(t & 31u);
-    const int Tx = T % nTx, Ty = T / nTx;
-    if (fa.nranks > 1 && (Tx + 3 * Ty) % fa.nranks != fa.rank) continue;
-    const int lx0 = Tx * 32 + (sub & 3) * 8, ly0 = Ty * 32 + (sub >> 2) * 4;
-    if (lx0 >= fa.out_w || ly0 >= fa.out_h) continue;
+    // items are taken in the order of the previous frame's cost, longest first (api.cu)
+    const unsigned item = fa.item_order ? __ldg(fa.item_order + t) : t;
+    int lx0, ly0;
+    if (!frame_item(fa, item, lx0, ly0)) continue;
+    if (fa.item_cost && lane == 0) s_begin[warp] = clock64();   // kept out of the register file
     for (int q = 0; q < a * a; ++q) {
       const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
       const int px = a * lx0 + sx, py = a * ly0 + sy;
@@ -431,6 +461,10 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       *reinterpret_cast<uint32_t *>(dst) = e;
     }
     __syncwarp();
+    if (fa.item_cost && lane == 0) {
+      const long long dt = (clock64() - s_begin[warp]) >> 6;  // 64-cycle units, 16 bits kept
+      fa.item_cost[item] = (unsigned short)(dt > 65535 ? 65535 : dt);
+    }
   }
   if (COUNT) {
     unsigned v[5] = {c.primary, c.shadow, c.bounce, c.nodes, c.tris};
@@ -534,6 +568,29 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);
   return count ? launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st)
                : launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
+}
+
+// ---- longest-first item order from the costs the previous frame left (api.cu) ----
+__global__ void __launch_bounds__(256) k_item_keys(const unsigned short *cost, unsigned n, uint64_t *keys,
+                                                   uint32_t *vals) {
+  const unsigned i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = 65535u - cost[i];       // ascending sort = descending cost; empty items (cost 0) last
+  vals[i] = i;
+}
+
+unsigned frame_item_count(int out_w, int out_h, int nranks) {
+  const int nTx = (out_w + RANK_TILE - 1) / RANK_TILE, nTy = (out_h + RANK_TILE - 1) / RANK_TILE;
+  return (unsigned)((nTx + nranks - 1) / nranks) * (unsigned)nTy * (unsigned)RT_ITEMS;
+}
+
+int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
+                      uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
+                      cudaStream_t st, int *result_in_alt) {
+  k_item_keys<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_keys, d_vals);
+  RTB_CUDA(cudaGetLastError());
+  return dev_radix_sort_pairs_u64(d_keys, d_vals, d_keys_alt, d_vals_alt, n, 16, d_scratch, scratch_words, st,
+                                  result_in_alt, nullptr);
 }
 
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,

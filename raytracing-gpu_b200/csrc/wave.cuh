@@ -200,19 +200,15 @@ __global__ void __launch_bounds__(WAVE_THREADS, RTB_FRAME_MINBLOCKS) k_frame_wav
     t.a = a;
   }
   const int nl = fa.n_shadow_lights;
-  const int nTx = (fa.out_w + 31) / 32, nTy = (fa.out_h + 31) / 32;
-  const unsigned total = (unsigned)nTx * (unsigned)nTy * 32u;
+  const unsigned total = frame_items(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
     unsigned tile = 0;
     if (lane == 0) tile = atomicAdd(fa.tile_counter, 1u);
     tile = __shfl_sync(0xffffffffu, tile, 0);
     if (tile >= total) break;
-    const int T = (int)(tile >> 5), sub = (int)(tile & 31u);
-    const int Tx = T % nTx, Ty = T / nTx;
-    if (fa.nranks > 1 && (Tx + 3 * Ty) % fa.nranks != fa.rank) continue;
-    const int lx0 = Tx * 32 + (sub & 3) * 8, ly0 = Ty * 32 + (sub >> 2) * 4;
-    if (lx0 >= fa.out_w || ly0 >= fa.out_h) continue;
+    int lx0, ly0;
+    if (!frame_item(fa, tile, lx0, ly0)) continue;
     t.px0 = a * lx0;
     t.py0 = a * ly0;
 

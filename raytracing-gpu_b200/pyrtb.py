@@ -69,7 +69,7 @@ ABI_SYMBOLS = [
     "rtb_scene_render", "rtb_scene_render_device", "rtb_scene_sync", "rtb_scene_hit_ids", "rtb_scene_trace_rays",
     "rtb_scene_stats", "rtb_radix_sort_pairs_u32", "rtb_radix_sort_pairs_u64", "rtb_inclusive_scan_u32",
     "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_scene_dump_tree",
-    "rtb_device_count", "rtb_version", "rtb_scene_root", "rtb_set_margin_k", "rtb_scene_timer_start",
+    "rtb_device_count", "rtb_version", "rtb_scene_root", "rtb_set_margin_k", "rtb_set_schedule", "rtb_scene_timer_start",
     "rtb_scene_timer_stop", "rtb_host_alloc", "rtb_host_free", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_memset",
     "rtb_dev_download", "rtb_scene_mem_alloc", "rtb_scene_mem_free", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close",
     "rtb_parse_svati", "rtb_free_scene", "rtb_write_png", "rtb_cli_main", "rtb_synth_terrain", "rtb_write_svati",
@@ -115,6 +115,8 @@ def lib():
         L.rtb_scene_root.argtypes = [C.c_void_p]
         L.rtb_set_margin_k.argtypes = [C.c_float]
         L.rtb_set_margin_k.restype = None
+        L.rtb_set_schedule.argtypes = [C.c_int]
+        L.rtb_set_schedule.restype = None
         L.rtb_scene_timer_start.argtypes = [C.c_void_p]
         L.rtb_scene_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.rtb_radix_sort_pairs_u32.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]

@@ -271,3 +271,29 @@ def test_set_camera_and_limit(gpu):
         assert e.value.code == pyrtb.RTB_ERR_LIMIT
     finally:
         ds.close()
+
+
+def test_longest_first_schedule_never_changes_the_frame(gpu):
+    """api.cu render_async: frame 2 of a handle records item costs, later frames take the items
+    longest first; a camera change re-records.  Bytes must equal the unscheduled frame."""
+    hs = pyrtb.HostScene.terrain(96, 200, 120)
+    lib = pyrtb.lib()
+    try:
+        lib.rtb_set_schedule(0)
+        ds = pyrtb.DeviceScene(hs, 3)
+        want = ds.render().copy()
+        want_r = [ds.render(rank=r, nranks=3).copy() for r in range(3)]
+        ds.close()
+        lib.rtb_set_schedule(1)
+        ds = pyrtb.DeviceScene(hs, 3)
+        for _ in range(4):
+            assert np.array_equal(ds.render(), want)
+        for r in range(3):
+            for _ in range(3):
+                assert np.array_equal(ds.render(rank=r, nranks=3), want_r[r])
+        ds.set_camera(hs.scaled(3).camera)      # same camera, new generation: re-record path
+        for _ in range(3):
+            assert np.array_equal(ds.render(), want)
+        ds.close()
+    finally:
+        lib.rtb_set_schedule(1)

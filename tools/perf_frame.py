@@ -18,8 +18,10 @@ ap.add_argument("--w", type=int, default=3840)
 ap.add_argument("--h", type=int, default=2160)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--wave", action="store_true")
+ap.add_argument("--nosched", action="store_true")
 ap.add_argument("--scene", default=None, help="golden scene name instead of the terrain (rendered at --w x --h)")
 a = ap.parse_args()
+pyrtb.lib().rtb_set_schedule(0 if a.nosched else 1)
 if a.scene:
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     from util import load_golden
