@@ -130,7 +130,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
-  if (o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
+  if (!RTB_BVH4 && o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
       S.n_lights <= 255) {
     const size_t need = wave_scratch_floats(o.aliasing, S.sm_count);
     if (S.d_bounce_floats < need) {
@@ -466,7 +466,7 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
   memset(out, 0, sizeof *out);
   out->triangles = S.n_tris; out->objects = S.n_objects; out->lights = S.n_lights;
   out->nodes = S.n_nodes; out->leaves = S.n_leaves; out->max_depth = (uint64_t)S.height; out->max_leaf_tris = S.max_leaf;
-  out->tree_bytes = (uint64_t)S.n_nodes * 64;
+  out->tree_bytes = (uint64_t)S.n_nodes * NODE_QUADS * 16;
   out->triangle_bytes = (uint64_t)S.n_tris * 96;
   out->upload_ms = S.upload_ms; out->build_ms = S.build_ms; out->frame_ms = S.frame_ms;
   out->rays_primary = S.counters[0]; out->rays_shadow = S.counters[1]; out->rays_bounce = S.counters[2];
@@ -482,7 +482,7 @@ int rtb_scene_dump_tree(rtb_scene_t *h, void *nodes_out, size_t *n_nodes, uint32
   RTB_CUDA(cudaSetDevice(S.device));
   if (n_nodes) *n_nodes = S.n_nodes;
   if (n_tris) *n_tris = S.n_tris;
-  if (nodes_out) RTB_CUDA(cudaMemcpy(nodes_out, S.nodes, (size_t)S.n_nodes * 64, cudaMemcpyDeviceToHost));
+  if (nodes_out) RTB_CUDA(cudaMemcpy(nodes_out, S.nodes, (size_t)S.n_nodes * NODE_QUADS * 16, cudaMemcpyDeviceToHost));
   if (perm_out && S.n_tris) RTB_CUDA(cudaMemcpy(perm_out, S.order, (size_t)S.n_tris * 4, cudaMemcpyDeviceToHost));
   return RTB_OK;
 }

@@ -291,7 +291,7 @@ __device__ __forceinline__ void sliver_pad(const float *raw_v, uint32_t i, float
 __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
                                              uint32_t n, RawNode *raw, int *visit, int *child_height,
                                              int *root_info /* [0]=raw root, [1]=height */,
-                                             const uint32_t *bounds, float origin_radius) {
+                                             const uint32_t *bounds, float origin_radius, int *raw_parent) {
   const uint32_t i = blockIdx.x * BT + threadIdx.x;
   if (i >= n) return;
   V3 lo, hi;
@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
   int height = 0;     // inner nodes on the longest path below (collapsed subtrees count 0)
   for (;;) {
     const uint32_t cnt = r - l + 1;
-    if (cnt == n) { root_info[0] = cur; root_info[1] = height; return; }
+    if (cnt == n) { root_info[0] = cur; root_info[1] = height; if (cur >= 0) raw_parent[cur] = -1; return; }
     const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
     const int my_h = cnt <= (uint32_t)LEAF_MAX ? 0 : height;
     int parent, side;
@@ -314,6 +314,7 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     else { parent = (int)l - 1; side = 1; }
     store_child(&raw[parent], side, lo, hi, my_ref);
     child_height[2 * parent + side] = my_h;
+    if (cur >= 0) raw_parent[cur] = parent;
     __threadfence();
     const int other = atomicExch(&visit[parent], side == 0 ? (int)l : (int)r);
     if (other < 0) return;                       // first to arrive: the sibling will carry on
@@ -331,6 +332,7 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
   }
 }
 
+#if !RTB_BVH4
 // live[j] = 1 when raw node j survives (its range is larger than a leaf)
 __global__ void __launch_bounds__(BT) k_live(const RawNode *raw, uint32_t n_inner, uint32_t *live) {
   const uint32_t j = blockIdx.x * BT + threadIdx.x;
@@ -378,6 +380,76 @@ __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_i
   dst[3] = make_float4(__int_as_float(nd.ref0), __int_as_float(nd.ref1), __int_as_float(nd.lo), __int_as_float(nd.cnt));
   if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
 }
+#endif
+
+#if RTB_BVH4
+// live[j] = 1 when raw node j survives as a 4-wide node: larger than a leaf and at even depth
+__global__ void __launch_bounds__(BT) k_live4(const RawNode *raw, const int *raw_parent, uint32_t n_inner,
+                                              uint32_t *live, unsigned char *keep) {
+  const uint32_t j = blockIdx.x * BT + threadIdx.x;
+  if (j >= n_inner) return;
+  unsigned char k = 0;
+  if (raw[j].cnt > LEAF_MAX) {
+    int depth = 0;
+    for (int p = raw_parent[j]; p >= 0; p = raw_parent[p]) ++depth;
+    k = (depth & 1) ? 0 : 1;
+  }
+  keep[j] = k;
+  live[j] = k;
+}
+
+__device__ __forceinline__ void put_child4(float4 *dst, int slot, V3 lo, V3 hi, int ref) {
+  float *f = reinterpret_cast<float *>(dst);
+  float *xy = f + 4 * slot;
+  xy[0] = lo.x; xy[1] = hi.x; xy[2] = lo.y; xy[3] = hi.y;
+  f[16 + 2 * slot] = lo.z;
+  f[17 + 2 * slot] = hi.z;
+  f[24 + slot] = __int_as_float(ref);
+}
+
+__device__ __forceinline__ void raw_child(const RawNode &nd, int side, V3 &lo, V3 &hi, int &ref) {
+  const float *f = reinterpret_cast<const float *>(&nd);
+  const float *xy = f + 4 * side;
+  lo = mk(xy[0], xy[2], f[8 + 2 * side]);
+  hi = mk(xy[1], xy[3], f[9 + 2 * side]);
+  ref = (&nd.ref0)[side];
+}
+
+// new_index = exclusive scan of live.  One thread per kept raw node: its grandchildren (or a
+// child that is a leaf) become the four children.  stats: [0] leaves, [1] max leaf size
+__global__ void __launch_bounds__(BT) k_compact4(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
+                                                 const unsigned char *keep, float4 *nodes, unsigned int *stats) {
+  const uint32_t j = blockIdx.x * BT + threadIdx.x;
+  if (j >= n_inner || !keep[j]) return;
+  const RawNode nd = raw[j];
+  const float INF = __int_as_float(0x7f800000);
+  float4 *dst = nodes + (size_t)NODE_QUADS * new_index[j];
+  unsigned leaves = 0, maxleaf = 0;
+  for (int side = 0; side < 2; ++side) {
+    V3 lo, hi;
+    int ref;
+    raw_child(nd, side, lo, hi, ref);
+    int slot = 2 * side;
+    if (ref < 0) {
+      put_child4(dst, slot++, lo, hi, ref);
+      ++leaves; maxleaf = max(maxleaf, (unsigned)(~ref & 7));
+    } else {
+      const RawNode c = raw[ref];
+      for (int s2 = 0; s2 < 2; ++s2) {
+        int r2;
+        raw_child(c, s2, lo, hi, r2);
+        if (r2 >= 0) r2 = (int)new_index[r2];
+        else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~r2 & 7)); }
+        put_child4(dst, slot++, lo, hi, r2);
+      }
+    }
+    for (; slot < 2 * side + 2; ++slot)
+      put_child4(dst, slot, mk(INF, INF, INF), mk(-INF, -INF, -INF), leaf_ref(0, 0));
+  }
+  dst[7] = make_float4(__int_as_float(nd.lo), __int_as_float(nd.cnt), 0.0f, 0.0f);
+  if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
+}
+#endif
 
 // Scenes of at most LEAF_MAX triangles (and brute-force-only scenes): one node whose first
 // child is a leaf over everything with an unbounded box (nothing to cull, so nothing to pad),
@@ -386,6 +458,12 @@ __global__ void k_single_node(uint32_t n, float4 *nodes) {
   const float INF = __int_as_float(0x7f800000);
   float lx = INF, ly = INF, lz = INF, hx = -INF, hy = -INF, hz = -INF;
   if (n) { lx = ly = lz = -INF; hx = hy = hz = INF; }
+#if RTB_BVH4
+  put_child4(nodes, 0, mk(lx, ly, lz), mk(hx, hy, hz), leaf_ref(0, n));
+  for (int k = 1; k < 4; ++k) put_child4(nodes, k, mk(INF, INF, INF), mk(-INF, -INF, -INF), leaf_ref(0, 0));
+  nodes[7] = make_float4(__int_as_float(0), __int_as_float((int)n), 0.0f, 0.0f);
+  return;
+#endif
 #if RTB_NODE_CH
   nodes[0] = to_centre_half(make_float4(lx, hx, ly, hy));
   nodes[1] = to_centre_half(make_float4(INF, -INF, INF, -INF));
@@ -600,12 +678,21 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     CK(tmp.alloc(&raw, n_inner)); CK(tmp.alloc(&visit, n_inner)); CK(tmp.alloc(&child_h, 2ull * n_inner));
     CK(tmp.alloc(&root_info, 2)); CK(tmp.alloc(&live, n_inner + 1)); CK(tmp.alloc(&scan_scratch, ssw));
     CK(tmp.alloc(&d_stats, 2));
+    int *raw_parent = nullptr;
+    CK(tmp.alloc(&raw_parent, n_inner));
     RTB_CUDA(cudaMemsetAsync(visit, 0xff, 4ull * n_inner, st));
     RTB_CUDA(cudaMemsetAsync(raw, 0, sizeof(RawNode) * (size_t)n_inner, st));
     RTB_CUDA(cudaMemsetAsync(d_stats, 0, 8, st));
     RTB_CUDA(cudaMemsetAsync(live, 0, 4ull * (n_inner + 1), st));
-    k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info, d_bounds, S->origin_radius);
+    k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info, d_bounds, S->origin_radius,
+                              raw_parent);
+#if RTB_BVH4
+    unsigned char *keep = nullptr;
+    CK(tmp.alloc(&keep, n_inner));
+    k_live4<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, raw_parent, n_inner, live, keep);
+#else
     k_live<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live);
+#endif
     launches += 2;
     CK(dev_exclusive_scan_u32(live, n_inner + 1, scan_scratch, ssw, false, st, &launches));
     uint32_t n_live = 0;
@@ -614,9 +701,13 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     RTB_CUDA(cudaMemcpyAsync(h_root, root_info, 8, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
     if (n_live == 0 || h_root[0] < 0) { set_error("hierarchy build produced no root"); return RTB_ERR_CUDA; }
-    if (h_root[1] > STACK_MAX) { set_error("hierarchy depth %d exceeds %d", h_root[1], STACK_MAX); return RTB_ERR_LIMIT; }
-    CK(dev_alloc(&S->nodes, 4ull * n_live));
+    if (h_root[1] > HEIGHT_MAX) { set_error("hierarchy depth %d exceeds %d", h_root[1], HEIGHT_MAX); return RTB_ERR_LIMIT; }
+    CK(dev_alloc(&S->nodes, (size_t)NODE_QUADS * n_live));
+#if RTB_BVH4
+    k_compact4<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, keep, S->nodes, d_stats);
+#else
     k_compact<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, S->nodes, d_stats);
+#endif
     ++launches;
     uint32_t new_root = 0;
     unsigned int h_stats[2] = {0, 0};
@@ -626,7 +717,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     S->n_nodes = n_live; S->root = (int)new_root; S->height = h_root[1];
     S->n_leaves = h_stats[0]; S->max_leaf = h_stats[1];
   } else {
-    CK(dev_alloc(&S->nodes, 4));
+    CK(dev_alloc(&S->nodes, NODE_QUADS));
     k_single_node<<<1, 1, 0, st>>>(n, S->nodes);
     ++launches;
   }

@@ -160,58 +160,66 @@ __device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, f
 }
 #endif
 
-#ifndef RTB_LOOP_SHAPE
-#define RTB_LOOP_SHAPE 2
-#endif
 constexpr int TRAVERSAL_DONE = (int)0x80000000;   // stack sentinel: not a valid leaf reference
 
-// "while-while" traversal: every lane first descends inner nodes until it holds a leaf
-// (or has nothing left), then the warp tests triangles together.  Keeping the two phases
-// apart keeps the lanes of a warp in the same code at the same time; with a single
-// if-inner-else-leaf loop the triangle code ran at 7.5 of 32 lanes (profiles/r1_v1).
-// Default shape 2 adds Aila-Laine style speculation: a lane that reaches its first leaf
-// keeps it aside and goes on descending until every lane of the warp holds one
-// (C5: 46.8 -> 44.5 ms).  Shapes 0 (plain while-while) and 1 (if-if) remain for A/B builds.
+#if RTB_BVH4
+// 4-wide nodes (rtb_internal.h): one visit tests the four grandchildren of the binary node, so
+// a ray makes about half as many visits, dependent loads and loop/stack/vote steps as on the
+// binary tree for the same box tests.  Same speculative while-while shape as below.
 template <bool ANY, bool COUNT>
 __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
   best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
   const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
   const float eps = sc.margin_k * 1.1920929e-7f * amax;
   const Slabs sl = make_slabs(o, d, eps);
-  // distance -> ray parameter, rounded up
-  const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
+  const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);   // distance -> ray parameter, rounded up
   float tmax = INF;
   int stack[STACK_MAX + 1];
   stack[0] = TRAVERSAL_DONE;
   int sp = 1;
   int cur = sc.root;
-#if RTB_LOOP_SHAPE == 2   /* while-while with one postponed leaf (speculative traversal) */
   int pending = 0;        // leaf references are negative, 0 = none held
   for (;;) {
     while (cur >= 0) {
       if (COUNT) ++c.nodes;
-      const float4 *np = sc.nodes + 4ll * cur;
-      const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
-      float tn0, tn1;
-      const bool h0 = slab_hit<!ANY>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
-      const bool h1 = slab_hit<!ANY>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
-      const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
-      if (h0 && h1) {
-        // shadow rays only ask "anything?": no near-first ordering (42.7 vs 43.9 ms on C5)
-#ifdef RTB_ANY_ORDERED
-        const bool far0 = tn1 < tn0;
-#else
-        const bool far0 = ANY ? false : tn1 < tn0;
-#endif
-        cur = far0 ? r1 : r0;
-        stack[sp++] = far0 ? r0 : r1;
-      } else if (h0) cur = r0;
-      else if (h1) cur = r1;
-      else cur = stack[--sp];
-      if (cur < 0 && cur != TRAVERSAL_DONE && pending == 0) {   // first leaf: keep it, go on
-        pending = cur;
-        cur = stack[--sp];
+      const float4 *np = sc.nodes + 8ll * cur;
+      const float4 b0 = __ldg(np), b1 = __ldg(np + 1), b2 = __ldg(np + 2), b3 = __ldg(np + 3);
+      const float4 z01 = __ldg(np + 4), z23 = __ldg(np + 5), rf = __ldg(np + 6);
+      float t0, t1, t2, t3;
+      const bool h0 = slab_hit<!ANY>(sl, b0.x, b0.y, b0.z, b0.w, z01.x, z01.y, tmax, t0);
+      const bool h1 = slab_hit<!ANY>(sl, b1.x, b1.y, b1.z, b1.w, z01.z, z01.w, tmax, t1);
+      const bool h2 = slab_hit<!ANY>(sl, b2.x, b2.y, b2.z, b2.w, z23.x, z23.y, tmax, t2);
+      const bool h3 = slab_hit<!ANY>(sl, b3.x, b3.y, b3.z, b3.w, z23.z, z23.w, tmax, t3);
+      const int r0 = __float_as_int(rf.x), r1 = __float_as_int(rf.y), r2 = __float_as_int(rf.z),
+                r3 = __float_as_int(rf.w);
+      // cur = one hit child, the others go on the stack
+      constexpr int NONE = 0x7fffffff;     // neither a node index (< 2^28) nor a leaf (negative)
+      int next = NONE;
+      if (ANY) {
+        // shadow rays only ask "anything?": storage order
+        if (h3) next = r3;
+        if (h2) { if (next != NONE) stack[sp++] = next; next = r2; }
+        if (h1) { if (next != NONE) stack[sp++] = next; next = r1; }
+        if (h0) { if (next != NONE) stack[sp++] = next; next = r0; }
+      } else {
+        // nearest entry point first; the rest in storage order.  Entry distances are >= 0, so
+        // their bit patterns order like unsigned integers; the low 2 bits carry the child index.
+        const unsigned k0 = h0 ? (__float_as_uint(t0) & ~3u) : 0xffffffffu;
+        const unsigned k1 = h1 ? (__float_as_uint(t1) & ~3u) | 1u : 0xffffffffu;
+        const unsigned k2 = h2 ? (__float_as_uint(t2) & ~3u) | 2u : 0xffffffffu;
+        const unsigned k3 = h3 ? (__float_as_uint(t3) & ~3u) | 3u : 0xffffffffu;
+        const unsigned m = min(min(k0, k1), min(k2, k3));
+        if (h3 && k3 != m) stack[sp++] = r3;
+        if (h2 && k2 != m) stack[sp++] = r2;
+        if (h1 && k1 != m) stack[sp++] = r1;
+        if (h0 && k0 != m) stack[sp++] = r0;
+        if (m != 0xffffffffu) next = (m & 2u) ? ((m & 1u) ? r3 : r2) : ((m & 1u) ? r1 : r0);
       }
+      if (next < 0 && pending == 0) {      // first leaf: keep it, go on
+        pending = next;
+        next = NONE;
+      }
+      cur = next != NONE ? next : stack[--sp];
       if (!__any_sync(__activemask(), pending == 0)) break;     // every lane here holds a leaf
     }
     while (pending != 0 || (cur < 0 && cur != TRAVERSAL_DONE)) {
@@ -231,46 +239,71 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
     if (cur == TRAVERSAL_DONE) break;
   }
   return best.slot >= 0;
+}
 #else
+// Speculative "while-while" traversal (Aila-Laine): every lane descends inner nodes; the first
+// leaf it reaches is set aside and the descent goes on until every lane of the warp holds one,
+// then the warp tests triangles together.  Keeping the two phases apart keeps the lanes of a
+// warp in the same code at the same time; with a single if-inner-else-leaf loop the triangle
+// code ran at 7.5 of 32 lanes (profiles/r1_ncu_frame_v1.txt).  History on C5: if-else 53.9 ms,
+// plain while-while 47.4, speculative 44.5, one pop per step 40.5.
+template <bool ANY, bool COUNT>
+__device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
+  best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
+  const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
+  const float eps = sc.margin_k * 1.1920929e-7f * amax;
+  const Slabs sl = make_slabs(o, d, eps);
+  // distance -> ray parameter, rounded up
+  const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
+  float tmax = INF;
+  int stack[STACK_MAX + 1];
+  stack[0] = TRAVERSAL_DONE;
+  int sp = 1;
+  int cur = sc.root;
+  int pending = 0;                       // leaf references are negative, 0 = none held
+  constexpr int NONE = 0x7fffffff;       // neither a node index nor a leaf
   for (;;) {
-#if RTB_LOOP_SHAPE == 1   /* if-if: one node OR one leaf per trip */
-    if (cur >= 0) {
-#else                     /* while-while */
     while (cur >= 0) {
-#endif
       if (COUNT) ++c.nodes;
       const float4 *np = sc.nodes + 4ll * cur;
       const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
       float tn0, tn1;
-      const bool h0 = slab_hit(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
-      const bool h1 = slab_hit(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
+      const bool h0 = slab_hit<!ANY>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
+      const bool h1 = slab_hit<!ANY>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
       const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
+      int next = h0 ? r0 : (h1 ? r1 : NONE);
       if (h0 && h1) {
-        const bool far0 = tn1 < tn0;
-        cur = far0 ? r1 : r0;
+        // shadow rays only ask "anything?": storage order, no near-first compare
+        const bool far0 = ANY ? false : tn1 < tn0;
+        next = far0 ? r1 : r0;
         stack[sp++] = far0 ? r0 : r1;
-      } else if (h0) cur = r0;
-      else if (h1) cur = r1;
-      else cur = stack[--sp];
-#if RTB_LOOP_SHAPE == 1
-      continue;
-#endif
+      }
+      if (next < 0 && pending == 0) {      // first leaf: keep it, go on
+        pending = next;
+        next = NONE;
+      }
+      cur = next != NONE ? next : stack[--sp];                  // the only pop of a step
+      if (!__any_sync(__activemask(), pending == 0)) break;     // every lane here holds a leaf
     }
-    if (cur == TRAVERSAL_DONE) break;
-    const uint32_t packed = (uint32_t)~cur;
-    const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
-    for (int k = 0; k < cnt; ++k) {
-      if (COUNT) ++c.tris;
-      if (consider<ANY>(sc, o, d, first + k, best)) {
-        if (ANY) return true;
-        tmax = (best.dist * 1.0001f + eps) * inv_len;
+    while (pending != 0 || (cur < 0 && cur != TRAVERSAL_DONE)) {
+      int leaf;
+      if (pending != 0) { leaf = pending; pending = 0; }
+      else { leaf = cur; cur = stack[--sp]; }
+      const uint32_t packed = (uint32_t)~leaf;
+      const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
+      for (int k = 0; k < cnt; ++k) {
+        if (COUNT) ++c.tris;
+        if (consider<ANY>(sc, o, d, first + k, best)) {
+          if (ANY) return true;
+          tmax = (best.dist * 1.0001f + eps) * inv_len;
+        }
       }
     }
-    cur = stack[--sp];
+    if (cur == TRAVERSAL_DONE) break;
   }
   return best.slot >= 0;
-#endif
 }
+#endif   // RTB_BVH4
 
 template <int TRACER, bool ANY, bool COUNT>
 __device__ __forceinline__ bool trace(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
@@ -304,28 +337,24 @@ __device__ uint32_t apply_light(const DevScene &sc, int obj, const V3 P, const V
     const V3 lv = mk(l1);
     if (type == AMBIENT) {
       color = color_add(color, color_mults(lcol, ka));
-    } else if (type == DIRECTIONAL) {
+    } else if (type == DIRECTIONAL || type == POINT) {
+      // one shadow-ray call site for both light kinds: the traversal is inlined once, not twice
       const V3 L = vscale(lv, -1);
-      Best b;
-      if (COUNT) ++c.shadow;
-      if (!trace<TRACER, true, COUNT>(sc, P, L, b, c)) {
-        uint32_t t = color_mults(lcol, kd);
-        t = color_mul(t, vdot(L, Nrm));
-        t = apply_specular(t, vadd(P, vscale(lv, -10)), lv, P, Nrm, ks, ns);
-        color = color_add(color, t);
-      }
-    } else if (type == POINT) {
-      const V3 L = vscale(lv, -1);
-      V3 N = Nrm;
-      if (vdot(L, N) < 0) N = vscale(N, -1);
-      const V3 dir = vsub(lv, P);
-      const float dist = vlen(vsub(lv, P));
+      const V3 dir = type == DIRECTIONAL ? L : vsub(lv, P);
       Best b;
       if (COUNT) ++c.shadow;
       if (!trace<TRACER, true, COUNT>(sc, P, dir, b, c)) {
         uint32_t t = color_mults(lcol, kd);
-        t = color_mul(t, vdot(L, N) * 1 / dist);
-        t = apply_specular(t, vadd(P, vscale(dir, -10)), dir, P, Nrm, ks, ns);
+        if (type == DIRECTIONAL) {
+          t = color_mul(t, vdot(L, Nrm));
+          t = apply_specular(t, vadd(P, vscale(lv, -10)), lv, P, Nrm, ks, ns);
+        } else {
+          V3 N = Nrm;
+          if (vdot(L, N) < 0) N = vscale(N, -1);
+          const float dist = vlen(vsub(lv, P));
+          t = color_mul(t, vdot(L, N) * 1 / dist);
+          t = apply_specular(t, vadd(P, vscale(dir, -10)), dir, P, Nrm, ks, ns);
+        }
         color = color_add(color, t);
       }
     }
@@ -511,7 +540,9 @@ __global__ void __launch_bounds__(128) k_trace_rays(const DevScene sc, const flo
   if (dist) dist[i] = (hit && !ANY) ? b.dist : 0.0f;
 }
 
-#include "wave.cuh"
+#if !RTB_BVH4
+#include "wave.cuh"   // staged wavefront kernel: binary node layout only (A/B builds)
+#endif
 
 float g_margin_k = 24.0f;
 
@@ -533,6 +564,9 @@ static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count,
   return RTB_OK;
 }
 
+#if RTB_BVH4
+size_t wave_scratch_floats(int, int) { return 0; }
+#else
 constexpr int WAVE_MAX_BLOCKS_PER_SM = 16;
 
 size_t wave_scratch_floats(int aliasing, int sm_count) {
@@ -553,6 +587,8 @@ static int launch_wave_t(const DevScene &sc, const FrameArgs &fa, int sm_count, 
   return RTB_OK;
 }
 
+#endif
+
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches) {
   if (fa.aliasing < 1 || fa.aliasing > 16) { set_error("aliasing must be in 1..16"); return RTB_ERR_ARG; }
@@ -561,8 +597,10 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
   if (launches) *launches = 1;
   // RTB_KERNEL_WAVEFRONT was requested and is applicable (api.cu sets bounce_scratch only then);
   // everything else runs the persistent-warp per-sample kernel, the faster of the two
+#if !RTB_BVH4
   if (tracer == RTB_TRACER_TREE && fa.bounce_scratch && fa.n_shadow_lights <= 32 && fa.aliasing <= WAVE_MAX_ALIASING)
     return count ? launch_wave_t<true>(sc, fa, sm_count, st) : launch_wave_t<false>(sc, fa, sm_count, st);
+#endif
   if (tracer == RTB_TRACER_BRUTE)
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);

@@ -387,7 +387,9 @@ class DeviceScene:
     def dump_tree(self):
         nn, nt = C.c_size_t(), C.c_size_t()
         _check(lib().rtb_scene_dump_tree(self.h, None, C.byref(nn), None, C.byref(nt)))
-        nodes = np.empty((nn.value, 16), np.float32)
+        st = self.stats()
+        floats = int(st["tree_bytes"] // max(1, st["nodes"])) // 4      # 32 per 4-wide node (16: binary A/B build)
+        nodes = np.empty((nn.value, floats), np.float32)
         perm = np.empty(nt.value, np.uint32)
         _check(lib().rtb_scene_dump_tree(self.h, nodes.ctypes.data, C.byref(nn), perm.ctypes.data, C.byref(nt)))
         return nodes, perm, lib().rtb_scene_root(self.h)

@@ -179,9 +179,13 @@ def test_build_is_deterministic_and_structurally_sound(gpu):
         assert ra == rb and np.array_equal(pa, pb) and np.array_equal(na.view(np.uint32), nb.view(np.uint32))
         T = hs.triangle_count
         assert sorted(pa.tolist()) == list(range(T)), "leaf order is a permutation of the triangles"
-        refs = na[:, 12:14].copy().view(np.int32)
-        rng_lo = na[:, 14].copy().view(np.int32)
-        rng_cnt = na[:, 15].copy().view(np.int32)
+        # 64-byte binary nodes (product) or 128-byte 4-wide nodes (RTB_BVH4 A/B build): rtb_internal.h
+        wide = na.shape[1] == 32
+        fan = 4 if wide else 2
+        refs = (na[:, 24:28] if wide else na[:, 12:14]).copy().view(np.int32)
+        rng_lo = na[:, 28 if wide else 14].copy().view(np.int32)
+        rng_cnt = na[:, 29 if wide else 15].copy().view(np.int32)
+        zoff = 16 if wide else 8
         seen = np.zeros(T, np.int32)
         verts = hs.arrays()["vertex"][pa]        # leaf order
         stack = [ra]
@@ -191,23 +195,27 @@ def test_build_is_deterministic_and_structurally_sound(gpu):
             k = stack.pop()
             visited += 1
             lo, cnt = int(rng_lo[k]), int(rng_cnt[k])
-            for side in (0, 1):
-                ref = int(refs[k, side])
-                if side == 0:
-                    box = (na[k, 0], na[k, 1], na[k, 2], na[k, 3], na[k, 8], na[k, 9])
-                else:
-                    box = (na[k, 4], na[k, 5], na[k, 6], na[k, 7], na[k, 10], na[k, 11])
+            covered = 0
+            for slot in range(fan):
+                ref = int(refs[k, slot])
+                # (min.x, max.x, min.y, max.y) per child first, then the (min.z, max.z) pairs
+                box = (na[k, 4 * slot], na[k, 4 * slot + 1], na[k, 4 * slot + 2], na[k, 4 * slot + 3],
+                       na[k, zoff + 2 * slot], na[k, zoff + 2 * slot + 1])
                 if ref >= 0:
                     stack.append(ref)
                     f, c = int(rng_lo[ref]), int(rng_cnt[ref])
                 else:
                     packed = ~ref
                     f, c = packed >> 3, packed & 7
-                    assert 1 <= c <= 4
+                    if c == 0:                  # unused slot: inverted box
+                        assert box[0] > box[1]
+                        continue
+                    assert 1 <= c <= 3
                     seen[f:f + c] += 1
                 assert lo <= f and f + c <= lo + cnt
+                covered += c
                 pts = verts[f:f + c].reshape(-1, 3)
-                # boxes contain their triangles; they are tight except for the sliver padding
+                # boxes contain their triangles; they are tight except for the needle padding
                 # (build.cu), which never exceeds the triangle's longest edge
                 slack = 1.5     # terrain edges are < 1.5 units at this grid
                 for ax in range(3):
@@ -215,11 +223,12 @@ def test_build_is_deterministic_and_structurally_sound(gpu):
                     assert box[2 * ax + 1] - slack <= pts[:, ax].max() <= box[2 * ax + 1]
                     tight += int(box[2 * ax] == pts[:, ax].min()) + int(box[2 * ax + 1] == pts[:, ax].max())
                     planes += 2
+            assert covered == cnt, "the children partition the node's slot range"
         assert (seen == 1).all(), "every triangle is in exactly one leaf"
         assert visited == len(na)
         assert tight > 0.5 * planes, "most boxes are exact min/max of their vertices"
         st = a.stats()
-        assert st["nodes"] == len(na) and st["max_leaf_tris"] <= 4
+        assert st["nodes"] == len(na) and st["max_leaf_tris"] <= 3
     finally:
         a.close()
         b.close()
