@@ -91,7 +91,7 @@ struct FrameArgs {
   long long pitch;
   unsigned int *tile_counter;
   // work-item scheduling (trace.cu frame_item): order to take the items in (nullptr = 0,1,2,..)
-  // and where to leave each item's cost, in 64-cycle units (nullptr = not recorded)
+  // and where to leave each item's cost, in 256-cycle units (nullptr = not recorded)
   const unsigned int *item_order;
   unsigned short *item_cost;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests

@@ -444,12 +444,14 @@ __device__ __forceinline__ bool frame_item(const FrameArgs &fa, unsigned item, i
 #endif
 template <int TRACER, bool COUNT>
 __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
-  extern __shared__ uint32_t s_cols[];
-  __shared__ long long s_begin[FRAME_WARPS];
+  // Per output pixel of the warp tile: the channel sums of its a x a samples (x: r | g << 16,
+  // y: b).  The reference sums the u8 channels as floats (gpu/raytracer.cu:62-70); sums of at
+  // most 256 values below 256 are exact in either arithmetic, so integers give the same bits.
+  // 1 KB per CTA whatever the aliasing, which leaves the unified L1 its largest share.
+  __shared__ uint2 s_acc[FRAME_WARPS][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = fa.aliasing;
-  const int tw = 8 * a;                          // samples per tile row
-  uint32_t *tile = s_cols + (size_t)warp * 32 * a * a;
+  uint2 *acc = s_acc[warp];
   const unsigned total = frame_items(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
@@ -461,26 +463,26 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
     const unsigned item = fa.item_order ? __ldg(fa.item_order + t) : t;
     int lx0, ly0;
     if (!frame_item(fa, item, lx0, ly0)) continue;
-    if (fa.item_cost && lane == 0) s_begin[warp] = clock64();   // kept out of the register file
+    // start time parked in the cost slot itself (256-cycle units, 16 bits): no register, no shared memory
+    if (fa.item_cost && lane == 0) fa.item_cost[item] = (unsigned short)(clock64() >> 8);
+    acc[lane] = make_uint2(0u, 0u);
+    __syncwarp();
     for (int q = 0; q < a * a; ++q) {
       const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
       const int px = a * lx0 + sx, py = a * ly0 + sy;
-      uint32_t col = 0;
-      if (px < fa.cam.W && py < fa.cam.H) col = shade_sample<TRACER, COUNT>(sc, fa.cam, px, py, c);
-      tile[sy * tw + sx] = col;
+      if (px < fa.cam.W && py < fa.cam.H) {
+        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa.cam, px, py, c);
+        uint2 *dst = acc + (sy / a) * 8 + sx / a;
+        atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
+        atomicAdd(&dst->y, ch_b(col));
+      }
     }
     __syncwarp();
     // downscale kernel body (gpu/raytracer.cu:49-85) for this lane's output pixel
     const int lx = lx0 + (lane & 7), ly = ly0 + (lane >> 3);
     if (lx < fa.out_w && ly < fa.out_h) {
-      float r = 0, g = 0, b = 0;
-      for (int j = 0; j < a; ++j)
-        for (int i = 0; i < a; ++i) {
-          const uint32_t col = tile[(a * (lane >> 3) + j) * tw + a * (lane & 7) + i];
-          r += (float)ch_r(col);
-          g += (float)ch_g(col);
-          b += (float)ch_b(col);
-        }
+      const uint2 sum = acc[lane];
+      float r = (float)(sum.x & 0xffffu), g = (float)(sum.x >> 16), b = (float)sum.y;
       const float ali2 = 255.0f * (float)a * (float)a;
       r /= ali2;
       g /= ali2;
@@ -490,10 +492,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       *reinterpret_cast<uint32_t *>(dst) = e;
     }
     __syncwarp();
-    if (fa.item_cost && lane == 0) {
-      const long long dt = (clock64() - s_begin[warp]) >> 6;  // 64-cycle units, 16 bits kept
-      fa.item_cost[item] = (unsigned short)(dt > 65535 ? 65535 : dt);
-    }
+    if (fa.item_cost && lane == 0)
+      fa.item_cost[item] = (unsigned short)((unsigned short)(clock64() >> 8) - fa.item_cost[item]);   // modulo 2^16
   }
   if (COUNT) {
     unsigned v[5] = {c.primary, c.shadow, c.bounce, c.nodes, c.tris};
@@ -553,9 +553,11 @@ float get_margin_k() { return g_margin_k; }
 
 template <int TRACER, bool COUNT>
 static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
-  const size_t smem = (size_t)FRAME_WARPS * 32 * fa.aliasing * fa.aliasing * sizeof(uint32_t);
+  const size_t smem = 0;
   auto kern = k_frame<TRACER, COUNT>;
-  if (smem > 48 * 1024) RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+#ifdef RTB_CARVEOUT   /* A/B only: shared-memory share of the unified L1, percent */
+  RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, RTB_CARVEOUT));
+#endif
   int per_sm = 0;
   RTB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FRAME_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
@@ -609,11 +611,18 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
 }
 
 // ---- longest-first item order from the costs the previous frame left (api.cu) ----
+// Keys are coarse cost classes (half octaves), not the costs themselves: the radix sort is
+// stable, so items of one class keep their spatial order and neighbouring warps keep working
+// on neighbouring tiles (a full sort by cost quadrupled the DRAM traffic of the frame).
+#ifndef RTB_COST_CLASSES_PER_OCTAVE
+#define RTB_COST_CLASSES_PER_OCTAVE 2
+#endif
 __global__ void __launch_bounds__(256) k_item_keys(const unsigned short *cost, unsigned n, uint64_t *keys,
                                                    uint32_t *vals) {
   const unsigned i = blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
-  keys[i] = 65535u - cost[i];       // ascending sort = descending cost; empty items (cost 0) last
+  const int cls = (int)((float)RTB_COST_CLASSES_PER_OCTAVE * log2f((float)cost[i] + 1.0f));   // 0 .. 16 * classes
+  keys[i] = (uint64_t)(255 - min(cls, 255));   // ascending sort = heaviest class first; empty items (cost 0) last
   vals[i] = i;
 }
 
@@ -627,7 +636,7 @@ int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys
                       cudaStream_t st, int *result_in_alt) {
   k_item_keys<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_keys, d_vals);
   RTB_CUDA(cudaGetLastError());
-  return dev_radix_sort_pairs_u64(d_keys, d_vals, d_keys_alt, d_vals_alt, n, 16, d_scratch, scratch_words, st,
+  return dev_radix_sort_pairs_u64(d_keys, d_vals, d_keys_alt, d_vals_alt, n, 8, d_scratch, scratch_words, st,
                                   result_in_alt, nullptr);
 }
 
