@@ -126,6 +126,9 @@ __device__ __forceinline__ uint32_t object_of(const uint32_t *obj_first, uint32_
   return lo;
 }
 
+// POS: positions (v0|id, e1|obj, e2), NRM: unit normals.  Two launches for big scenes, where
+// the normals are still on their way over PCIe while the hierarchy is built (build_scene).
+template <bool POS, bool NRM>
 __global__ void __launch_bounds__(BT) k_permute(const float *raw_v, const float *raw_n, const uint32_t *order,
                                                 uint32_t n, const uint32_t *obj_first, uint32_t n_obj,
                                                 float4 *v0, float4 *e1, float4 *e2, float4 *n0, float4 *n1,
@@ -133,17 +136,21 @@ __global__ void __launch_bounds__(BT) k_permute(const float *raw_v, const float 
   const uint32_t s = blockIdx.x * BT + threadIdx.x;
   if (s >= n) return;
   const uint32_t i = order[s];
-  const float *p = raw_v + 9ull * i;
-  const V3 a = mk(p[0], p[1], p[2]), b = mk(p[3], p[4], p[5]), c = mk(p[6], p[7], p[8]);
-  const V3 ab = vsub(b, a), ac = vsub(c, a);   // edge1/edge2 of gpu/hit.cu:20-21, same subtraction
-  v0[s] = make_float4(a.x, a.y, a.z, __uint_as_float(i));
-  e1[s] = make_float4(ab.x, ab.y, ab.z, __uint_as_float(object_of(obj_first, n_obj, i)));
-  e2[s] = make_float4(ac.x, ac.y, ac.z, 0.0f);
-  const float *q = raw_n + 9ull * i;
-  const V3 na = vnorm(mk(q[0], q[1], q[2])), nb = vnorm(mk(q[3], q[4], q[5])), nc = vnorm(mk(q[6], q[7], q[8]));
-  n0[s] = make_float4(na.x, na.y, na.z, 0.0f);
-  n1[s] = make_float4(nb.x, nb.y, nb.z, 0.0f);
-  n2[s] = make_float4(nc.x, nc.y, nc.z, 0.0f);
+  if (POS) {
+    const float *p = raw_v + 9ull * i;
+    const V3 a = mk(p[0], p[1], p[2]), b = mk(p[3], p[4], p[5]), c = mk(p[6], p[7], p[8]);
+    const V3 ab = vsub(b, a), ac = vsub(c, a);   // edge1/edge2 of gpu/hit.cu:20-21, same subtraction
+    v0[s] = make_float4(a.x, a.y, a.z, __uint_as_float(i));
+    e1[s] = make_float4(ab.x, ab.y, ab.z, __uint_as_float(object_of(obj_first, n_obj, i)));
+    e2[s] = make_float4(ac.x, ac.y, ac.z, 0.0f);
+  }
+  if (NRM) {
+    const float *q = raw_n + 9ull * i;
+    const V3 na = vnorm(mk(q[0], q[1], q[2])), nb = vnorm(mk(q[3], q[4], q[5])), nc = vnorm(mk(q[6], q[7], q[8]));
+    n0[s] = make_float4(na.x, na.y, na.z, 0.0f);
+    n1[s] = make_float4(nb.x, nb.y, nb.z, 0.0f);
+    n2[s] = make_float4(nc.x, nc.y, nc.z, 0.0f);
+  }
 }
 
 // "How different are sorted neighbours j and j+1": position of the highest differing key
@@ -576,6 +583,26 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   struct EvGuard { cudaEvent_t e; ~EvGuard() { cudaEventDestroy(e); } } evg{e_b1};
 
   // ---- upload (to_cuda, gpu/scene.cu:224-352): raw float3 arrays, object table, lights ----
+  // Big scenes: only the vertex arrays go up on the build stream; the normals (needed by the
+  // last kernel of the build alone) follow on a second stream and cross PCIe while the
+  // hierarchy is being built.
+  const bool overlap = n >= (1u << 20);
+  struct Side {
+    cudaStream_t st = nullptr;
+    cudaEvent_t verts = nullptr, normals = nullptr;
+    ~Side() {
+      if (st) { cudaStreamSynchronize(st); cudaStreamDestroy(st); }
+      if (verts) cudaEventDestroy(verts);
+      if (normals) cudaEventDestroy(normals);
+    }
+  } side;
+  if (overlap) {
+    RTB_CUDA(cudaStreamCreateWithFlags(&side.st, cudaStreamNonBlocking));
+    RTB_CUDA(cudaEventCreateWithFlags(&side.verts, cudaEventDisableTiming));
+    RTB_CUDA(cudaEventCreateWithFlags(&side.normals, cudaEventDisableTiming));
+  }
+  struct Span { const vector3 *src; size_t first, tri; };
+  std::vector<Span> normal_spans;
   RTB_CUDA(cudaEventRecord(e_up0, st));
   float *raw_v = nullptr, *raw_n = nullptr;
   uint32_t *d_first = nullptr;
@@ -594,9 +621,17 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     }
     if (tri) {
       RTB_CUDA(cudaMemcpyAsync(raw_v + 9ull * first[o], pv, 36ull * tri, cudaMemcpyHostToDevice, st));
-      RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * first[o], pn, 36ull * tri, cudaMemcpyHostToDevice, st));
+      if (overlap) normal_spans.push_back({pn, first[o], tri});
+      else RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * first[o], pn, 36ull * tri, cudaMemcpyHostToDevice, st));
     }
     o = e + 1;
+  }
+  if (overlap) {
+    RTB_CUDA(cudaEventRecord(side.verts, st));               // also orders raw_n's allocation before its use
+    RTB_CUDA(cudaStreamWaitEvent(side.st, side.verts, 0));   // vertices first: they gate the build
+    for (const Span &sp : normal_spans)
+      RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * sp.first, sp.src, 36ull * sp.tri, cudaMemcpyHostToDevice, side.st));
+    RTB_CUDA(cudaEventRecord(side.normals, side.st));
   }
   RTB_CUDA(cudaMemcpyAsync(d_first, first.data(), (n_obj + 1) * 4, cudaMemcpyHostToDevice, st));
   std::vector<float> mat(8 * (n_obj ? n_obj : 1), 0.0f);
@@ -662,8 +697,12 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     ++launches;
   }
   if (n) {
-    k_permute<<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2, S->n0,
-                                 S->n1, S->n2);
+    if (overlap)
+      k_permute<true, false><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1,
+                                                S->e2, S->n0, S->n1, S->n2);
+    else
+      k_permute<true, true><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1,
+                                               S->e2, S->n0, S->n1, S->n2);
     ++launches;
   }
 
@@ -719,6 +758,12 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   } else {
     CK(dev_alloc(&S->nodes, NODE_QUADS));
     k_single_node<<<1, 1, 0, st>>>(n, S->nodes);
+    ++launches;
+  }
+  if (overlap) {
+    RTB_CUDA(cudaStreamWaitEvent(st, side.normals, 0));
+    k_permute<false, true><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2,
+                                              S->n0, S->n1, S->n2);
     ++launches;
   }
   uint32_t h_bounds[8];
