@@ -255,6 +255,13 @@ def run_ours(args):
         ds.sync()
         kernel_ms.append(ds.stats()["frame_ms"])
     kernel_ms_avg = max_over_ranks(float(np.mean(kernel_ms)))
+    per_rank_ms = [float(np.mean(kernel_ms))]
+    if dist is not None:
+        import torch
+        t = torch.zeros(world, dtype=torch.float64, device="cuda")
+        t[rank] = per_rank_ms[0]
+        dist.all_reduce(t)
+        per_rank_ms = [round(float(x), 3) for x in t.cpu().tolist()]
     barrier()
 
     # ---- e2e: the drop-in call with HOST buffers ----
@@ -325,6 +332,7 @@ def run_ours(args):
                     "tensor cores (SURVEY 8d); achieved = algorithmic un-fused FP32 ops per launch / CUDA-event "
                     "duration of the launch",
             "algorithmic_ops_per_launch": alg_ops // world, "kernel_ms": kernel_ms_avg,
+            "kernel_ms_per_rank": per_rank_ms,
             "hbm": {"achieved": alg_bytes / world / kern_s / 1e9, "peak": pk["hbm_gbs"], "unit": "GB/s",
                     "frac": alg_bytes / world / kern_s / 1e9 / pk["hbm_gbs"],
                     "note": "cache-less request volume (64 B/node visit, 48 B/triangle test); real DRAM traffic: profiles/"},
