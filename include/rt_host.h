@@ -34,6 +34,9 @@ vector3 create_vec(FILE *file);
 /* Non-exiting variant for tests/bindings: returns 0 or -1 and fills err[errlen]. */
 extern "C" int rtb_parse_svati(const char *path, struct scene *out, char *err, size_t errlen);
 extern "C" void rtb_free_scene(struct scene *scene);
+/* Extension: room for `triangles` triangles in total now, so that the add_object_to_scene
+ * calls that follow never move the vertex / normal arrays (loaders that know the size). */
+extern "C" int rtb_scene_reserve(struct scene *scene, size_t triangles);
 
 /* gpu/headers/printer.h:11-12 (PPM P3 text) */
 FILE *open_output(const char *output, int width, int height);

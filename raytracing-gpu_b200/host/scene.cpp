@@ -18,15 +18,29 @@ extern "C" void rtb_scene_mem_free(void *p) __attribute__((weak));
 
 namespace {
 
-void *bulk_alloc(size_t bytes) { return rtb_scene_mem_alloc ? rtb_scene_mem_alloc(bytes) : std::malloc(bytes); }
-void bulk_free(void *p) {
+// Every bulk array carries its capacity (in vector3) in a 64-byte header in front of the
+// data, so the ABI struct needs no extra field and a caller that knows the final size can
+// reserve once (rtb_scene_reserve) instead of growing by doubling.
+constexpr size_t BULK_HEADER = 64;
+
+void *raw_alloc(size_t bytes) { return rtb_scene_mem_alloc ? rtb_scene_mem_alloc(bytes) : std::malloc(bytes); }
+void raw_free(void *p) {
   if (rtb_scene_mem_free) rtb_scene_mem_free(p);
   else std::free(p);
 }
+size_t bulk_capacity(const vector3 *p) {
+  return p ? *reinterpret_cast<const size_t *>(reinterpret_cast<const char *>(p) - BULK_HEADER) : 0;
+}
+void bulk_free(vector3 *p) {
+  if (p) raw_free(reinterpret_cast<char *>(p) - BULK_HEADER);
+}
 vector3 *bulk_grow(vector3 *old, size_t old_count, size_t new_count) {
-  vector3 *p = static_cast<vector3 *>(bulk_alloc(new_count * sizeof(vector3)));
-  if (old && p) std::memcpy(p, old, old_count * sizeof(vector3));
-  if (old) bulk_free(old);
+  char *base = static_cast<char *>(raw_alloc(BULK_HEADER + new_count * sizeof(vector3)));
+  if (!base) return nullptr;
+  *reinterpret_cast<size_t *>(base) = new_count;
+  vector3 *p = reinterpret_cast<vector3 *>(base + BULK_HEADER);
+  if (old) std::memcpy(p, old, old_count * sizeof(vector3));
+  bulk_free(old);
   return p;
 }
 
@@ -57,9 +71,7 @@ struct scene empty_scene() {
 struct object *add_object_to_scene(struct scene *s, uint32_t nb_triangles) {
   const size_t old_total = s->triangle_count;
   const size_t new_total = old_total + nb_triangles;
-  const bool grow = s->objects_data.vertex == nullptr ||
-                    capacity_for(new_total) != capacity_for(old_total);
-  if (grow) {
+  if (s->objects_data.vertex == nullptr || bulk_capacity(s->objects_data.vertex) < 3 * new_total) {
     const size_t count = capacity_for(new_total) * 3;
     s->objects_data.vertex = bulk_grow(s->objects_data.vertex, 3 * old_total, count);
     s->objects_data.normal = bulk_grow(s->objects_data.normal, 3 * old_total, count);
@@ -88,11 +100,26 @@ vector3 *get_normal(const struct triangles_layout t, uint32_t i) { return t.norm
 
 void free_scene(struct scene *s) {
   if (!s) return;
-  if (s->objects_data.vertex) bulk_free(s->objects_data.vertex);
-  if (s->objects_data.normal) bulk_free(s->objects_data.normal);
+  bulk_free(s->objects_data.vertex);
+  bulk_free(s->objects_data.normal);
   std::free(s->objects);
   std::free(s->lights);
   std::memset(s, 0, sizeof *s);
 }
 
 extern "C" void rtb_free_scene(struct scene *s) { free_scene(s); }
+
+// Extension: make room for `triangles` triangles in total now (exact size, one allocation),
+// so that the add_object_to_scene calls that follow never move the arrays.
+extern "C" int rtb_scene_reserve(struct scene *s, size_t triangles) {
+  if (!s) return -1;
+  if (bulk_capacity(s->objects_data.vertex) >= 3 * triangles && s->objects_data.vertex) return 0;
+  const size_t have = 3 * s->triangle_count, count = 3 * (triangles ? triangles : 1);
+  vector3 *v = bulk_grow(s->objects_data.vertex, have, count);
+  vector3 *n = bulk_grow(s->objects_data.normal, have, count);
+  if (!v || !n) return -1;
+  s->objects_data.vertex = v;
+  s->objects_data.normal = n;
+  reanchor(s);
+  return 0;
+}

@@ -12,6 +12,8 @@
 #include <vector>
 #include "rt_host.h"
 
+extern "C" int rtb_scene_reserve(struct scene *s, size_t triangles);   // scene.cpp
+
 namespace {
 
 uint64_t splitmix64(uint64_t &s) {
@@ -100,6 +102,7 @@ extern "C" int rtb_synth_terrain(struct scene *out, int grid, uint64_t seed, int
       p.first = 0;
       patches.push_back(p);
     }
+  rtb_scene_reserve(out, 2ull * G * G);   // one allocation of the final size
   for (size_t k = 0; k < patches.size(); ++k) {
     Patch &p = patches[k];
     const uint32_t tris = (uint32_t)(2ull * (p.x1 - p.x0) * (p.z1 - p.z0));

@@ -142,3 +142,79 @@ def test_rt_cli_usage_and_errors(tmp_path):
     r = subprocess.run([rt, "/nonexistent.svati", str(tmp_path / "o.png")], capture_output=True, text=True)
     assert r.returncode == 1
     assert "Using structure of arrays (SOA) layout" in r.stdout      # banner of gpu/rt.cpp:58-64
+
+
+def _big_scene_text(n_objects=5, tris=4000, seed=3, comment=None, break_at=None):
+    """A > 1 MB .svati (the size from which the loader cuts the file at `object` tokens)."""
+    rng = np.random.default_rng(seed)
+    out = ["camera 64 48 0 0 -4 1 0 0 0 -1 0 90", "a_light 0.5 0.25 0.125", "# heading comment"]
+    for o in range(n_objects):
+        if comment is not None and o == 2:
+            out.append(comment)
+        out.append("object %d" % (3 * tris))
+        out.append("Kd %.3f 0.5 0.25" % (o / 10))
+        if o % 2:
+            out.append("Nr 0.5")
+        v = rng.standard_normal((3 * tris, 3)).astype(np.float32) * 50
+        n = rng.standard_normal((3 * tris, 3)).astype(np.float32)
+        for i in range(3 * tris):
+            if break_at == (o, i):
+                out.append("v 1.0 oops 2.0")
+            out.append("v %.9g %+.8e %s" % (v[i, 0], v[i, 1], repr(float(v[i, 2]))))
+            out.append("vn %.9g %.9g %.9g" % tuple(n[i]))
+        out.append("d_light 1 1 1 0 -1 %d" % o)
+    return "\n".join(out) + "\n"
+
+
+def _parse_with_threads(path, threads):
+    old = os.environ.get("RTB_PARSE_THREADS")
+    os.environ["RTB_PARSE_THREADS"] = str(threads)
+    try:
+        return pyrtb.HostScene.parse(path)
+    finally:
+        if old is None:
+            del os.environ["RTB_PARSE_THREADS"]
+        else:
+            os.environ["RTB_PARSE_THREADS"] = old
+
+
+def test_parallel_loader_equals_the_one_piece_parse(tmp_path):
+    """host/parser.cpp cuts big files at `object` tokens and parses the pieces on all threads;
+    arrays, materials, light order and camera must equal the single-threaded walk."""
+    p = tmp_path / "big.svati"
+    text = _big_scene_text()
+    assert len(text) > (1 << 20)
+    p.write_text(text)
+    one = _parse_with_threads(str(p), 1).arrays()
+    many = _parse_with_threads(str(p), 8).arrays()
+    assert one["tri_counts"].tolist() == [4000] * 5
+    for k in one:
+        assert np.array_equal(one[k], many[k]), k
+    assert one["lights"][:, 0].tolist() == [pyrtb.AMBIENT] + [pyrtb.DIRECTIONAL] * 5
+    assert one["lights"][1:, 6].tolist() == [0, 1, 2, 3, 4]            # file order kept
+    # values: correctly rounded decimal -> binary32, whatever spelling the writer used
+    rng = np.random.default_rng(3)
+    v0 = rng.standard_normal((12000, 3)).astype(np.float32) * 50
+    assert np.array_equal(many["vertex"][:4000].reshape(-1, 3), v0[::-1])   # LIFO reversal
+
+
+def test_parallel_loader_comment_holding_the_word_object(tmp_path):
+    """`# ... object ...` at top level: the cut inside the comment must not become an object."""
+    p = tmp_path / "c.svati"
+    p.write_text(_big_scene_text(comment="# the next object is big"))
+    one = _parse_with_threads(str(p), 1).arrays()
+    many = _parse_with_threads(str(p), 8).arrays()
+    assert many["tri_counts"].tolist() == [4000] * 5
+    for k in one:
+        assert np.array_equal(one[k], many[k]), k
+
+
+def test_parallel_loader_reports_the_same_error(tmp_path):
+    p = tmp_path / "e.svati"
+    p.write_text(_big_scene_text(break_at=(3, 7)))
+    msgs = []
+    for threads in (1, 8):
+        with pytest.raises(ValueError) as e:
+            _parse_with_threads(str(p), threads)
+        msgs.append(str(e.value))
+    assert msgs[0] == msgs[1] and "number" in msgs[0]
