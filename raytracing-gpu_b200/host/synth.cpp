@@ -8,6 +8,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <charconv>
+#include <cstring>
+#include <string>
 #include <thread>
 #include <vector>
 #include "rt_host.h"
@@ -155,6 +158,48 @@ extern "C" int rtb_synth_terrain(struct scene *out, int grid, uint64_t seed, int
 
 // Scene -> .svati text.  %.9g round-trips binary32 exactly; vertices are written in the
 // order that parse_object's LIFO reversal turns back into the memory order (App. B).
+namespace {
+
+// "<tag>x y z\n" for arr[n-1] .. arr[0] (the loader's LIFO reversal undone), shortest
+// round-trip spelling of every float (std::to_chars), formatted on all threads in batches.
+bool write_lines(FILE *f, const char *tag, const vector3 *arr, size_t n) {
+  const size_t chunk = 1 << 16;
+  const size_t n_chunks = (n + chunk - 1) / chunk;
+  int nt = (int)std::thread::hardware_concurrency();
+  if (nt < 1) nt = 1;
+  if (nt > 64) nt = 64;
+  std::vector<std::string> text((size_t)nt);
+  const size_t tag_len = strlen(tag);
+  for (size_t c0 = 0; c0 < n_chunks; c0 += (size_t)nt) {
+    const size_t batch = std::min<size_t>((size_t)nt, n_chunks - c0);
+    std::vector<std::thread> pool;
+    for (size_t b = 0; b < batch; ++b)
+      pool.emplace_back([&, b] {
+        std::string &out = text[b];
+        out.clear();
+        const size_t lo = (c0 + b) * chunk, hi = std::min(n, lo + chunk);   // positions in output order
+        out.reserve((hi - lo) * 40);
+        char buf[64];
+        for (size_t pos = lo; pos < hi; ++pos) {
+          const vector3 &v = arr[n - 1 - pos];
+          out.append(tag, tag_len);
+          const float xyz[3] = {v.x, v.y, v.z};
+          for (int a = 0; a < 3; ++a) {
+            const std::to_chars_result r = std::to_chars(buf, buf + sizeof buf, xyz[a]);
+            out.append(buf, (size_t)(r.ptr - buf));
+            out.push_back(a == 2 ? '\n' : ' ');
+          }
+        }
+      });
+    for (std::thread &t : pool) t.join();
+    for (size_t b = 0; b < batch; ++b)
+      if (fwrite(text[b].data(), 1, text[b].size(), f) != text[b].size()) return false;
+  }
+  return true;
+}
+
+}  // namespace
+
 extern "C" int rtb_write_svati(const struct scene *s, const char *path, int width, int height) {
   FILE *f = fopen(path, "w");
   if (!f) return -1;
@@ -172,8 +217,10 @@ extern "C" int rtb_write_svati(const struct scene *s, const char *path, int widt
     const size_t nv = 3 * (size_t)ob.triangle_count;
     fprintf(f, "\nobject %zu\nNs %.9g\nKa %.9g %.9g %.9g\nKd %.9g %.9g %.9g\nKs %.9g %.9g %.9g\nNi %.9g\nNr %.9g\nd %.9g\n",
             nv, ob.ns, ob.ka.x, ob.ka.y, ob.ka.z, ob.kd.x, ob.kd.y, ob.kd.z, ob.ks.x, ob.ks.y, ob.ks.z, ob.ni, ob.nr, ob.d);
-    for (size_t k = nv; k-- > 0;) fprintf(f, "v %.9g %.9g %.9g\n", ob.triangles.vertex[k].x, ob.triangles.vertex[k].y, ob.triangles.vertex[k].z);
-    for (size_t k = nv; k-- > 0;) fprintf(f, "vn %.9g %.9g %.9g\n", ob.triangles.normal[k].x, ob.triangles.normal[k].y, ob.triangles.normal[k].z);
+    if (!write_lines(f, "v ", ob.triangles.vertex, nv) || !write_lines(f, "vn ", ob.triangles.normal, nv)) {
+      fclose(f);
+      return -1;
+    }
   }
   return fclose(f) == 0 ? 0 : -1;
 }
