@@ -37,6 +37,9 @@ extern "C" void rtb_free_scene(struct scene *scene);
 /* Extension: room for `triangles` triangles in total now, so that the add_object_to_scene
  * calls that follow never move the vertex / normal arrays (loaders that know the size). */
 extern "C" int rtb_scene_reserve(struct scene *scene, size_t triangles);
+/* Extension: 1 = bulk arrays allocated by this thread from now on are plain memory instead of
+ * page-locked (page-locking costs ~1 s per GB; a one-shot loader does not earn it back). */
+extern "C" void rtb_scene_mem_pageable(int on);
 
 /* gpu/headers/printer.h:11-12 (PPM P3 text) */
 FILE *open_output(const char *output, int width, int height);

@@ -218,6 +218,11 @@ void rtb_set_margin_k(float k);
  * off for A/B measurements.  The frame's bytes do not depend on it. */
 void rtb_set_schedule(int on);
 
+/* Starts the CUDA driver and the device context and returns; no other effect.  A fresh
+ * process pays 0.2 - 1 s for this at its first CUDA call: a loader can spend it on a side
+ * thread while it reads the scene (host/parser.cpp does). */
+void rtb_warmup(void);
+
 /* Page-locked host memory (a frame buffer the D2H copy can target directly) and plain
  * device buffers / CUDA-IPC handles for the multi-process tile gather: rank 0 exports
  * its frame, the other ranks open it and pass the mapped pointer to

@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <chrono>
 #include <mutex>
 #include <vector>
 #include "rtb_internal.h"
@@ -301,15 +302,26 @@ int rtb_device_count(void) {
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out) {
   if (!out) { set_error("out is NULL"); return RTB_ERR_ARG; }
   *out = nullptr;
+  const char *tr = getenv("RTB_TRACE");
+  const bool trace = tr && *tr == '1';
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
   int rc = pick_device(device);
   if (rc) return rc;
+  const auto t1 = clk::now();
   rtb_scene_handle *h = new rtb_scene_handle();
   SceneStore &S = h->store;
   S.device = device;
   rc = acquire_frame_ctx(device, S);
   if (rc) { delete h; return rc; }
+  const auto t2 = clk::now();
   rc = build_scene(scene, flags, &S);
   if (rc) { delete h; return rc; }
+  if (trace) {
+    auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    fprintf(stderr, "rtb_scene_create: device %.2f ms, stream/events/pool %.2f ms, upload+build %.2f ms\n", ms(t0, t1),
+            ms(t1, t2), ms(t2, clk::now()));
+  }
   *out = h;
   return RTB_OK;
 }
@@ -391,15 +403,30 @@ int rtb_scene_render(rtb_scene_t *h, const rtb_frame_opts *opts, unsigned char *
 
 int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing, ptrdiff_t stride, int out_h,
                int out_w) {
+  // RTB_TRACE=1: wall-clock of the three phases on stderr (first-call costs of a fresh process show up here)
+  const char *tr = getenv("RTB_TRACE");
+  const bool trace = tr && *tr == '1';
+  using clk = std::chrono::steady_clock;
+  const auto t0 = clk::now();
   rtb_scene_t *h = nullptr;
   int rc = rtb_scene_create(scene, 0, RTB_BUILD_DEFAULT, &h);
   if (rc) return rc;
+  const auto t1 = clk::now();
   rtb_frame_opts o;
   memset(&o, 0, sizeof o);
   o.aliasing = aliasing;
   o.nranks = 1;
   rc = rtb_scene_render(h, &o, rgba_out, stride, out_h, out_w);
+  const auto t2 = clk::now();
+  rtb_stats st;
+  memset(&st, 0, sizeof st);
+  if (trace) rtb_scene_stats(h, &st);
   rtb_scene_destroy(h);
+  if (trace) {
+    auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    fprintf(stderr, "rtb_render: create %.2f ms (device: upload %.2f + build %.2f), render %.2f ms (frame kernel %.2f), destroy %.2f ms\n",
+            ms(t0, t1), st.upload_ms, st.build_ms, ms(t1, t2), st.frame_ms, ms(t2, clk::now()));
+  }
   return rc;
 }
 
@@ -522,13 +549,22 @@ static std::vector<void *> g_pinned;
 
 void *rtb_scene_mem_alloc(size_t bytes) {
   void *p = nullptr;
-  if (bytes >= (1u << 20) && cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) {
-    std::lock_guard<std::mutex> lk(g_pin_mu);
-    g_pinned.push_back(p);
-    return p;
+  if (bytes >= (1u << 20)) {      // small arrays: plain memory, and no CUDA call at all (the first one initialises the driver)
+    if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) {
+      std::lock_guard<std::mutex> lk(g_pin_mu);
+      g_pinned.push_back(p);
+      return p;
+    }
+    cudaGetLastError();
   }
-  cudaGetLastError();
   return malloc(bytes);
+}
+
+// Driver and context start-up (0.2 - 1 s in a fresh process) without doing any work: loaders
+// call this on a side thread so that it overlaps with reading the scene (host/parser.cpp).
+void rtb_warmup(void) {
+  cudaFree(0);
+  cudaGetLastError();
 }
 
 void rtb_scene_mem_free(void *p) {

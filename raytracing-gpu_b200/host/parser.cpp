@@ -29,6 +29,9 @@
 #include "rt_host.h"
 
 extern "C" int rtb_scene_reserve(struct scene *s, size_t triangles);   // scene.cpp
+extern "C" void rtb_scene_mem_pageable(int on);                        // scene.cpp
+// Present when this file is part of librtb200.so (csrc/api.cu), absent in the host-only library.
+extern "C" void rtb_warmup(void) __attribute__((weak));
 
 namespace {
 
@@ -322,7 +325,10 @@ void parse_buffer(const char *data, size_t size, struct scene *s) {
     size_t total = 0;
     for (const Piece &pc : pieces)
       for (const ObjectData &od : pc.objects) total += od.nv / 3;
+    // plain memory: page-locking 720 MB costs more than the one upload of a one-shot run gains
+    rtb_scene_mem_pageable(1);
     rtb_scene_reserve(s, total);
+    rtb_scene_mem_pageable(0);
     const double t2 = now_s();
     for (Piece &pc : pieces)
       for (const TopItem &it : pc.items) {
@@ -401,9 +407,18 @@ bool load_file(const char *path, FileBuf &buf, std::string &why) {
 
 extern "C" int rtb_parse_svati(const char *path, struct scene *out, char *errbuf, size_t errlen) {
   *out = empty_scene();
+  // the device starts up on a side thread while the file is read and tokenised
+  struct Warm {
+    std::thread t;
+    Warm() { if (rtb_warmup) t = std::thread(rtb_warmup); }
+    ~Warm() { if (t.joinable()) t.join(); }
+  } warm;
   FileBuf buf;
   std::string why;
-  if (!load_file(path, buf, why)) {
+  const double t_load = now_s();
+  const bool loaded = load_file(path, buf, why);
+  if (getenv("RTB_PARSE_TIMING")) fprintf(stderr, "parse: read %zu bytes in %.3f s\n", buf.size, now_s() - t_load);
+  if (!loaded) {
     if (errbuf && errlen) snprintf(errbuf, errlen, "%s\n", why.c_str());
     return -1;
   }

@@ -23,7 +23,13 @@ namespace {
 // reserve once (rtb_scene_reserve) instead of growing by doubling.
 constexpr size_t BULK_HEADER = 64;
 
-void *raw_alloc(size_t bytes) { return rtb_scene_mem_alloc ? rtb_scene_mem_alloc(bytes) : std::malloc(bytes); }
+// Page-locking costs about a second per GB: worth it for a scene that is uploaded many times
+// (bench, fly-through), not for the loader of a one-shot `rt` run, which asks for plain memory.
+thread_local bool t_pageable = false;
+
+void *raw_alloc(size_t bytes) {
+  return rtb_scene_mem_alloc && !t_pageable ? rtb_scene_mem_alloc(bytes) : std::malloc(bytes);
+}
 void raw_free(void *p) {
   if (rtb_scene_mem_free) rtb_scene_mem_free(p);
   else std::free(p);
@@ -108,6 +114,9 @@ void free_scene(struct scene *s) {
 }
 
 extern "C" void rtb_free_scene(struct scene *s) { free_scene(s); }
+
+// Extension (loaders): 1 = the bulk arrays this thread allocates from now on are plain memory, 0 = page-locked when possible.
+extern "C" void rtb_scene_mem_pageable(int on) { t_pageable = on != 0; }
 
 // Extension: make room for `triangles` triangles in total now (exact size, one allocation),
 // so that the add_object_to_scene calls that follow never move the arrays.
