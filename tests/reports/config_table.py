@@ -52,6 +52,9 @@ def ref_gpu(name, w, h):
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--cpu", default="C1,C2a")
+    ap.add_argument("--cpu-scaled", default="C3:8,C4:12",
+                    help="cfg:k pairs: reference CPU renderer at 1/k x 1/k of the resolution, time scaled by k*k (cost is linear in pixels)")
+    ap.add_argument("--oracle", default="C1,C2a,C2b", help="configs also rendered by the oracle (our CPU restatement, all host threads)")
     ap.add_argument("--frames", type=int, default=20)
     ap.add_argument("--skip-ref-gpu", action="store_true")
     ap.add_argument("--ref-gpu-one", nargs=3, default=None)
@@ -94,10 +97,15 @@ if __name__ == "__main__":
             except subprocess.TimeoutExpired:
                 ref_ms = float("inf")
         cpu = ""
-        if cfg in a.cpu.split(",") and name is not None:
+        scaled = dict(x.split(":") for x in a.cpu_scaled.split(",") if x)
+        if (cfg in a.cpu.split(",") or cfg in scaled) and name is not None:
+            k = int(scaled.get(cfg, 1)) if cfg not in a.cpu.split(",") else 1
             with tempfile.TemporaryDirectory() as td:
                 sv = os.path.join(td, "s.svati")
-                hs.write_svati(sv)
+                if k > 1:
+                    scene_of(name, w // k, h // k).write_svati(sv)
+                else:
+                    hs.write_svati(sv)
 
                 def unlimited_stack():      # the CPU renderer's frame is a stack VLA (cpu/raytracer.c:91)
                     resource.setrlimit(resource.RLIMIT_STACK, (resource.RLIM_INFINITY, resource.RLIM_INFINITY))
@@ -106,9 +114,18 @@ if __name__ == "__main__":
                     try:
                         r = subprocess.run([os.path.join(ROOT, "oracle", "_ref", exe), sv, os.path.join(td, "o.ppm")],
                                            capture_output=True, timeout=600, preexec_fn=unlimited_stack)
-                        cpu += "%s %.2f s (rc %d)  " % (exe, time.perf_counter() - t0, r.returncode)
+                        dt = time.perf_counter() - t0
+                        if k > 1:
+                            cpu += "%s %.0f s scaled (%.2f s at %dx%d x %d) (rc %d)  " % (exe, dt * k * k, dt, w // k, h // k, k * k, r.returncode)
+                        else:
+                            cpu += "%s %.2f s (rc %d)  " % (exe, dt, r.returncode)
                     except subprocess.TimeoutExpired:
                         cpu += "%s > 600 s  " % exe
+        if cfg in a.oracle.split(",") and name is not None:
+            import oracle_py
+            t0 = time.perf_counter()
+            oracle_py.orc_render(hs, 3, want_ids=False)
+            cpu += "| oracle (ours, %d threads, GPU semantics 3x3) %.2f s" % (os.cpu_count() or 1, time.perf_counter() - t0)
         ref_txt = "-" if ref_ms is None else ("> %d s" % a.timeout if ref_ms == float("inf") else "%.2f" % ref_ms)
         sp = "-" if ref_ms in (None, float("inf")) else "%.1fx" % (ref_ms / min(to[1:]))
         print("%-4s %-18s %-10s %9d %11d %11d %9d %10.3f %10.1f %11.2f | %13s %9s | %s" % (
