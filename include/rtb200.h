@@ -100,6 +100,13 @@ const char *rtb_last_error(void);
 int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing,
                ptrdiff_t stride, int out_h, int out_w);
 
+/* The same call on `n_devices` GPUs of this process (devices 0 .. n-1): the scene is uploaded
+ * and the hierarchy built on every device, each renders the 32x32-pixel tiles it owns
+ * ((Tx + 3*Ty) mod n) and stores them into device 0's frame through peer access; device 0
+ * downloads the frame.  Same bytes as rtb_render.  `rt` uses it when RT_GPUS > 1. */
+int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int aliasing,
+                     ptrdiff_t stride_bytes, int out_h, int out_w, int n_devices);
+
 /* ---- persistent scene: replaces to_cuda() (gpu/scene.cu:224-352) and the whole
  *      create_octree() host pipeline (gpu/partitioning/octree.cu:362-411):
  *      upload, triangle bounds, Morton codes, radix sort, node emit. ---- */

@@ -8,6 +8,8 @@
 #include <string.h>
 #include <chrono>
 #include <mutex>
+#include <string>
+#include <thread>
 #include <vector>
 #include "rtb_internal.h"
 #include "scene_store.h"
@@ -428,6 +430,69 @@ int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing,
             ms(t0, t1), st.upload_ms, st.build_ms, ms(t1, t2), st.frame_ms, ms(t2, clk::now()));
   }
   return rc;
+}
+
+// render() on several GPUs of this process (SURVEY 8e process model; `rt` reads RT_GPUS):
+// one host thread per device uploads the scene and builds the hierarchy there (the build is
+// deterministic, every device holds the same tree), renders the rank tiles it owns and stores
+// the finished pixels straight into device 0's frame through peer access (NVLink); device 0
+// downloads the frame.  No collective, no intermediate buffers.
+int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int aliasing, ptrdiff_t stride, int out_h,
+                     int out_w, int n_devices) {
+  if (n_devices <= 1) return rtb_render(scene, rgba_out, aliasing, stride, out_h, out_w);
+  if (!scene || !rgba_out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  if (out_w <= 0 || out_h <= 0 || stride < (ptrdiff_t)out_w * 4) { set_error("bad frame geometry"); return RTB_ERR_ARG; }
+  int have = 0;
+  if (cudaGetDeviceCount(&have) != cudaSuccess || have < n_devices) {
+    cudaGetLastError();
+    set_error("%d devices requested, %d present", n_devices, have);
+    return have > 0 ? RTB_ERR_ARG : RTB_ERR_NOGPU;
+  }
+  int rc = pick_device(0);
+  if (rc) return rc;
+  const size_t row = (size_t)out_w * 4, bytes = row * out_h;
+  unsigned char *d_frame = nullptr;
+  RTB_CUDA(cudaMalloc((void **)&d_frame, bytes));
+  RTB_CUDA(cudaMemset(d_frame, 0, bytes));
+  RTB_CUDA(cudaDeviceSynchronize());      // the other devices' streams know nothing of this one
+  std::vector<int> rcs((size_t)n_devices, RTB_OK);
+  std::vector<std::string> errs((size_t)n_devices);
+  std::vector<std::thread> workers;
+  for (int dev = 0; dev < n_devices; ++dev)
+    workers.emplace_back([&, dev] {
+      rtb_scene_t *h = nullptr;
+      int r = rtb_scene_create(scene, dev, RTB_BUILD_DEFAULT, &h);
+      if (!r && dev != 0) {
+        const cudaError_t e = cudaDeviceEnablePeerAccess(0, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) r = cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
+        cudaGetLastError();
+      }
+      if (!r) {
+        rtb_frame_opts o;
+        memset(&o, 0, sizeof o);
+        o.aliasing = aliasing;
+        o.rank = dev;
+        o.nranks = n_devices;
+        r = rtb_scene_render_device(h, &o, d_frame, (ptrdiff_t)row, out_h, out_w, nullptr);
+        if (!r) r = rtb_scene_sync(h);
+      }
+      if (r) errs[(size_t)dev] = g_err;
+      if (h) rtb_scene_destroy(h);
+      rcs[(size_t)dev] = r;
+    });
+  for (std::thread &t : workers) t.join();
+  for (int dev = 0; dev < n_devices; ++dev)
+    if (rcs[(size_t)dev]) {
+      set_error("device %d: %s", dev, errs[(size_t)dev].c_str());
+      cudaSetDevice(0);
+      cudaFree(d_frame);
+      return rcs[(size_t)dev];
+    }
+  RTB_CUDA(cudaSetDevice(0));
+  cudaError_t e = cudaMemcpy2D(rgba_out, (size_t)stride, d_frame, row, row, (size_t)out_h, cudaMemcpyDeviceToHost);
+  cudaFree(d_frame);
+  if (e != cudaSuccess) return cuda_fail(e, "frame download", __FILE__, __LINE__);
+  return RTB_OK;
 }
 
 int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_out, int32_t *obj_out, int out_h,

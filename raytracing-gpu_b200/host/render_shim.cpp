@@ -11,7 +11,12 @@ void render(const scene &scene, char *buffer, int aliasing, std::ptrdiff_t strid
   const int wi = (int)std::ceil((float)scene.camera.width / bsize);
   const int he = (int)std::ceil((float)scene.camera.height / bsize);
   printf("lancement. %i %i %i %i.\n", wi, he, scene.camera.width, scene.camera.height);
-  const int rc = rtb_render(&scene, reinterpret_cast<unsigned char *>(buffer), aliasing, stride, pre_h, pre_w);
+  // RT_GPUS=n: the same frame on n GPUs of this process (argv stays that of the reference)
+  const char *g = getenv("RT_GPUS");
+  const int gpus = g ? atoi(g) : 1;
+  const int rc = gpus > 1 ? rtb_render_multi(&scene, reinterpret_cast<unsigned char *>(buffer), aliasing, stride, pre_h,
+                                             pre_w, gpus)
+                          : rtb_render(&scene, reinterpret_cast<unsigned char *>(buffer), aliasing, stride, pre_h, pre_w);
   printf("done..\n");
   if (rc != RTB_OK) {
     fprintf(stderr, "[error] Computation Error (rtb200 %d): %s\n", rc, rtb_last_error());

@@ -65,7 +65,7 @@ assert C.sizeof(Object) == 72 and C.sizeof(SceneStruct) == 120
 
 # every symbol include/rtb200.h and include/rt_host.h declare with C linkage
 ABI_SYMBOLS = [
-    "rtb_last_error", "rtb_render", "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_set_camera",
+    "rtb_last_error", "rtb_render", "rtb_render_multi", "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_set_camera",
     "rtb_scene_render", "rtb_scene_render_device", "rtb_scene_sync", "rtb_scene_hit_ids", "rtb_scene_trace_rays",
     "rtb_scene_stats", "rtb_radix_sort_pairs_u32", "rtb_radix_sort_pairs_u64", "rtb_inclusive_scan_u32",
     "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_scene_dump_tree",
@@ -288,6 +288,18 @@ class HostScene:
             self.close()
         except Exception:
             pass
+
+
+def render_multi(hs, n_devices, aliasing=3, out=None):
+    """rtb_render_multi: render() on n_devices GPUs of this process, frame composed on device 0."""
+    w, h = hs.width, hs.height
+    if out is None:
+        out = np.empty((h, w, 4), np.uint8)
+    s = hs.scaled(aliasing)
+    fn = lib().rtb_render_multi
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_ssize_t, C.c_int, C.c_int, C.c_int]
+    _check(fn(C.byref(s), out.ctypes.data, aliasing, w * 4, h, w, n_devices))
+    return out
 
 
 def render_oneshot(hs, aliasing=3, out=None):

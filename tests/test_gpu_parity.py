@@ -306,3 +306,16 @@ def test_longest_first_schedule_never_changes_the_frame(gpu):
         ds.close()
     finally:
         lib.rtb_set_schedule(1)
+
+
+def test_render_multi_equals_single_device(gpu):
+    """rtb_render_multi (one host thread per device, tiles stored into device 0's frame over
+    peer access) must give the bytes of rtb_render.  Needs >= 2 devices."""
+    n = pyrtb.device_count()
+    if n < 2:
+        pytest.skip("one device only")
+    for hs in (pyrtb.HostScene.terrain(160, 640, 360), load_golden("car-on-road")[0]):
+        want = pyrtb.render_oneshot(hs, 3)
+        for k in sorted({2, min(n, 4), n}):
+            got = pyrtb.render_multi(hs, k, 3)
+            assert np.array_equal(got, want), "%d devices" % k
