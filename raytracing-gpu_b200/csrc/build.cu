@@ -206,6 +206,15 @@ __device__ __forceinline__ void load_child(const volatile RawNode *nd, int side,
 // longest edge and inherited by inner boxes through the union.  What no finite pad covers:
 // triangles seen edge-on (a -> 0), accepted by the reference arithmetic anywhere in their
 // plane.
+#ifndef RTB_EMIT_WARP_PHASE
+#define RTB_EMIT_WARP_PHASE 1
+#endif
+#ifndef RTB_EMIT_RELEASE_ATOM
+#define RTB_EMIT_RELEASE_ATOM 0
+#endif
+#ifndef RTB_EMIT_ACQUIRE_FENCE
+#define RTB_EMIT_ACQUIRE_FENCE 1
+#endif
 constexpr float SLIVER_KAPPA0 = 4.0f;
 #ifndef RTB_SLIVER_K
 #define RTB_SLIVER_K 3.0f
@@ -300,6 +309,8 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
                                              int *root_info /* [0]=raw root, [1]=height */,
                                              const uint32_t *bounds, float origin_radius, int *raw_parent) {
   const uint32_t i = blockIdx.x * BT + threadIdx.x;
+  [[maybe_unused]] const unsigned lane = threadIdx.x & 31u;
+  const unsigned wmask = __ballot_sync(0xffffffffu, i < n);     // lanes of this warp that hold a triangle
   if (i >= n) return;
   V3 lo, hi;
   tri_box(raw_v, order[i], lo, hi);
@@ -311,9 +322,73 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
   uint32_t l = i, r = i;
   int cur = -1;       // raw inner index of the node we stand on (-1: still the single triangle)
   int height = 0;     // inner nodes on the longest path below (collapsed subtrees count 0)
+#if RTB_EMIT_WARP_PHASE
+  // ---- warp phase: subtrees whose two children are both held by lanes of this warp are
+  // merged through shuffles, no flag, no fence (31 of 32 merges of the whole build; the
+  // fences of the global phase below were 60 % of this kernel's stall cycles).  Two lanes
+  // are siblings exactly when they computed the same parent.
+  {
+    bool holding = true;
+    for (;;) {
+      int parent = -1, side = 0;
+      if (holding) {
+        if (r - l + 1 == n) {            // the whole scene fits in this warp
+          root_info[0] = cur; root_info[1] = height;
+#if RTB_BVH4
+          if (cur >= 0) raw_parent[cur] = -1;
+#endif
+          holding = false;
+        } else if (l == 0 || (r != n - 1 && delta(keys, r) < delta(keys, l - 1))) { parent = (int)r; side = 0; }
+        else { parent = (int)l - 1; side = 1; }
+      }
+      const unsigned hm = __ballot_sync(wmask, holding);
+      if (!hm) return;
+      unsigned grp = 0;
+      if (holding) grp = __match_any_sync(hm, parent);
+      const bool pair = holding && __popc(grp) == 2;
+      const unsigned pm = __ballot_sync(wmask, pair);
+      if (!pm) break;                    // every sibling still missing lives in another warp
+      if (pair) {
+        const int mate = __ffs((int)(grp & ~(1u << lane))) - 1;
+        const uint32_t cnt = r - l + 1;
+        const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
+        const int my_h = cnt <= (uint32_t)LEAF_MAX ? 0 : height;
+#if RTB_BVH4
+        if (cur >= 0) raw_parent[cur] = parent;
+#endif
+        const float mlx = __shfl_sync(pm, lo.x, mate), mly = __shfl_sync(pm, lo.y, mate), mlz = __shfl_sync(pm, lo.z, mate);
+        const float mhx = __shfl_sync(pm, hi.x, mate), mhy = __shfl_sync(pm, hi.y, mate), mhz = __shfl_sync(pm, hi.z, mate);
+        const int m_ref = __shfl_sync(pm, my_ref, mate), m_h = __shfl_sync(pm, my_h, mate);
+        const uint32_t m_r = __shfl_sync(pm, r, mate);
+        if (side == 0) {                 // the left child writes the node and carries on
+          r = m_r;
+          float4 *dst = reinterpret_cast<float4 *>(&raw[parent]);
+          dst[0] = make_float4(lo.x, hi.x, lo.y, hi.y);
+          dst[1] = make_float4(mlx, mhx, mly, mhy);
+          dst[2] = make_float4(lo.z, hi.z, mlz, mhz);
+          dst[3] = make_float4(__int_as_float(my_ref), __int_as_float(m_ref), __int_as_float((int)l),
+                               __int_as_float((int)(r - l + 1)));
+          lo = mk(fminf(lo.x, mlx), fminf(lo.y, mly), fminf(lo.z, mlz));
+          hi = mk(fmaxf(hi.x, mhx), fmaxf(hi.y, mhy), fmaxf(hi.z, mhz));
+          height = (my_h > m_h ? my_h : m_h) + 1;
+          cur = parent;
+        } else {
+          holding = false;
+        }
+      }
+    }
+    if (!holding) return;
+  }
+#endif
   for (;;) {
     const uint32_t cnt = r - l + 1;
-    if (cnt == n) { root_info[0] = cur; root_info[1] = height; if (cur >= 0) raw_parent[cur] = -1; return; }
+    if (cnt == n) {
+      root_info[0] = cur; root_info[1] = height;
+#if RTB_BVH4
+      if (cur >= 0) raw_parent[cur] = -1;
+#endif
+      return;
+    }
     const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
     const int my_h = cnt <= (uint32_t)LEAF_MAX ? 0 : height;
     int parent, side;
@@ -321,11 +396,24 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     else { parent = (int)l - 1; side = 1; }
     store_child(&raw[parent], side, lo, hi, my_ref);
     child_height[2 * parent + side] = my_h;
+#if RTB_BVH4
     if (cur >= 0) raw_parent[cur] = parent;
-    __threadfence();
+#endif
+#if RTB_EMIT_RELEASE_ATOM
+    int other;
+    asm volatile("atom.release.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(other) : "l"(visit + parent), "r"(side == 0 ? (int)l : (int)r) : "memory");
+    if (other < 0) return;
+#else
+    __threadfence();                             // our child record is visible before the flag is
     const int other = atomicExch(&visit[parent], side == 0 ? (int)l : (int)r);
     if (other < 0) return;                       // first to arrive: the sibling will carry on
+#if RTB_EMIT_ACQUIRE_FENCE
     __threadfence();
+#endif
+#endif
+    // The sibling's record is read with volatile loads (L2, never a stale L1 line).  Tried and
+    // not faster on 10 M triangles: one acq_rel exchange (libcu++), a release exchange, no
+    // acquire fence; what pays is needing the flag protocol for 1 merge in 32 only (warp phase).
     V3 slo, shi;
     load_child(&raw[parent], side ^ 1, slo, shi);
     const int oh = ((volatile int *)child_height)[2 * parent + (side ^ 1)];
