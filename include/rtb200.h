@@ -116,6 +116,7 @@ typedef struct rtb_scene_handle rtb_scene_t;
 /* flags for rtb_scene_create */
 #define RTB_BUILD_DEFAULT     0u
 #define RTB_BUILD_NO_TREE     1u   /* skip the hierarchy (brute-force tracer only) */
+#define RTB_BUILD_CUBIC_KEYS  2u   /* keep the x,y,z-interleaved sort keys: no choice between key layouts */
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
                      rtb_scene_t **out);
@@ -181,7 +182,13 @@ typedef struct rtb_stats {
   uint64_t rays_primary, rays_shadow, rays_bounce;   /* last render with count_rays */
   uint64_t node_visits, tri_tests;                    /* idem */
   uint64_t kernel_launches;                           /* kernels launched by last render */
-  uint64_t reserved[4];
+  uint64_t build_launches;             /* kernels launched by the last rtb_scene_create */
+  uint64_t key_mode;                   /* sort-key layout of the hierarchy: 0 = x,y,z interleaved,
+                                          1 / 2 / 3 = axis x / y / z last (last rtb_scene_create) */
+  uint64_t mode_cost;                  /* sample-tree surface-area cost of modes 1, 2, 3 relative to
+                                          mode 0 in 1/1000, 16 bits each (bits 0-15: mode 1);
+                                          0 = the choice was not evaluated */
+  uint64_t builder;                    /* 0 = Morton radix tree, 1 = binned surface-area splits */
 } rtb_stats;
 
 int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);

@@ -564,7 +564,16 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
   out->rays_primary = S.counters[0]; out->rays_shadow = S.counters[1]; out->rays_bounce = S.counters[2];
   out->node_visits = S.counters[3]; out->tri_tests = S.counters[4];
   out->kernel_launches = S.frame_launches;
-  out->reserved[0] = S.build_launches;
+  out->build_launches = S.build_launches;
+  out->key_mode = (uint64_t)S.key_mode;
+  out->mode_cost = 0;
+  if (S.mode_cost[0] > 0)
+    for (int k = 1; k < 4; ++k) {
+      unsigned long long rel = (unsigned long long)(1000.0 * S.mode_cost[k] / S.mode_cost[0] + 0.5);
+      if (rel > 0xffffull) rel = 0xffffull;
+      out->mode_cost |= rel << (16 * (k - 1));
+    }
+  out->builder = (uint64_t)S.builder;
   return RTB_OK;
 }
 

@@ -30,6 +30,8 @@ namespace rtb {
 namespace {
 
 constexpr int BT = 256;
+constexpr uint32_t MODE_CHOICE_MIN = 8192;      // scenes below this keep the cubic key layout
+constexpr uint32_t MODE_SAMPLE_MAX = 1u << 18;   // triangles in a sample tree
 
 __device__ __forceinline__ float warp_min(float v) {
 #pragma unroll
@@ -87,14 +89,43 @@ __device__ __forceinline__ uint64_t spread21(uint32_t v) {
   return x;
 }
 
-__global__ void __launch_bounds__(BT) k_morton(const float *raw_v, uint32_t n, const uint32_t *bounds,
-                                               uint64_t *keys, uint32_t *vals) {
+// 21 bits -> every second bit (two-way interleave)
+__device__ __forceinline__ uint64_t spread21_2(uint32_t v) {
+  uint64_t x = v & 0x1fffffu;
+  x = (x | x << 16) & 0x0000ffff0000ffffull;
+  x = (x | x << 8) & 0x00ff00ff00ff00ffull;
+  x = (x | x << 4) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | x << 2) & 0x3333333333333333ull;
+  x = (x | x << 1) & 0x5555555555555555ull;
+  return x;
+}
+
+// Key layouts (all 63 bits, cubic cells).  Mode 0: x, y, z bits interleaved, the octree cell
+// path.  Mode 1 / 2 / 3: axis x / y / z comes LAST: the other two axes interleaved (42 bits,
+// a quadtree path), then the 21 bits of that axis.  A surface that is mostly perpendicular to
+// one axis (a height field) gains nothing from cuts along it: such a cut separates the
+// triangles of a cell by height into two sets that both span the cell, a wasted level for
+// every ray (C5: 42.8 -> 37.1 node visits and 5.2 -> 4.6 triangle tests per ray,
+// tools/tree_quality.cpp).  build_scene picks the mode by the surface-area cost of sample
+// trees (k_emit sah_acc, k_choose_mode).
+__device__ __forceinline__ uint64_t morton_key(int mode, uint32_t qx, uint32_t qy, uint32_t qz) {
+  if (mode == 1) return ((spread21_2(qy) | (spread21_2(qz) << 1)) << 21) | qx;
+  if (mode == 2) return ((spread21_2(qx) | (spread21_2(qz) << 1)) << 21) | qy;
+  if (mode == 3) return ((spread21_2(qx) | (spread21_2(qy) << 1)) << 21) | qz;
+  return spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
+}
+
+// Entry i is triangle i * stride (stride > 1: the sample trees of the mode choice).
+__global__ void __launch_bounds__(BT) k_morton(const float *raw_v, uint32_t n, uint32_t stride, const uint32_t *bounds,
+                                               int mode, const int *d_mode, uint64_t *keys, uint32_t *vals) {
   const uint32_t i = blockIdx.x * BT + threadIdx.x;
   if (i >= n) return;
+  if (d_mode) mode = *d_mode;
+  const uint32_t tri = i * stride;
   const V3 smin = mk(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
   const V3 smax = mk(ord2f(bounds[3]), ord2f(bounds[4]), ord2f(bounds[5]));
   V3 lo, hi;
-  tri_box(raw_v, i, lo, hi);
+  tri_box(raw_v, tri, lo, hi);
   const float S = 2097152.0f;   // 2^21 cells per axis
   // cubic cells: one scale for the three axes (the scene box's longest side), so a code
   // prefix is an octree cell and flat scenes do not waste their top splits on a thin axis
@@ -106,8 +137,8 @@ __global__ void __launch_bounds__(BT) k_morton(const float *raw_v, uint32_t n, c
   uint32_t qx = (uint32_t)fminf(fmaxf(fx, 0.0f), S - 1.0f);
   uint32_t qy = (uint32_t)fminf(fmaxf(fy, 0.0f), S - 1.0f);
   uint32_t qz = (uint32_t)fminf(fmaxf(fz, 0.0f), S - 1.0f);
-  keys[i] = spread21(qx) | (spread21(qy) << 1) | (spread21(qz) << 2);
-  vals[i] = i;
+  keys[i] = morton_key(mode, qx, qy, qz);
+  vals[i] = tri;
 }
 
 // Identity order (RTB_BUILD_NO_TREE): slot == global id.
@@ -304,10 +335,47 @@ __device__ __forceinline__ void sliver_pad(const float *raw_v, uint32_t i, float
 #endif
 }
 
+// Surface-area cost of one merge (sample trees of the mode choice): the merged node is visited
+// in proportion to its box area; a child that stays a leaf costs 1.5 visits per triangle (a
+// triangle test against a node visit in k_frame).  Fixed point, so the sum does not depend on
+// the order of the atomics and every build of a scene takes the same decision.
+constexpr int SAH_SLOTS = 64;
+__device__ __forceinline__ float box_area(V3 lo, V3 hi) {
+  const float dx = hi.x - lo.x, dy = hi.y - lo.y, dz = hi.z - lo.z;
+  return dx * dy + dy * dz + dz * dx;
+}
+__device__ __forceinline__ void sah_add(unsigned long long *acc, int node, float scale, V3 alo, V3 ahi, uint32_t acnt,
+                                        V3 blo, V3 bhi, uint32_t bcnt) {
+  if (acnt + bcnt <= (uint32_t)LEAF_MAX) return;      // stays inside a leaf
+  const V3 mlo = mk(fminf(alo.x, blo.x), fminf(alo.y, blo.y), fminf(alo.z, blo.z));
+  const V3 mhi = mk(fmaxf(ahi.x, bhi.x), fmaxf(ahi.y, bhi.y), fmaxf(ahi.z, bhi.z));
+  float c = box_area(mlo, mhi);
+  if (acnt <= (uint32_t)LEAF_MAX) c += 1.5f * (float)acnt * box_area(alo, ahi);
+  if (bcnt <= (uint32_t)LEAF_MAX) c += 1.5f * (float)bcnt * box_area(blo, bhi);
+  atomicAdd(acc + (node & (SAH_SLOTS - 1)), (unsigned long long)(c * scale));
+}
+
+// cost[c * SAH_SLOTS + k]: slot sums of candidate c.  Mode 0 (cubic) stays unless another
+// mode's sample tree is at least 5 % cheaper.  out[0] = mode, out[1 + c] = cost >> 8.
+__global__ void k_choose_mode(const unsigned long long *cost, int n_cand, int *out) {
+  if (threadIdx.x || blockIdx.x) return;
+  unsigned long long best = 0;
+  int mode = 0;
+  for (int c = 0; c < n_cand; ++c) {
+    unsigned long long s = 0;
+    for (int k = 0; k < SAH_SLOTS; ++k) s += cost[c * SAH_SLOTS + k];
+    out[1 + c] = (int)min(s >> 8, 0x7fffffffull);
+    if (c == 0) best = s - s / 20;
+    else if (s < best) { best = s; mode = c; }
+  }
+  out[0] = mode;
+}
+
 __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
                                              uint32_t n, RawNode *raw, int *visit, int *child_height,
                                              int *root_info /* [0]=raw root, [1]=height */,
-                                             const uint32_t *bounds, float origin_radius, int *raw_parent) {
+                                             const uint32_t *bounds, float origin_radius, int *raw_parent,
+                                             unsigned long long *sah_acc /* nullptr or [SAH_SLOTS] */) {
   const uint32_t i = blockIdx.x * BT + threadIdx.x;
   [[maybe_unused]] const unsigned lane = threadIdx.x & 31u;
   const unsigned wmask = __ballot_sync(0xffffffffu, i < n);     // lanes of this warp that hold a triangle
@@ -318,6 +386,14 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     float amax = 0;
     for (int k = 0; k < 6; ++k) amax = fmaxf(amax, fabsf(ord2f(bounds[k])));
     sliver_pad(raw_v, order[i], SLIVER_K * 1.1920929e-7f * (amax + origin_radius), lo, hi);
+  }
+  // surface-area cost of the tree in units of 2^-24 of the scene box's area (sah_acc only)
+  float sah_scale = 0.0f;
+  if (sah_acc) {
+    const float ex = ord2f(bounds[3]) - ord2f(bounds[0]), ey = ord2f(bounds[4]) - ord2f(bounds[1]),
+                ez = ord2f(bounds[5]) - ord2f(bounds[2]);
+    const float ra = ex * ey + ey * ez + ez * ex;
+    sah_scale = ra > 0 ? 16777216.0f / ra : 0.0f;
   }
   uint32_t l = i, r = i;
   int cur = -1;       // raw inner index of the node we stand on (-1: still the single triangle)
@@ -368,6 +444,8 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
           dst[2] = make_float4(lo.z, hi.z, mlz, mhz);
           dst[3] = make_float4(__int_as_float(my_ref), __int_as_float(m_ref), __int_as_float((int)l),
                                __int_as_float((int)(r - l + 1)));
+          if (sah_acc)
+            sah_add(sah_acc, parent, sah_scale, lo, hi, cnt, mk(mlx, mly, mlz), mk(mhx, mhy, mhz), r - l + 1 - cnt);
           lo = mk(fminf(lo.x, mlx), fminf(lo.y, mly), fminf(lo.z, mlz));
           hi = mk(fmaxf(hi.x, mhx), fmaxf(hi.y, mhy), fmaxf(hi.z, mhz));
           height = (my_h > m_h ? my_h : m_h) + 1;
@@ -417,9 +495,10 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     V3 slo, shi;
     load_child(&raw[parent], side ^ 1, slo, shi);
     const int oh = ((volatile int *)child_height)[2 * parent + (side ^ 1)];
+    if (side == 0) r = (uint32_t)other; else l = (uint32_t)other;
+    if (sah_acc) sah_add(sah_acc, parent, sah_scale, lo, hi, cnt, slo, shi, r - l + 1 - cnt);
     lo = mk(fminf(lo.x, slo.x), fminf(lo.y, slo.y), fminf(lo.z, slo.z));
     hi = mk(fmaxf(hi.x, shi.x), fmaxf(hi.y, shi.y), fmaxf(hi.z, shi.z));
-    if (side == 0) r = (uint32_t)other; else l = (uint32_t)other;
     raw[parent].lo = (int)l;
     raw[parent].cnt = (int)(r - l + 1);
     height = (my_h > oh ? my_h : oh) + 1;
@@ -766,12 +845,44 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   const bool tree = !(flags & RTB_BUILD_NO_TREE) && n > (uint32_t)LEAF_MAX;
   const unsigned gN = (n + BT - 1) / BT;
   uint64_t *keys = nullptr;
+  // build scratch of the hierarchy (also used by the sample trees of the key-mode choice)
+  RawNode *raw = nullptr;
+  int *visit = nullptr, *child_h = nullptr, *root_info = nullptr, *raw_parent = nullptr;
+  int *d_mode = nullptr;                      // [0] chosen key mode, [1..4] sample-tree costs
+  S->key_mode = 0;
+  for (int k = 0; k < 4; ++k) S->mode_cost[k] = 0;
   if (tree) {
+    const uint32_t n_inner = n - 1;
+    CK(tmp.alloc(&raw, n_inner)); CK(tmp.alloc(&visit, n_inner)); CK(tmp.alloc(&child_h, 2ull * n_inner));
+    CK(tmp.alloc(&root_info, 2)); CK(tmp.alloc(&raw_parent, n_inner));
+    CK(tmp.alloc(&d_mode, 8));
+    RTB_CUDA(cudaMemsetAsync(d_mode, 0, 8 * sizeof(int), st));
     uint64_t *keys_a = nullptr, *keys_b = nullptr;
     uint32_t *vals_b = nullptr, *scratch = nullptr;
     const size_t sw = radix_sort_scratch_words(n);
     CK(tmp.alloc(&keys_a, n)); CK(tmp.alloc(&keys_b, n)); CK(tmp.alloc(&vals_b, n)); CK(tmp.alloc(&scratch, sw));
-    k_morton<<<gN, BT, 0, st>>>(raw_v, n, d_bounds, keys_a, S->order);
+    // ---- key mode: surface-area cost of the four candidate trees over a strided sample ----
+    const bool choose = n >= MODE_CHOICE_MIN && !(flags & RTB_BUILD_CUBIC_KEYS);
+    if (choose) {
+      const uint32_t stride = (n + MODE_SAMPLE_MAX - 1) / MODE_SAMPLE_MAX;
+      const uint32_t m = (n + stride - 1) / stride;
+      unsigned long long *d_cost = nullptr;
+      CK(tmp.alloc(&d_cost, 4 * SAH_SLOTS));
+      RTB_CUDA(cudaMemsetAsync(d_cost, 0, 4 * SAH_SLOTS * sizeof(unsigned long long), st));
+      const unsigned gM = (m + BT - 1) / BT;
+      for (int c = 0; c < 4; ++c) {
+        k_morton<<<gM, BT, 0, st>>>(raw_v, m, stride, d_bounds, c, nullptr, keys_a, S->order);
+        int in_alt = 0;
+        CK(dev_radix_sort_pairs_u64(keys_a, S->order, keys_b, vals_b, m, MORTON_BITS, scratch, sw, st, &in_alt, &launches));
+        RTB_CUDA(cudaMemsetAsync(visit, 0xff, 4ull * (m - 1), st));
+        k_emit<<<gM, BT, 0, st>>>(raw_v, in_alt ? vals_b : S->order, in_alt ? keys_b : keys_a, m, raw, visit, child_h,
+                                  root_info, d_bounds, S->origin_radius, raw_parent, d_cost + c * SAH_SLOTS);
+        launches += 2;
+      }
+      k_choose_mode<<<1, 32, 0, st>>>(d_cost, 4, d_mode);
+      ++launches;
+    }
+    k_morton<<<gN, BT, 0, st>>>(raw_v, n, 1, d_bounds, 0, d_mode, keys_a, S->order);
     ++launches;
     int in_alt = 0;
     CK(dev_radix_sort_pairs_u64(keys_a, S->order, keys_b, vals_b, n, MORTON_BITS, scratch, sw, st, &in_alt, &launches));
@@ -797,22 +908,17 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   S->n_nodes = 1; S->n_leaves = n ? 1 : 0; S->max_leaf = n; S->height = 1; S->root = 0;
   if (tree) {
     const uint32_t n_inner = n - 1;
-    RawNode *raw = nullptr;
-    int *visit = nullptr, *child_h = nullptr, *root_info = nullptr;
     uint32_t *live = nullptr, *scan_scratch = nullptr;
     unsigned int *d_stats = nullptr;
     const size_t ssw = scan_scratch_words(n_inner + 1);
-    CK(tmp.alloc(&raw, n_inner)); CK(tmp.alloc(&visit, n_inner)); CK(tmp.alloc(&child_h, 2ull * n_inner));
-    CK(tmp.alloc(&root_info, 2)); CK(tmp.alloc(&live, n_inner + 1)); CK(tmp.alloc(&scan_scratch, ssw));
+    CK(tmp.alloc(&live, n_inner + 1)); CK(tmp.alloc(&scan_scratch, ssw));
     CK(tmp.alloc(&d_stats, 2));
-    int *raw_parent = nullptr;
-    CK(tmp.alloc(&raw_parent, n_inner));
     RTB_CUDA(cudaMemsetAsync(visit, 0xff, 4ull * n_inner, st));
     RTB_CUDA(cudaMemsetAsync(raw, 0, sizeof(RawNode) * (size_t)n_inner, st));
     RTB_CUDA(cudaMemsetAsync(d_stats, 0, 8, st));
     RTB_CUDA(cudaMemsetAsync(live, 0, 4ull * (n_inner + 1), st));
     k_emit<<<gN, BT, 0, st>>>(raw_v, S->order, keys, n, raw, visit, child_h, root_info, d_bounds, S->origin_radius,
-                              raw_parent);
+                              raw_parent, nullptr);
 #if RTB_BVH4
     unsigned char *keep = nullptr;
     CK(tmp.alloc(&keep, n_inner));
@@ -826,7 +932,11 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     int h_root[2] = {0, 0};
     RTB_CUDA(cudaMemcpyAsync(&n_live, live + n_inner, 4, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaMemcpyAsync(h_root, root_info, 8, cudaMemcpyDeviceToHost, st));
+    int h_mode[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    RTB_CUDA(cudaMemcpyAsync(h_mode, d_mode, sizeof h_mode, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
+    S->key_mode = h_mode[0];
+    for (int k = 0; k < 4; ++k) S->mode_cost[k] = h_mode[1 + k];
     if (n_live == 0 || h_root[0] < 0) { set_error("hierarchy build produced no root"); return RTB_ERR_CUDA; }
     if (h_root[1] > HEIGHT_MAX) { set_error("hierarchy depth %d exceeds %d", h_root[1], HEIGHT_MAX); return RTB_ERR_LIMIT; }
     CK(dev_alloc(&S->nodes, (size_t)NODE_QUADS * n_live));

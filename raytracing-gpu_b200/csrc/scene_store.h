@@ -17,6 +17,9 @@ struct SceneStore {
   uint32_t n_tris = 0, n_objects = 0, n_lights = 0;
   uint32_t n_nodes = 0, n_leaves = 0, max_leaf = 0;
   int root = 0, height = 0;
+  int builder = 0;                      // 0: Morton radix tree, 1: binned surface-area splits (build.cu)
+  int key_mode = 0;                     // sort-key layout the build chose (build.cu morton_key)
+  int mode_cost[4] = {0, 0, 0, 0};      // surface-area cost of the four sample trees (0: not evaluated)
   bool has_tree = false;
   float abs_max = 0;
   float origin_radius = 0;              // ray-origin radius the sliver padding was built for (build.cu)

@@ -57,7 +57,8 @@ class Stats(C.Structure):
                 ("tree_bytes", C.c_uint64), ("triangle_bytes", C.c_uint64), ("upload_ms", C.c_double),
                 ("build_ms", C.c_double), ("frame_ms", C.c_double), ("rays_primary", C.c_uint64),
                 ("rays_shadow", C.c_uint64), ("rays_bounce", C.c_uint64), ("node_visits", C.c_uint64),
-                ("tri_tests", C.c_uint64), ("kernel_launches", C.c_uint64), ("reserved", C.c_uint64 * 4)]
+                ("tri_tests", C.c_uint64), ("kernel_launches", C.c_uint64), ("build_launches", C.c_uint64),
+                ("key_mode", C.c_uint64), ("mode_cost", C.c_uint64), ("builder", C.c_uint64)]
 
 
 assert C.sizeof(Vec3) == 12 and C.sizeof(Light) == 28 and C.sizeof(Camera) == 48
@@ -392,9 +393,7 @@ class DeviceScene:
     def stats(self):
         st = Stats()
         _check(lib().rtb_scene_stats(self.h, C.byref(st)))
-        d = {k: getattr(st, k) for k, _ in Stats._fields_ if k != "reserved"}
-        d["build_launches"] = st.reserved[0]
-        return d
+        return {k: getattr(st, k) for k, _ in Stats._fields_}
 
     def dump_tree(self):
         nn, nt = C.c_size_t(), C.c_size_t()

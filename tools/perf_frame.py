@@ -19,6 +19,7 @@ ap.add_argument("--h", type=int, default=2160)
 ap.add_argument("--count", action="store_true")
 ap.add_argument("--wave", action="store_true")
 ap.add_argument("--nosched", action="store_true")
+ap.add_argument("--flags", type=int, default=0, help="rtb_scene_create flags (2: cubic keys only)")
 ap.add_argument("--scene", default=None, help="golden scene name instead of the terrain (rendered at --w x --h)")
 a = ap.parse_args()
 pyrtb.lib().rtb_set_schedule(0 if a.nosched else 1)
@@ -28,10 +29,12 @@ if a.scene:
     hs = load_golden(a.scene)[0].with_resolution(a.w, a.h)
 else:
     hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
-ds = pyrtb.DeviceScene(hs, 3)
+ds = pyrtb.DeviceScene(hs, 3, flags=a.flags)
 ds.frame_kernel = int(a.wave)
 st = ds.stats()
-print("build %.2f ms upload %.2f ms nodes %d depth %d" % (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"]))
+print("build %.2f ms upload %.2f ms nodes %d depth %d  builder %d key mode %d (sample-tree cost of modes 1,2,3 vs 0: %s)" %
+      (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"], st["builder"], st["key_mode"],
+       [((st["mode_cost"] >> (16 * k)) & 0xffff) / 1000 for k in range(3)]))
 ks = [float(x) for x in a.k.split(",")] if a.k else [None]
 for k in ks:
     if k is not None:
