@@ -117,6 +117,7 @@ typedef struct rtb_scene_handle rtb_scene_t;
 #define RTB_BUILD_DEFAULT     0u
 #define RTB_BUILD_NO_TREE     1u   /* skip the hierarchy (brute-force tracer only) */
 #define RTB_BUILD_CUBIC_KEYS  2u   /* keep the x,y,z-interleaved sort keys: no choice between key layouts */
+#define RTB_BUILD_RADIX_ONLY  4u   /* plain Morton radix tree: no surface-area rebuild of the clusters */
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
                      rtb_scene_t **out);
