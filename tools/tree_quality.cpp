@@ -48,6 +48,7 @@ static float g_margin_k = 24.0f;
 static uint32_t g_cluster = 0;   // > 0: radix ranges of at most this many triangles are built with binned SAH
 static int g_axes = 3;           // 3: bin all axes, 1: longest centroid axis only
 static int sah_build(struct Tree &t, uint32_t l, uint32_t r, struct Box &out, int depth, int &maxdepth);
+static uint32_t g_small = 0;     // segments of at most this many triangles are halved by position (no binning)
 static int g_pad = 1;            // needle padding of build.cu (sliver_pad, mode 5)
 static int g_mode = 0;          // 0 cubic xyz interleave, 1/2/3: axis x/y/z last (2D Morton of the other two first)
 static std::vector<V3> g_v;       // 3 per triangle
@@ -187,9 +188,11 @@ static int sah_build(Tree &t, uint32_t l, uint32_t r, Box &out, int depth, int &
   if (cnt <= (uint32_t)LEAF_MAX) return leaf_ref(l, cnt);
   constexpr int NB = 16;
   float best_cost = INFINITY; int best_axis = -1, best_bin = 0;
+  const bool skip_bins = cnt <= g_small;
   int longest = 0;
   { const V3 e = cb.hi - cb.lo; longest = e.x >= e.y ? (e.x >= e.z ? 0 : 2) : (e.y >= e.z ? 1 : 2); }
   for (int ax = 0; ax < 3; ++ax) {
+    if (skip_bins) break;
     if (g_axes == 1 && ax != longest) continue;
     const float lo = (&cb.lo.x)[ax], hi = (&cb.hi.x)[ax];
     if (!(hi > lo)) continue;
@@ -453,6 +456,7 @@ int main(int argc, char **argv) {
   if (argc > 6) g_cluster = (uint32_t)atoi(argv[6]);
   if (argc > 7) g_axes = atoi(argv[7]);
   if (argc > 8) g_pad = atoi(argv[8]);
+  if (getenv("SMALL")) g_small = (uint32_t)atoi(getenv("SMALL"));
   struct scene sc;
   if (strstr(what, ".svati")) {
     char err[256];
