@@ -118,6 +118,9 @@ typedef struct rtb_scene_handle rtb_scene_t;
 #define RTB_BUILD_NO_TREE     1u   /* skip the hierarchy (brute-force tracer only) */
 #define RTB_BUILD_CUBIC_KEYS  2u   /* keep the x,y,z-interleaved sort keys: no choice between key layouts */
 #define RTB_BUILD_RADIX_ONLY  4u   /* plain Morton radix tree: no surface-area rebuild of the clusters */
+#define RTB_BUILD_ONE_FRAME   8u   /* the scene will be rendered once (rtb_render passes this): scenes of more
+                                      than 2^18 triangles keep the radix tree, whose build is 3 ms shorter on
+                                      10 M triangles than the 1.3 ms the better clusters save per 4K frame */
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
                      rtb_scene_t **out);

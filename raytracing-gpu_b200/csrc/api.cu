@@ -411,7 +411,7 @@ int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing,
   using clk = std::chrono::steady_clock;
   const auto t0 = clk::now();
   rtb_scene_t *h = nullptr;
-  int rc = rtb_scene_create(scene, 0, RTB_BUILD_DEFAULT, &h);
+  int rc = rtb_scene_create(scene, 0, RTB_BUILD_ONE_FRAME, &h);
   if (rc) return rc;
   const auto t1 = clk::now();
   rtb_frame_opts o;
@@ -461,7 +461,7 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
   for (int dev = 0; dev < n_devices; ++dev)
     workers.emplace_back([&, dev] {
       rtb_scene_t *h = nullptr;
-      int r = rtb_scene_create(scene, dev, RTB_BUILD_DEFAULT, &h);
+      int r = rtb_scene_create(scene, dev, RTB_BUILD_ONE_FRAME, &h);
       if (!r && dev != 0) {
         const cudaError_t e = cudaDeviceEnablePeerAccess(0, 0);
         if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) r = cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);

@@ -32,6 +32,7 @@ namespace {
 constexpr int BT = 256;
 constexpr uint32_t MODE_CHOICE_MIN = 8192;      // scenes below this keep the cubic key layout
 constexpr uint32_t MODE_SAMPLE_MAX = 1u << 18;   // triangles in a sample tree
+constexpr uint32_t ONE_FRAME_SAH_MAX = 1u << 18; // RTB_BUILD_ONE_FRAME: larger scenes keep the radix tree
 
 __device__ __forceinline__ float warp_min(float v) {
 #pragma unroll
@@ -366,20 +367,52 @@ __device__ __forceinline__ void sah_add(unsigned long long *acc, int node, float
   atomicAdd(acc + (node & (SAH_SLOTS - 1)), (unsigned long long)(c * scale));
 }
 
-// cost[c * SAH_SLOTS + k]: slot sums of candidate c.  Mode 0 (cubic) stays unless another
-// mode's sample tree is at least 5 % cheaper.  out[0] = mode, out[1 + c] = cost >> 8.
-__global__ void k_choose_mode(const unsigned long long *cost, int n_cand, int *out) {
-  if (threadIdx.x || blockIdx.x) return;
-  unsigned long long best = 0;
-  int mode = 0;
-  for (int c = 0; c < n_cand; ++c) {
-    unsigned long long s = 0;
-    for (int k = 0; k < SAH_SLOTS; ++k) s += cost[c * SAH_SLOTS + k];
-    out[1 + c] = (int)min(s >> 8, 0x7fffffffull);
-    if (c == 0) best = s - s / 20;
-    else if (s < best) { best = s; mode = c; }
+// Which axis could come last: the one the surface is most perpendicular to.  acc[a] = sum over
+// the sample of |(e1 x e2)_a| = 2 x area x |normal_a|, in fixed point (order-independent).
+__global__ void __launch_bounds__(BT) k_normal_stat(const float *raw_v, uint32_t n, uint32_t stride,
+                                                    const uint32_t *bounds, unsigned long long *acc) {
+  const uint32_t i = blockIdx.x * BT + threadIdx.x;
+  unsigned long long v[3] = {0, 0, 0};
+  if (i < n) {
+    const float *p = raw_v + 9ull * (i * stride);
+    const V3 a = mk(p[0], p[1], p[2]), e1 = vsub(mk(p[3], p[4], p[5]), a), e2 = vsub(mk(p[6], p[7], p[8]), a);
+    const V3 c = vcross(e1, e2);
+    const float ext = fmaxf(fmaxf(ord2f(bounds[3]) - ord2f(bounds[0]), ord2f(bounds[4]) - ord2f(bounds[1])),
+                            ord2f(bounds[5]) - ord2f(bounds[2]));
+    const float sc = ext > 0 ? 1099511627776.0f / ext / ext : 0.0f;     // 2^40 / extent^2
+    const float q[3] = {fabsf(c.x) * sc, fabsf(c.y) * sc, fabsf(c.z) * sc};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) v[k] = q[k] < 1.0e13f ? (unsigned long long)q[k] : 0ull;    // NaN / overflow: ignored
   }
-  out[0] = mode;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], d);
+    if ((threadIdx.x & 31) == 0 && v[k]) atomicAdd(acc + k, v[k]);
+  }
+}
+
+// cand[0] = key mode of the second candidate (1 + dominant normal axis; ties: lowest axis)
+__global__ void k_pick_axis(const unsigned long long *acc, int *cand) {
+  if (threadIdx.x || blockIdx.x) return;
+  int a = 0;
+  if (acc[1] > acc[a]) a = 1;
+  if (acc[2] > acc[a]) a = 2;
+  cand[0] = 1 + a;
+}
+
+// cost[c * SAH_SLOTS + k]: slot sums of candidate c.  Mode 0 (cubic) stays unless another
+// candidate's sample tree (one axis last, cand[0]) is at least 5 % cheaper.
+// out[0] = mode, out[1 + mode] = cost >> 8 of the trees that were built.
+__global__ void k_choose_mode(const unsigned long long *cost, const int *cand, int *out) {
+  if (threadIdx.x || blockIdx.x) return;
+  unsigned long long s0 = 0, s1 = 0;
+  for (int k = 0; k < SAH_SLOTS; ++k) { s0 += cost[k]; s1 += cost[SAH_SLOTS + k]; }
+  const int m = cand[0];
+  for (int c = 1; c < 5; ++c) out[c] = 0;
+  out[1] = (int)min(s0 >> 8, 0x7fffffffull);
+  out[1 + m] = (int)min(s1 >> 8, 0x7fffffffull);
+  out[0] = s1 < s0 - s0 / 20 ? m : 0;
 }
 
 __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t *order, const uint64_t *keys,
@@ -535,11 +568,11 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
 // ---- binned surface-area splits inside clusters ----
 // The radix tree cuts a cell where the Morton curve says, whatever its contents.  Below
 // SAH_CLUSTER_MAX triangles the subtree is rebuilt top-down with the binned surface-area
-// heuristic (16 bins on each axis of the centroid box, cost = area x count of both sides),
+// heuristic (8 bins on each axis of the centroid box, cost = area x count of both sides),
 // which is what the traversal cost actually follows.  One CTA per cluster, everything in
 // shared memory: padded triangle boxes, the slot permutation, per-warp bins and the segment
 // lists of two successive levels.  A level's segments are taken by the CTA's warps; a warp
-// bins its segment, picks the cheapest of the 45 cuts, partitions the slots (stable) and writes
+// bins its segment, picks the cheapest of the 21 cuts, partitions the slots (stable) and writes
 // the node at raw[first slot of the right part - 1], the index the radix tree uses for the same
 // cut position, so the node array stays collision-free and k_live / k_compact run unchanged.
 // Deterministic: node indices and slot order depend on the geometry only.  CPU study of the
@@ -548,27 +581,54 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
 #define RTB_SAH_CLUSTER 1024
 #endif
 constexpr uint32_t SAH_CLUSTER_MAX = RTB_SAH_CLUSTER;
-constexpr int SAH_T = 256, SAH_W = SAH_T / 32;
-constexpr int SAH_BINS = 16, SAH_CUTS = 3 * (SAH_BINS - 1);
-static_assert(SAH_CLUSTER_MAX <= 1024 && LEAF_MAX >= 3, "shared-memory budget of k_sah_clusters");
+// Scenes up to this size are ONE cluster: no sort, no radix tree.  5120 (the <5120, 512> instance,
+// 191 KB of shared memory, one CTA) was measured and is not the default: the build takes 0.5-1.0 ms
+// on one SM and the frames at 3840x2160 are a mixed bag against 1024-triangle clusters under a
+// radix top (car-on-road 18.1 -> 17.3 ms, secret 17.1 -> 15.7, susans 5.00 -> 5.13, spheres 22.3 -> 26.1).
+#ifndef RTB_SAH_WHOLE
+#define RTB_SAH_WHOLE RTB_SAH_CLUSTER
+#endif
+constexpr uint32_t SAH_WHOLE_MAX = RTB_SAH_WHOLE;
+constexpr int SAH_BINS = 8;              // 16 bins: same tree quality within 1 % (tools/tree_quality.cpp), twice the sweep
+static_assert(SAH_WHOLE_MAX >= SAH_CLUSTER_MAX && SAH_WHOLE_MAX < 65536, "cluster-local indices are 16 bits wide");
 constexpr int SAH_MEDIAN_LEVEL = 24;      // deeper segments are halved by position: depth <= 24 + log2(cluster)
 
 struct SahSeg { unsigned short start, count; int parent_side; };   // parent_side = 2 * raw index + side, < 0: scene root
+
+// warp-wide float min / max through the order-preserving integer mapping: one REDUX instruction
+__device__ __forceinline__ float redux_min(float v) { return ord2f(__reduce_min_sync(0xffffffffu, f2ord(v))); }
+__device__ __forceinline__ float redux_max(float v) { return ord2f(__reduce_max_sync(0xffffffffu, f2ord(v))); }
 
 __device__ __forceinline__ int sah_bin(float c, float lo, float scale) {
   const int b = (int)((c - lo) * scale);
   return b < 0 ? 0 : (b > SAH_BINS - 1 ? SAH_BINS - 1 : b);
 }
 
-__global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint32_t *order, const Cluster *clusters,
-                                                        const uint32_t *n_clusters, RawNode *raw, int *root_info,
-                                                        const uint32_t *bounds, float origin_radius) {
-  __shared__ float s_box[6][SAH_CLUSTER_MAX];            // lo.xyz, hi.xyz by local id
-  __shared__ uint32_t s_tri[SAH_CLUSTER_MAX];            // local id -> global triangle id
-  __shared__ unsigned short s_idx[2][SAH_CLUSTER_MAX];   // slot -> local id; [1]: partition scratch
-  __shared__ uint32_t s_bins[SAH_W][3][SAH_BINS][7];     // min xyz, max xyz (ordered uint), count
-  __shared__ SahSeg s_seg[2][SAH_CLUSTER_MAX / (LEAF_MAX + 1) + 1];
-  __shared__ unsigned s_nseg[2];
+// CLMAX: largest cluster, T: threads per CTA.  <SAH_CLUSTER_MAX, 256> (42 KB of shared memory,
+// 5 CTAs per SM) serves the clusters of a radix tree and scenes small enough to be one cluster;
+// <SAH_WHOLE_MAX, 512> exists only when RTB_SAH_WHOLE is raised (A/B builds).
+template <int CLMAX>
+constexpr size_t sah_seg_cap() { return CLMAX / (LEAF_MAX + 1) + 1; }
+template <int CLMAX, int T>
+constexpr size_t sah_smem_bytes() {
+  return (size_t)CLMAX * (6 * 4 + 4 + 2 * 2) + (size_t)(T / 32) * 3 * SAH_BINS * 7 * 4 + 2 * sah_seg_cap<CLMAX>() * sizeof(SahSeg) + 16;
+}
+
+#define BX(k, i) s_box[(k) * CLMAX + (i)]
+template <int CLMAX, int T>
+__global__ void __launch_bounds__(T) k_sah_clusters(const float *raw_v, uint32_t *order, const Cluster *clusters,
+                                                    const uint32_t *n_clusters, RawNode *raw, int *root_info,
+                                                    const uint32_t *bounds, float origin_radius) {
+  constexpr int SAH_T = T, SAH_W = T / 32;
+  constexpr int SEG_CAP = CLMAX / (LEAF_MAX + 1) + 1;      // = sah_seg_cap<CLMAX>()
+  extern __shared__ __align__(16) unsigned char sah_smem[];
+  float *s_box = reinterpret_cast<float *>(sah_smem);                          // [6][CLMAX] lo.xyz, hi.xyz by local id
+  uint32_t *s_tri = reinterpret_cast<uint32_t *>(s_box + 6 * CLMAX);           // local id -> global triangle id
+  uint32_t *s_bins = s_tri + CLMAX;                                            // [warps][3][SAH_BINS][7] min xyz, max xyz (ordered), count
+  SahSeg *s_seg = reinterpret_cast<SahSeg *>(s_bins + SAH_W * 3 * SAH_BINS * 7);   // [2][SEG_CAP]
+  unsigned *s_nseg = reinterpret_cast<unsigned *>(s_seg + 2 * SEG_CAP);        // [2]
+  unsigned short *s_idx0 = reinterpret_cast<unsigned short *>(s_nseg + 2);     // slot -> local id
+  unsigned short *s_idx1 = s_idx0 + CLMAX;                                     // partition scratch
   if (blockIdx.x >= *n_clusters) return;
   const Cluster cl = clusters[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -582,20 +642,20 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
       V3 lo, hi;
       tri_box(raw_v, tri, lo, hi);
       sliver_pad(raw_v, tri, pad_unit, lo, hi);
-      s_box[0][i] = lo.x; s_box[1][i] = lo.y; s_box[2][i] = lo.z;
-      s_box[3][i] = hi.x; s_box[4][i] = hi.y; s_box[5][i] = hi.z;
+      BX(0, i) = lo.x; BX(1, i) = lo.y; BX(2, i) = lo.z;
+      BX(3, i) = hi.x; BX(4, i) = hi.y; BX(5, i) = hi.z;
       s_tri[i] = tri;
-      s_idx[0][i] = (unsigned short)i;
+      s_idx0[i] = (unsigned short)i;
       if (i + 1 < cl.count) raw[cl.start + i].cnt = 0;      // the radix subtree goes away
     }
   }
   if (threadIdx.x == 0) {
-    s_seg[0][0].start = 0; s_seg[0][0].count = (unsigned short)cl.count;
-    s_seg[0][0].parent_side = cl.parent < 0 ? -1 : 2 * cl.parent + cl.side;
+    s_seg[0].start = 0; s_seg[0].count = (unsigned short)cl.count;
+    s_seg[0].parent_side = cl.parent < 0 ? -1 : 2 * cl.parent + cl.side;
     s_nseg[0] = 1; s_nseg[1] = 0;
   }
   int cur = 0, level = 0;
-  uint32_t *bins = &s_bins[warp][0][0][0];
+  uint32_t *bins = s_bins + warp * 3 * SAH_BINS * 7;
   for (;;) {
     __syncthreads();                        // segments pushed by the previous level are complete
     const unsigned n_seg = s_nseg[cur];
@@ -604,31 +664,31 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
     if (threadIdx.x == 0) s_nseg[cur ^ 1] = 0;
     __syncthreads();
     for (unsigned sg = warp; sg < n_seg; sg += SAH_W) {
-      const SahSeg seg = s_seg[cur][sg];
+      const SahSeg seg = s_seg[cur * SEG_CAP + sg];
       const uint32_t st = seg.start, cnt = seg.count;
-      // centroid box
+      // centroid box (warp reductions on order-preserving integers: one REDUX each)
       float cl0 = INF, cl1 = INF, cl2 = INF, ch0 = -INF, ch1 = -INF, ch2 = -INF;
       for (uint32_t i = lane; i < cnt; i += 32) {
-        const int id = s_idx[0][st + i];
-        const float cx = 0.5f * s_box[0][id] + 0.5f * s_box[3][id], cy = 0.5f * s_box[1][id] + 0.5f * s_box[4][id],
-                    cz = 0.5f * s_box[2][id] + 0.5f * s_box[5][id];
+        const int id = s_idx0[st + i];
+        const float cx = 0.5f * BX(0, id) + 0.5f * BX(3, id), cy = 0.5f * BX(1, id) + 0.5f * BX(4, id),
+                    cz = 0.5f * BX(2, id) + 0.5f * BX(5, id);
         cl0 = fminf(cl0, cx); cl1 = fminf(cl1, cy); cl2 = fminf(cl2, cz);
         ch0 = fmaxf(ch0, cx); ch1 = fmaxf(ch1, cy); ch2 = fmaxf(ch2, cz);
       }
-      cl0 = warp_min(cl0); cl1 = warp_min(cl1); cl2 = warp_min(cl2);
-      ch0 = warp_max(ch0); ch1 = warp_max(ch1); ch2 = warp_max(ch2);
+      cl0 = redux_min(cl0); cl1 = redux_min(cl1); cl2 = redux_min(cl2);
+      ch0 = redux_max(ch0); ch1 = redux_max(ch1); ch2 = redux_max(ch2);
       const float clo[3] = {cl0, cl1, cl2};
       float scale[3];
       scale[0] = ch0 > cl0 ? (float)SAH_BINS / (ch0 - cl0) : 0.0f;
       scale[1] = ch1 > cl1 ? (float)SAH_BINS / (ch1 - cl1) : 0.0f;
       scale[2] = ch2 > cl2 ? (float)SAH_BINS / (ch2 - cl2) : 0.0f;
-      int cut = -1;                          // axis * (SAH_BINS - 1) + last bin of the left part; -1: halve by position
+      int cut = -1;                          // axis * SAH_BINS + last bin of the left part; -1: halve by position
       if (level < SAH_MEDIAN_LEVEL && (scale[0] > 0 || scale[1] > 0 || scale[2] > 0)) {
         for (int k = lane; k < 3 * SAH_BINS * 7; k += 32) bins[k] = (k % 7) < 3 ? 0xffffffffu : 0u;
         __syncwarp();
         for (uint32_t i = lane; i < cnt; i += 32) {
-          const int id = s_idx[0][st + i];
-          const float lo[3] = {s_box[0][id], s_box[1][id], s_box[2][id]}, hi[3] = {s_box[3][id], s_box[4][id], s_box[5][id]};
+          const int id = s_idx0[st + i];
+          const float lo[3] = {BX(0, id), BX(1, id), BX(2, id)}, hi[3] = {BX(3, id), BX(4, id), BX(5, id)};
           const uint32_t ol[3] = {f2ord(lo[0]), f2ord(lo[1]), f2ord(lo[2])}, oh[3] = {f2ord(hi[0]), f2ord(hi[1]), f2ord(hi[2])};
 #pragma unroll
           for (int a = 0; a < 3; ++a) {
@@ -640,38 +700,51 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
           }
         }
         __syncwarp();
-        float best = INF;
-        int best_cut = 0x7fffffff;
-        for (int c = lane; c < SAH_CUTS; c += 32) {
-          const int a = c / (SAH_BINS - 1), k = c % (SAH_BINS - 1);
-          V3 llo = mk(INF, INF, INF), lhi = mk(-INF, -INF, -INF), rlo = llo, rhi = lhi;
-          uint32_t nl = 0, nr = 0;
-          for (int b = 0; b < SAH_BINS; ++b) {
-            const uint32_t *q = bins + (a * SAH_BINS + b) * 7;
-            const uint32_t m = q[6];
-            if (!m) continue;
-            const V3 blo = mk(ord2f(q[0]), ord2f(q[1]), ord2f(q[2])), bhi = mk(ord2f(q[3]), ord2f(q[4]), ord2f(q[5]));
-            if (b <= k) { grow(llo, lhi, blo); grow(llo, lhi, bhi); nl += m; }
-            else { grow(rlo, rhi, blo); grow(rlo, rhi, bhi); nr += m; }
+        // sweep: lane = axis * SAH_BINS + bin holds its bin; prefix (left part) and suffix (right
+        // part) unions by shuffles inside the groups of SAH_BINS lanes, all in ordered integers
+        const int bb = lane & (SAH_BINS - 1);
+        uint32_t pl[7], sf[7];
+        {
+          const uint32_t *q = bins + (lane < 3 * SAH_BINS ? lane : 0) * 7;
+          const uint32_t m = lane < 3 * SAH_BINS ? q[6] : 0u;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            pl[k] = m ? q[k] : 0xff800000u;          // f2ord(+inf)
+            pl[3 + k] = m ? q[3 + k] : 0x007fffffu;  // f2ord(-inf)
           }
-          if (nl && nr) {
-            const float cost = box_area(llo, lhi) * (float)nl + box_area(rlo, rhi) * (float)nr;
-            if (cost < best) { best = cost; best_cut = c; }
-          }
+          pl[6] = m;
+#pragma unroll
+          for (int k = 0; k < 7; ++k) sf[k] = pl[k];
         }
 #pragma unroll
-        for (int d = 16; d; d >>= 1) {
-          const float ob = __shfl_xor_sync(0xffffffffu, best, d);
-          const int oc = __shfl_xor_sync(0xffffffffu, best_cut, d);
-          if (ob < best || (ob == best && oc < best_cut)) { best = ob; best_cut = oc; }
+        for (int d = 1; d < SAH_BINS; d <<= 1) {
+#pragma unroll
+          for (int k = 0; k < 7; ++k) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, pl[k], d, SAH_BINS);
+            const uint32_t dn = __shfl_down_sync(0xffffffffu, sf[k], d, SAH_BINS);
+            if (bb >= d) pl[k] = k < 3 ? min(pl[k], up) : (k < 6 ? max(pl[k], up) : pl[k] + up);
+            if (bb + d < SAH_BINS) sf[k] = k < 3 ? min(sf[k], dn) : (k < 6 ? max(sf[k], dn) : sf[k] + dn);
+          }
         }
-        if (best < INF) cut = best_cut;
+        uint32_t rt[7];                      // right part of the cut after bin bb: suffix of the next lane
+#pragma unroll
+        for (int k = 0; k < 7; ++k) rt[k] = __shfl_down_sync(0xffffffffu, sf[k], 1, SAH_BINS);
+        uint32_t key = 0xffffffffu;
+        if (lane < 3 * SAH_BINS && bb < SAH_BINS - 1 && pl[6] && rt[6]) {
+          const float cost =
+              box_area(mk(ord2f(pl[0]), ord2f(pl[1]), ord2f(pl[2])), mk(ord2f(pl[3]), ord2f(pl[4]), ord2f(pl[5]))) * (float)pl[6] +
+              box_area(mk(ord2f(rt[0]), ord2f(rt[1]), ord2f(rt[2])), mk(ord2f(rt[3]), ord2f(rt[4]), ord2f(rt[5]))) * (float)rt[6];
+          // costs are >= 0, so their bit patterns order like integers; the low 5 bits carry the lane
+          if (cost >= 0.0f && cost < INF) key = (__float_as_uint(cost) & ~31u) | (uint32_t)lane;
+        }
+        key = __reduce_min_sync(0xffffffffu, key);
+        if (key != 0xffffffffu) cut = (int)(key & 31u);
       }
       // stable partition of the segment's slots: left part first
       uint32_t nleft = 0;
       V3 llo, lhi, rlo, rhi;
       for (int attempt = 0; attempt < 2; ++attempt) {
-        const int axis = cut < 0 ? 0 : cut / (SAH_BINS - 1), kbin = cut < 0 ? 0 : cut % (SAH_BINS - 1);
+        const int axis = cut < 0 ? 0 : cut / SAH_BINS, kbin = cut < 0 ? 0 : cut % SAH_BINS;
         llo = mk(INF, INF, INF); lhi = mk(-INF, -INF, -INF); rlo = llo; rhi = lhi;
         uint32_t run = 0;
         for (int side = 0; side < 2; ++side) {
@@ -680,16 +753,16 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
             bool take = false;
             int id = 0;
             if (i < cnt) {
-              id = s_idx[0][st + i];
+              id = s_idx0[st + i];
               bool left;
               if (cut < 0) left = i < cnt / 2;
-              else left = sah_bin(0.5f * s_box[axis][id] + 0.5f * s_box[3 + axis][id], clo[axis], scale[axis]) <= kbin;
+              else left = sah_bin(0.5f * BX(axis, id) + 0.5f * BX(3 + axis, id), clo[axis], scale[axis]) <= kbin;
               take = left == (side == 0);
             }
             const unsigned m = __ballot_sync(0xffffffffu, take);
             if (take) {
-              s_idx[1][st + run + __popc(m & ((1u << lane) - 1u))] = (unsigned short)id;
-              const V3 blo = mk(s_box[0][id], s_box[1][id], s_box[2][id]), bhi = mk(s_box[3][id], s_box[4][id], s_box[5][id]);
+              s_idx1[st + run + __popc(m & ((1u << lane) - 1u))] = (unsigned short)id;
+              const V3 blo = mk(BX(0, id), BX(1, id), BX(2, id)), bhi = mk(BX(3, id), BX(4, id), BX(5, id));
               if (side == 0) { grow(llo, lhi, blo); grow(llo, lhi, bhi); }
               else { grow(rlo, rhi, blo); grow(rlo, rhi, bhi); }
             }
@@ -701,9 +774,9 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
         cut = -1;                            // cannot happen for a cut with both sides non-empty; be safe
       }
       __syncwarp();
-      for (uint32_t i = lane; i < cnt; i += 32) s_idx[0][st + i] = s_idx[1][st + i];
-      llo = mk(warp_min(llo.x), warp_min(llo.y), warp_min(llo.z)); lhi = mk(warp_max(lhi.x), warp_max(lhi.y), warp_max(lhi.z));
-      rlo = mk(warp_min(rlo.x), warp_min(rlo.y), warp_min(rlo.z)); rhi = mk(warp_max(rhi.x), warp_max(rhi.y), warp_max(rhi.z));
+      for (uint32_t i = lane; i < cnt; i += 32) s_idx0[st + i] = s_idx1[st + i];
+      llo = mk(redux_min(llo.x), redux_min(llo.y), redux_min(llo.z)); lhi = mk(redux_max(lhi.x), redux_max(lhi.y), redux_max(lhi.z));
+      rlo = mk(redux_min(rlo.x), redux_min(rlo.y), redux_min(rlo.z)); rhi = mk(redux_max(rhi.x), redux_max(rhi.y), redux_max(rhi.z));
       if (lane == 0) {
         const uint32_t first = cl.start + st, nright = cnt - nleft;
         const int p = (int)(first + nleft - 1);
@@ -717,11 +790,11 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
         if (seg.parent_side >= 0) (&raw[seg.parent_side >> 1].ref0)[seg.parent_side & 1] = p;
         else root_info[0] = p;
         if (nleft > (uint32_t)LEAF_MAX) {
-          SahSeg &c = s_seg[cur ^ 1][atomicAdd(&s_nseg[cur ^ 1], 1u)];
+          SahSeg &c = s_seg[(cur ^ 1) * SEG_CAP + atomicAdd(&s_nseg[cur ^ 1], 1u)];
           c.start = (unsigned short)st; c.count = (unsigned short)nleft; c.parent_side = 2 * p;
         }
         if (nright > (uint32_t)LEAF_MAX) {
-          SahSeg &c = s_seg[cur ^ 1][atomicAdd(&s_nseg[cur ^ 1], 1u)];
+          SahSeg &c = s_seg[(cur ^ 1) * SEG_CAP + atomicAdd(&s_nseg[cur ^ 1], 1u)];
           c.start = (unsigned short)(st + nleft); c.count = (unsigned short)nright; c.parent_side = 2 * p + 1;
         }
       }
@@ -730,9 +803,10 @@ __global__ void __launch_bounds__(SAH_T) k_sah_clusters(const float *raw_v, uint
     cur ^= 1;
     ++level;
   }
-  for (uint32_t i = threadIdx.x; i < cl.count; i += SAH_T) order[cl.start + i] = s_tri[s_idx[0][i]];
+  for (uint32_t i = threadIdx.x; i < cl.count; i += SAH_T) order[cl.start + i] = s_tri[s_idx0[i]];
   if (threadIdx.x == 0) atomicMax(root_info + 2, level);
 }
+#undef BX
 
 #if !RTB_BVH4
 // live[j] = 1 when raw node j survives (its range is larger than a leaf)
@@ -1082,9 +1156,10 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
 #if RTB_BVH4
   const uint32_t cl_max = 0;                    // the 4-wide A/B layout keeps the plain radix tree
 #else
-  const uint32_t cl_max = (flags & RTB_BUILD_RADIX_ONLY) ? 0u : SAH_CLUSTER_MAX;
+  const uint32_t cl_max =
+      (flags & RTB_BUILD_RADIX_ONLY) || ((flags & RTB_BUILD_ONE_FRAME) && n > ONE_FRAME_SAH_MAX) ? 0u : SAH_CLUSTER_MAX;
 #endif
-  const bool sah_only = tree && cl_max && n <= cl_max;      // the whole scene is one cluster: no sort, no radix tree
+  const bool sah_only = tree && cl_max && n <= SAH_WHOLE_MAX;    // the whole scene is one cluster: no sort, no radix tree
   Cluster *d_clusters = nullptr;
   uint32_t *d_n_clusters = nullptr;
   const uint32_t clusters_cap = cl_max ? 2u * (n / cl_max) + 2u : 1u;   // sibling clusters hold > cl_max triangles together
@@ -1105,17 +1180,23 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     uint32_t *vals_b = nullptr, *scratch = nullptr;
     const size_t sw = radix_sort_scratch_words(n);
     CK(tmp.alloc(&keys_a, n)); CK(tmp.alloc(&keys_b, n)); CK(tmp.alloc(&vals_b, n)); CK(tmp.alloc(&scratch, sw));
-    // ---- key mode: surface-area cost of the four candidate trees over a strided sample ----
+    // ---- key mode: surface-area cost of two candidate trees over a strided sample: cubic keys,
+    //      and the axis the surface is most perpendicular to last ----
     const bool choose = n >= MODE_CHOICE_MIN && !(flags & RTB_BUILD_CUBIC_KEYS);
     if (choose) {
       const uint32_t stride = (n + MODE_SAMPLE_MAX - 1) / MODE_SAMPLE_MAX;
       const uint32_t m = (n + stride - 1) / stride;
-      unsigned long long *d_cost = nullptr;
-      CK(tmp.alloc(&d_cost, 4 * SAH_SLOTS));
-      RTB_CUDA(cudaMemsetAsync(d_cost, 0, 4 * SAH_SLOTS * sizeof(unsigned long long), st));
+      unsigned long long *d_cost = nullptr;     // [2][SAH_SLOTS] tree costs, then [3] normal statistic
+      int *d_cand = nullptr;
+      CK(tmp.alloc(&d_cost, 2 * SAH_SLOTS + 3));
+      CK(tmp.alloc(&d_cand, 1));
+      RTB_CUDA(cudaMemsetAsync(d_cost, 0, (2 * SAH_SLOTS + 3) * sizeof(unsigned long long), st));
       const unsigned gM = (m + BT - 1) / BT;
-      for (int c = 0; c < 4; ++c) {
-        k_morton<<<gM, BT, 0, st>>>(raw_v, m, stride, d_bounds, c, nullptr, keys_a, S->order);
+      k_normal_stat<<<gM, BT, 0, st>>>(raw_v, m, stride, d_bounds, d_cost + 2 * SAH_SLOTS);
+      k_pick_axis<<<1, 32, 0, st>>>(d_cost + 2 * SAH_SLOTS, d_cand);
+      launches += 2;
+      for (int c = 0; c < 2; ++c) {
+        k_morton<<<gM, BT, 0, st>>>(raw_v, m, stride, d_bounds, 0, c ? d_cand : nullptr, keys_a, S->order);
         int in_alt = 0;
         CK(dev_radix_sort_pairs_u64(keys_a, S->order, keys_b, vals_b, m, MORTON_BITS, scratch, sw, st, &in_alt, &launches));
         RTB_CUDA(cudaMemsetAsync(visit, 0xff, 4ull * (m - 1), st));
@@ -1124,7 +1205,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
                                   nullptr, 0u);
         launches += 2;
       }
-      k_choose_mode<<<1, 32, 0, st>>>(d_cost, 4, d_mode);
+      k_choose_mode<<<1, 32, 0, st>>>(d_cost, d_cand, d_mode);
       ++launches;
     }
     k_morton<<<gN, BT, 0, st>>>(raw_v, n, 1, d_bounds, 0, d_mode, keys_a, S->order);
@@ -1166,8 +1247,19 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
       ++launches;
     }
     if (cl_max) {
-      k_sah_clusters<<<sah_only ? 1u : clusters_cap, SAH_T, 0, st>>>(raw_v, S->order, d_clusters, d_n_clusters, raw,
-                                                                    root_info, d_bounds, S->origin_radius);
+      if (sah_only && n > SAH_CLUSTER_MAX) {
+        constexpr size_t smem = sah_smem_bytes<(int)SAH_WHOLE_MAX, 512>();
+        static_assert(smem <= 227 * 1024, "shared memory of the whole-scene instance");
+        auto kern = k_sah_clusters<(int)SAH_WHOLE_MAX, 512>;
+        RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<1, 512, smem, st>>>(raw_v, S->order, d_clusters, d_n_clusters, raw, root_info, d_bounds, S->origin_radius);
+      } else {
+        constexpr size_t smem = sah_smem_bytes<(int)SAH_CLUSTER_MAX, 256>();
+        static_assert(smem <= 48 * 1024, "shared memory of the cluster instance");
+        k_sah_clusters<(int)SAH_CLUSTER_MAX, 256><<<sah_only ? 1u : clusters_cap, 256, smem, st>>>(
+            raw_v, S->order, d_clusters, d_n_clusters, raw, root_info, d_bounds, S->origin_radius);
+      }
+      RTB_CUDA(cudaGetLastError());
       ++launches;
       S->builder = 1;
     }

@@ -125,7 +125,7 @@ __device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
 }
 
 // USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound)
-template <bool USE_TMAX = true>
+template <bool USE_TMAX = true, int OCT = -1>
 __device__ __forceinline__ bool slab_hit(const Slabs &s, float cx, float hx, float cy, float hy, float cz,
                                          float hz, float tmax, float &tn) {
   const float x0 = __fmaf_rn(-hx, s.ax, __fmaf_rn(cx, s.ix, s.nx)), x1 = __fmaf_rn(hx, s.ax, __fmaf_rn(cx, s.ix, s.fx));
@@ -146,16 +146,28 @@ __device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
   return s;
 }
 
-// USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound)
-template <bool USE_TMAX = true>
+// USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound).
+// OCT >= 0: the signs of the direction are known at compile time (bit a set: axis a negative),
+// so the entry plane of every slab is known and the six per-axis min / max disappear:
+// 6 FFMA + 2 FMNMX3 + 1-2 FMNMX per box instead of 6 FFMA + 6 FMNMX + 2 FMNMX3 + 1-2 FMNMX.
+template <bool USE_TMAX = true, int OCT = -1>
 __device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, float loy, float hiy, float loz,
                                          float hiz, float tmax, float &tn) {
   const float x0 = __fmaf_rn(lox, s.ix, -s.ax), x1 = __fmaf_rn(hix, s.ix, -s.bx);
   const float y0 = __fmaf_rn(loy, s.iy, -s.ay), y1 = __fmaf_rn(hiy, s.iy, -s.by);
   const float z0 = __fmaf_rn(loz, s.iz, -s.az), z1 = __fmaf_rn(hiz, s.iz, -s.bz);
-  tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-  const float tf = USE_TMAX ? fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax))
-                            : fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fmaxf(z0, z1));
+  float nx, fx, ny, fy, nz, fz;
+  if (OCT < 0) {
+    nx = fminf(x0, x1); fx = fmaxf(x0, x1);
+    ny = fminf(y0, y1); fy = fmaxf(y0, y1);
+    nz = fminf(z0, z1); fz = fmaxf(z0, z1);
+  } else {
+    nx = (OCT & 1) ? x1 : x0; fx = (OCT & 1) ? x0 : x1;
+    ny = (OCT & 2) ? y1 : y0; fy = (OCT & 2) ? y0 : y1;
+    nz = (OCT & 4) ? z1 : z0; fz = (OCT & 4) ? z0 : z1;
+  }
+  tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
+  const float tf = USE_TMAX ? fminf(fminf(fx, fy), fminf(fz, tmax)) : fminf(fminf(fx, fy), fz);
   return tn <= tf;
 }
 #endif
@@ -247,12 +259,10 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
 // warp in the same code at the same time; with a single if-inner-else-leaf loop the triangle
 // code ran at 7.5 of 32 lanes (profiles/r1_ncu_frame_v1.txt).  History on C5: if-else 53.9 ms,
 // plain while-while 47.4, speculative 44.5, one pop per step 40.5.
-template <bool ANY, bool COUNT>
-__device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
+template <bool ANY, bool COUNT, int OCT = -1>
+__device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, const Slabs &sl, float eps, Best &best,
+                           Counters &c) {
   best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
-  const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
-  const float eps = sc.margin_k * 1.1920929e-7f * amax;
-  const Slabs sl = make_slabs(o, d, eps);
   // distance -> ray parameter, rounded up
   const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
   float tmax = INF;
@@ -268,8 +278,8 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
       const float4 *np = sc.nodes + 4ll * cur;
       const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
       float tn0, tn1;
-      const bool h0 = slab_hit<!ANY>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
-      const bool h1 = slab_hit<!ANY>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
+      const bool h0 = slab_hit<!ANY, OCT>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
+      const bool h1 = slab_hit<!ANY, OCT>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
       const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
       int next = h0 ? r0 : (h1 ? r1 : NONE);
       if (h0 && h1) {
@@ -305,10 +315,38 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
 }
 #endif   // RTB_BVH4
 
+// RTB_OCTANT=1: one copy of the traversal per direction octant (slab_hit<.., OCT>).  The rays of
+// a warp nearly always share their octant, so the switch does not diverge.
+#ifndef RTB_OCTANT
+#define RTB_OCTANT 0
+#endif
 template <int TRACER, bool ANY, bool COUNT>
 __device__ __forceinline__ bool trace(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
   if (TRACER == RTB_TRACER_BRUTE) return trace_brute<ANY, COUNT>(sc, o, d, best, c);
+#if RTB_BVH4
   return trace_tree<ANY, COUNT>(sc, o, d, best, c);
+#else
+  const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
+  const float eps = sc.margin_k * 1.1920929e-7f * amax;
+  const Slabs sl = make_slabs(o, d, eps);
+#if RTB_OCTANT && !RTB_NODE_CH
+  // the sign of 1/d as safe_rcp computes it (-0 counts as negative)
+  const int oct = (int)(__float_as_uint(sl.ix) >> 31) | (int)((__float_as_uint(sl.iy) >> 31) << 1) |
+                  (int)((__float_as_uint(sl.iz) >> 31) << 2);
+  switch (oct) {
+    case 0: return trace_tree<ANY, COUNT, 0>(sc, o, d, sl, eps, best, c);
+    case 1: return trace_tree<ANY, COUNT, 1>(sc, o, d, sl, eps, best, c);
+    case 2: return trace_tree<ANY, COUNT, 2>(sc, o, d, sl, eps, best, c);
+    case 3: return trace_tree<ANY, COUNT, 3>(sc, o, d, sl, eps, best, c);
+    case 4: return trace_tree<ANY, COUNT, 4>(sc, o, d, sl, eps, best, c);
+    case 5: return trace_tree<ANY, COUNT, 5>(sc, o, d, sl, eps, best, c);
+    case 6: return trace_tree<ANY, COUNT, 6>(sc, o, d, sl, eps, best, c);
+    default: return trace_tree<ANY, COUNT, 7>(sc, o, d, sl, eps, best, c);
+  }
+#else
+  return trace_tree<ANY, COUNT>(sc, o, d, sl, eps, best, c);
+#endif
+#endif
 }
 
 // gpu/light.cu:12-27

@@ -186,7 +186,7 @@ static int sah_build(Tree &t, uint32_t l, uint32_t r, Box &out, int depth, int &
   }
   out = nb;
   if (cnt <= (uint32_t)LEAF_MAX) return leaf_ref(l, cnt);
-  constexpr int NB = 16;
+  const int NB = getenv("NB") ? atoi(getenv("NB")) : 16;
   float best_cost = INFINITY; int best_axis = -1, best_bin = 0;
   const bool skip_bins = cnt <= g_small;
   int longest = 0;
@@ -196,7 +196,7 @@ static int sah_build(Tree &t, uint32_t l, uint32_t r, Box &out, int depth, int &
     if (g_axes == 1 && ax != longest) continue;
     const float lo = (&cb.lo.x)[ax], hi = (&cb.hi.x)[ax];
     if (!(hi > lo)) continue;
-    Box bb[NB]; uint32_t bc[NB];
+    Box bb[64]; uint32_t bc[64];
     for (int k = 0; k < NB; ++k) { bb[k] = empty_box(); bc[k] = 0; }
     const float sc = NB / (hi - lo);
     for (uint32_t s = l; s <= r; ++s) {
@@ -205,7 +205,7 @@ static int sah_build(Tree &t, uint32_t l, uint32_t r, Box &out, int depth, int &
       int k = (int)((c - lo) * sc); if (k >= NB) k = NB - 1; if (k < 0) k = 0;
       bb[k] = merge(bb[k], b); ++bc[k];
     }
-    float ra[NB]; uint32_t rc[NB];
+    float ra[64]; uint32_t rc[64];
     Box acc = empty_box(); uint32_t n = 0;
     for (int k = NB - 1; k > 0; --k) { acc = merge(acc, bb[k]); n += bc[k]; ra[k] = n ? area(acc) : 0; rc[k] = n; }
     acc = empty_box(); n = 0;
