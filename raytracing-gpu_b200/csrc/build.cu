@@ -834,16 +834,28 @@ __device__ __forceinline__ float4 to_centre_half(float4 q) {
 #endif
 
 // new_index = exclusive scan of live.  stats: [0] leaves, [1] max leaf size
+// node_up / slot_up: the upward links of rtb_internal.h (the root's own entry is set by the host)
 __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
-                                                float4 *nodes, unsigned int *stats) {
+                                                float4 *nodes, unsigned int *stats, uint32_t *node_up, uint32_t *slot_up) {
   const uint32_t j = blockIdx.x * BT + threadIdx.x;
   if (j >= n_inner) return;
   RawNode nd = raw[j];
   if (nd.cnt <= LEAF_MAX) return;
   unsigned leaves = 0, maxleaf = 0;
-  if (nd.ref0 >= 0) nd.ref0 = (int)new_index[nd.ref0]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref0 & 7)); }
-  if (nd.ref1 >= 0) nd.ref1 = (int)new_index[nd.ref1]; else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~nd.ref1 & 7)); }
-  float4 *dst = nodes + 4ull * new_index[j];
+  const uint32_t me = new_index[j];
+#pragma unroll
+  for (int side = 0; side < 2; ++side) {
+    int &ref = side ? nd.ref1 : nd.ref0;
+    if (ref >= 0) {
+      ref = (int)new_index[ref];
+      if (node_up) node_up[ref] = 2u * me + (uint32_t)side;
+    } else {
+      const uint32_t packed = (uint32_t)~ref, first = packed >> 3, c = packed & 7u;
+      ++leaves; maxleaf = max(maxleaf, c);
+      if (slot_up) for (uint32_t k = 0; k < c; ++k) slot_up[first + k] = 2u * me + (uint32_t)side;
+    }
+  }
+  float4 *dst = nodes + 4ull * me;
 #if RTB_NODE_CH
   dst[0] = to_centre_half(nd.q0);
   dst[1] = to_centre_half(nd.q1);
@@ -982,10 +994,10 @@ SceneStore::~SceneStore() { release(); }
 // Stream, events and frame buffers go back to a per-device cache (recycle_frame_ctx).
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, d_sched};
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, d_sched};
   for (void *p : ptrs) if (p) cudaFreeAsync(p, stream);
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
-  order = nullptr;
+  order = nullptr; up = nullptr;
   d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);
   recycle_frame_ctx(*this);
@@ -1301,7 +1313,11 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
 #if RTB_BVH4
     k_compact4<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, keep, S->nodes, d_stats);
 #else
-    k_compact<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, S->nodes, d_stats);
+#if RTB_SHADOW_UP
+    CK(dev_alloc(&S->up, (size_t)n_live + n));
+#endif
+    k_compact<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, S->nodes, d_stats, S->up,
+                                                      S->up ? S->up + n_live : nullptr);
 #endif
     ++launches;
     uint32_t new_root = 0;
@@ -1309,6 +1325,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     RTB_CUDA(cudaMemcpyAsync(&new_root, live + h_root[0], 4, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaMemcpyAsync(h_stats, d_stats, 8, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
+    if (S->up) RTB_CUDA(cudaMemsetAsync(S->up + new_root, 0xff, 4, st));      // the root has no parent
     S->n_nodes = n_live; S->root = (int)new_root; S->height = height;
     S->n_leaves = h_stats[0]; S->max_leaf = h_stats[1];
   } else {

@@ -58,6 +58,11 @@ constexpr int NODE_QUADS = 4;
 constexpr int STACK_MAX = HEIGHT_MAX;
 #endif
 constexpr int MORTON_BITS = 63;      // 21 bits per axis
+// A/B option: shadow rays climb from the leaf they start on (trace.cu trace_up_any); needs the
+// upward links of DevScene.  Slower than the walk from the root on every scene measured.
+#ifndef RTB_SHADOW_UP
+#define RTB_SHADOW_UP 0
+#endif
 
 struct DevScene {
   // triangles in leaf (Morton) order, three float4 streams (SoA):
@@ -68,6 +73,10 @@ struct DevScene {
   // unit vertex normals (normalize() applied once at build: gpu/hit.cu:15-17), same order
   const float4 *n0, *n1, *n2;
   const float4 *nodes;      // 4 float4 per node
+  // upward links (binary layout only, else nullptr): node_up[k] = 2 * parent + (which child k is),
+  // 0xffffffff for the root; slot_up[s] = the same for the leaf that holds triangle slot s.
+  // Rays that start ON a triangle (shadow rays) climb from its leaf instead of descending from the root.
+  const uint32_t *node_up, *slot_up;
   int root;                 // index of the root node
   uint32_t n_tris;
   uint32_t n_objects, n_lights;

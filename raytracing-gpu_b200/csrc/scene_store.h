@@ -14,6 +14,7 @@ struct SceneStore {
   float4 *v0 = nullptr, *e1 = nullptr, *e2 = nullptr, *n0 = nullptr, *n1 = nullptr, *n2 = nullptr;
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
   uint32_t *order = nullptr;            // slot -> global triangle id
+  uint32_t *up = nullptr;               // [n_nodes] parent links, then [n_tris] slot -> leaf position (rtb_internal.h)
   uint32_t n_tris = 0, n_objects = 0, n_lights = 0;
   uint32_t n_nodes = 0, n_leaves = 0, max_leaf = 0;
   int root = 0, height = 0;
@@ -53,7 +54,7 @@ struct SceneStore {
   DevScene dev() const {
     DevScene d;
     d.v0 = v0; d.e1 = e1; d.e2 = e2; d.n0 = n0; d.n1 = n1; d.n2 = n2;
-    d.nodes = nodes; d.root = root; d.n_tris = n_tris; d.n_objects = n_objects; d.n_lights = n_lights;
+    d.nodes = nodes; d.node_up = up; d.slot_up = up ? up + n_nodes : nullptr; d.root = root; d.n_tris = n_tris; d.n_objects = n_objects; d.n_lights = n_lights;
     d.materials = materials; d.lights = lights; d.abs_max = abs_max; d.margin_k = get_margin_k();
     return d;
   }
