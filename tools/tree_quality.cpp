@@ -483,7 +483,7 @@ int main(int argc, char **argv) {
     const double L = W3 / (2 * std::tan(sc.camera.fov * M_PI / 360));
     const double pm = std::max((double)std::max(std::fabs(sc.camera.position.x), std::fabs(sc.camera.position.y)), (double)std::fabs(sc.camera.position.z));
     const float R = 2.0f * (float)(pm + std::fabs(L) + 0.5 * (W3 + H3));
-    const float pad_unit = 3.0f * 1.1920929e-7f * (g_absmax + R);
+    const float pad_unit = (getenv("PADSCALE") ? (float)atof(getenv("PADSCALE")) : 1.0f) * 3.0f * 1.1920929e-7f * (g_absmax + R);
     uint32_t padded = 0; double grow_sum = 0;
     for (uint32_t i = 0; i < g_n; ++i) {
       Box b = g_tb[i];
