@@ -109,7 +109,8 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
 
 /* ---- persistent scene: replaces to_cuda() (gpu/scene.cu:224-352) and the whole
  *      create_octree() host pipeline (gpu/partitioning/octree.cu:362-411):
- *      upload, triangle bounds, Morton codes, radix sort, node emit. ---- */
+ *      upload, triangle bounds, sort keys (layout chosen per scene), radix sort, node emit,
+ *      clusters rebuilt with surface-area splits. ---- */
 
 typedef struct rtb_scene_handle rtb_scene_t;
 
@@ -119,8 +120,8 @@ typedef struct rtb_scene_handle rtb_scene_t;
 #define RTB_BUILD_CUBIC_KEYS  2u   /* keep the x,y,z-interleaved sort keys: no choice between key layouts */
 #define RTB_BUILD_RADIX_ONLY  4u   /* plain Morton radix tree: no surface-area rebuild of the clusters */
 #define RTB_BUILD_ONE_FRAME   8u   /* the scene will be rendered once (rtb_render passes this): scenes of more
-                                      than 2^18 triangles keep the radix tree, whose build is 3 ms shorter on
-                                      10 M triangles than the 1.3 ms the better clusters save per 4K frame */
+                                      than 2^18 triangles keep the radix tree; rebuilding the clusters of
+                                      10 M triangles takes 6 ms and saves 1.3 ms per 4K frame */
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
                      rtb_scene_t **out);
@@ -138,6 +139,14 @@ int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam);
 #define RTB_KERNEL_PER_SAMPLE  0
 #define RTB_KERNEL_WAVEFRONT   1
 
+/* Primary rays all pass through the camera position, so their candidates per triangle are a
+ * screen rectangle: the projected culling box.  RASTER tests exactly those (same per-ray test,
+ * same winner as the tree walk) and falls back to the tree by itself when a box straddles the
+ * camera plane too often or the rectangles cover too much; AUTO = RASTER from 2^15 triangles. */
+#define RTB_PRIMARY_AUTO    0
+#define RTB_PRIMARY_TREE    1
+#define RTB_PRIMARY_RASTER  2
+
 typedef struct rtb_frame_opts {
   int aliasing;        /* SSAA factor, 3 in gpu/rt.cpp:67 */
   int tracer;          /* RTB_TRACER_* */
@@ -147,7 +156,8 @@ typedef struct rtb_frame_opts {
   int frame_kernel;    /* RTB_KERNEL_*: 0 = persistent-warp per-sample kernel (default, fastest measured);
                           1 = staged wavefront kernel with in-warp ray queues (tree tracer, <= 32
                           shadow-casting lights, aliasing <= 6; same bytes out) */
-  int reserved[2];
+  int primary;         /* RTB_PRIMARY_*: how the first ray of every sample finds its triangle */
+  int reserved;
 } rtb_frame_opts;
 
 /* Render into a HOST buffer (H2D nothing, D2H the frame): timed e2e path. */
@@ -196,6 +206,12 @@ typedef struct rtb_stats {
 } rtb_stats;
 
 int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);
+
+/* State the projection pass of the last frame (or hit-id query) left: out[0] rectangle items,
+ * out[1] != 0: it gave up (too many items or boxes across the camera plane), out[2] | out[3] << 32
+ * rectangle area in samples (the frame also walks the tree when this exceeds 8 x its samples),
+ * out[4] boxes across the camera plane.  All zero when no projection pass ran. */
+int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]);
 
 /* ---- build-pipeline primitives on HOST arrays (upload, run the device kernel,
  *      download) so the reference's own known-answer vectors can be replayed:

@@ -77,6 +77,8 @@ static DevCamera camera_frame(const struct camera &cam) {
   d.C = make_float3(cam.position.x + L * w.x, cam.position.y + L * w.y, cam.position.z + L * w.z);
   d.W = cam.width;
   d.H = cam.height;
+  d.w = make_float3(w.x, w.y, w.z);
+  d.L = L;
   return d;
 }
 
@@ -107,6 +109,46 @@ static int check_frame(const SceneStore &S, const rtb_frame_opts *o, int out_h, 
 
 static bool g_schedule = true;   // rtb_set_schedule (tests, A/B)
 
+constexpr uint32_t RASTER_AUTO_MIN_TRIS = 1u << 15;
+
+// Buffers of the projection pass, owned by the scene handle (stream-ordered pool: a one-shot
+// render gets them in microseconds), and the box inflation of this frame.
+static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st) {
+  const size_t samples = (size_t)fa.cam.W * fa.cam.H;
+  if (S.d_prim_count < samples) {
+    if (S.d_prim) cudaFreeAsync(S.d_prim, st);
+    S.d_prim = nullptr; S.d_prim_count = 0;
+    RTB_CUDA(cudaMallocAsync((void **)&S.d_prim, samples * 8, st));
+    S.d_prim_count = samples;
+  }
+  const size_t cap = 2 * (size_t)S.n_tris + (4u << 20);
+  if (S.d_rast_cap < cap) {
+    if (S.d_rast_items) cudaFreeAsync(S.d_rast_items, st);
+    S.d_rast_items = nullptr; S.d_rast_cap = 0;
+    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, cap * sizeof(uint4), st));
+    S.d_rast_cap = cap;
+  }
+  if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, RAST_STATE_WORDS * 4, st));
+  // largest |coordinate| of a primary-ray origin: the four corners of the sample grid
+  float omax = 0;
+  for (int k = 0; k < 4; ++k) {
+    const float fx = (float)(((k & 1) ? fa.cam.W - 1 : 0) - fa.cam.W / 2), fy = (float)(((k & 2) ? fa.cam.H - 1 : 0) - fa.cam.H / 2);
+    const float ox = fa.cam.C.x + fa.cam.u.x * fx + fa.cam.v.x * fy, oy = fa.cam.C.y + fa.cam.u.y * fx + fa.cam.v.y * fy,
+                oz = fa.cam.C.z + fa.cam.u.z * fx + fa.cam.v.z * fy;
+    omax = fmaxf(omax, fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))));
+  }
+  // the ray-time margin of trace_tree at that origin, two more float spacings for vertex0 + edge
+  fa.rast_eps = (get_margin_k() + 2.0f) * 1.1920929e-7f * (omax * 1.001f + S.abs_max);
+  // a tree walk costs about 3 000 instructions per sample, a rectangle sample about 100
+  static const unsigned area_factor = [] { const char *e = getenv("RTB_RASTER_AREA"); return e && atoi(e) > 0 ? (unsigned)atoi(e) : 20u; }();
+  fa.rast_area_factor = area_factor;
+  fa.prim = S.d_prim;
+  fa.rast_items = S.d_rast_items;
+  fa.rast_cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
+  fa.rast = S.d_rast;
+  return RTB_OK;
+}
+
 static int ensure_frame_resources(SceneStore &S) {
   if (!S.d_tile_counter) RTB_CUDA(cudaMalloc((void **)&S.d_tile_counter, sizeof(unsigned int)));
   if (!S.d_counters) RTB_CUDA(cudaMalloc((void **)&S.d_counters, 8 * sizeof(unsigned long long)));
@@ -133,6 +175,15 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
+  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_eps = 0; fa.rast_area_factor = 0;
+  // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
+  // The frame falls back to the tree by itself when the projection does not pay or is not defined.
+  const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
+  if (!RTB_BVH4 && want_raster && S.has_tree && S.inv_order && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
+      o.frame_kernel == RTB_KERNEL_PER_SAMPLE) {
+    rc = ensure_raster_resources(S, fa, st);
+    if (rc) return rc;
+  }
   if (!RTB_BVH4 && o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
       S.n_lights <= 255) {
     const size_t need = wave_scratch_floats(o.aliasing, S.sm_count);
@@ -510,7 +561,17 @@ int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_o
     cudaFree(d_tri);
     return cuda_fail(cudaGetLastError(), "cudaMalloc(obj ids)", __FILE__, __LINE__);
   }
-  rc = launch_hit_ids(S.dev(), camera_frame(S.camera), o.tracer, d_tri, d_obj, S.stream);
+  // opts->primary == RTB_PRIMARY_RASTER: the ids the projection pass records (tests); a frame that
+  // falls back to the tree reports -2 everywhere so that a test cannot pass by accident
+  if (o.primary == RTB_PRIMARY_RASTER && o.tracer == RTB_TRACER_TREE && S.has_tree && S.inv_order) {
+    FrameArgs fa;
+    memset(&fa, 0, sizeof fa);
+    fa.cam = camera_frame(S.camera);
+    fa.aliasing = o.aliasing; fa.out_w = out_w; fa.out_h = out_h; fa.rank = 0; fa.nranks = 1;
+    rc = ensure_raster_resources(S, fa, S.stream);
+    if (!rc) rc = launch_prim_ids(S.dev(), fa, d_tri, d_obj, S.stream);
+  } else
+    rc = launch_hit_ids(S.dev(), camera_frame(S.camera), o.tracer, d_tri, d_obj, S.stream);
   cudaError_t e = cudaSuccess;
   if (!rc) {
     e = cudaMemcpyAsync(tri_out, d_tri, n * 4, cudaMemcpyDeviceToHost, S.stream);
@@ -574,6 +635,17 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
       out->mode_cost |= rel << (16 * (k - 1));
     }
   out->builder = (uint64_t)S.builder;
+  return RTB_OK;
+}
+
+int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]) {
+  if (!h || !out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  memset(out, 0, 8 * sizeof(unsigned));
+  if (!S.d_rast) return RTB_OK;
+  RTB_CUDA(cudaSetDevice(S.device));
+  RTB_CUDA(cudaMemcpyAsync(out, S.d_rast, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, S.stream));
+  RTB_CUDA(cudaStreamSynchronize(S.stream));
   return RTB_OK;
 }
 

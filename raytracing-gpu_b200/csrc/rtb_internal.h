@@ -82,6 +82,8 @@ struct DevScene {
   uint32_t n_objects, n_lights;
   const float4 *materials;  // 3 float4 per object: (ka_col, kd_col, ks_col as packed RGBA8 bits; ns) (nr,0,0,0) ...
   const float4 *lights;     // 2 float4 per light: (type, packed colour, 0, 0) (v.xyz, 0)
+  const uint32_t *inv_order; // global triangle id -> slot (raster.cuh), nullptr when the scene has no hierarchy
+  float pad_unit;           // needle-padding unit the leaf boxes were built with (pad.cuh)
   float abs_max;            // largest |coordinate| of the scene bounds (conservative-margin scale)
   float margin_k;           // box inflation, in float spacings at abs_max + |origin| (trace.cu)
 };
@@ -89,6 +91,8 @@ struct DevScene {
 struct DevCamera {
   float3 u, v, C, pos;      // gpu/raytracer.cu:178-182 (host part of render())
   int W, H;                 // sample grid (already multiplied by aliasing)
+  float3 w;                 // u x v: C = pos + w L
+  float L;                  // distance of the image plane (raster.cuh)
 };
 
 struct FrameArgs {
@@ -104,6 +108,13 @@ struct FrameArgs {
   const unsigned int *item_order;
   unsigned short *item_cost;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
+  // primary visibility by projection (raster.cuh); prim == nullptr: every ray walks the tree
+  unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
+  uint4 *rast_items;              // (slot, x0 | y0 << 16, x1 | y1 << 16, -) rectangles clipped to 32x32-sample tiles
+  unsigned rast_cap;              // capacity of rast_items
+  unsigned *rast;                 // counters and flags (raster.cuh RAST_WORDS)
+  float rast_eps;                 // box inflation: the ray-time margin at this frame's farthest origin
+  unsigned rast_area_factor;      // give up when the rectangles cover more than this many times the frame
   // wavefront kernel only
   float *bounce_scratch;          // per resident warp: 7 x S floats (origin, direction, nr_ of reflected rays)
   int n_shadow_lights;            // DIRECTIONAL + POINT lights (<= 32 for the wavefront kernel)
@@ -132,6 +143,8 @@ int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys
                       cudaStream_t st, int *result_in_alt);
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
                    cudaStream_t st);
+int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, cudaStream_t st);
+constexpr int RAST_STATE_WORDS = 32;      // size of FrameArgs::rast, in 32-bit words
 int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,
                       float *d_dist, cudaStream_t st);
 void set_margin_k(float k);   // conservative-box scale factor (tests only)

@@ -14,6 +14,7 @@ struct SceneStore {
   float4 *v0 = nullptr, *e1 = nullptr, *e2 = nullptr, *n0 = nullptr, *n1 = nullptr, *n2 = nullptr;
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
   uint32_t *order = nullptr;            // slot -> global triangle id
+  uint32_t *inv_order = nullptr;        // global triangle id -> slot
   uint32_t *up = nullptr;               // [n_nodes] parent links, then [n_tris] slot -> leaf position (rtb_internal.h)
   uint32_t n_tris = 0, n_objects = 0, n_lights = 0;
   uint32_t n_nodes = 0, n_leaves = 0, max_leaf = 0;
@@ -23,6 +24,7 @@ struct SceneStore {
   int mode_cost[4] = {0, 0, 0, 0};      // surface-area cost of the four sample trees (0: not evaluated)
   bool has_tree = false;
   float abs_max = 0;
+  float pad_unit = 0;                   // needle-padding unit of the leaf boxes (pad.cuh)
   float origin_radius = 0;              // ray-origin radius the sliver padding was built for (build.cu)
   struct camera camera;                 // current camera (sample-grid resolution)
 
@@ -33,6 +35,12 @@ struct SceneStore {
   size_t h_frame_bytes = 0;
   unsigned int *d_tile_counter = nullptr;
   unsigned long long *d_counters = nullptr;
+  // primary visibility by projection (raster.cuh), grown on demand by api.cu
+  unsigned long long *d_prim = nullptr;
+  size_t d_prim_count = 0;
+  uint4 *d_rast_items = nullptr;
+  size_t d_rast_cap = 0;
+  unsigned *d_rast = nullptr;
   float *d_bounce = nullptr;            // wavefront kernel: reflected-ray scratch
   size_t d_bounce_floats = 0;
   int n_shadow_lights = 0;              // DIRECTIONAL + POINT lights
@@ -56,6 +64,7 @@ struct SceneStore {
     d.v0 = v0; d.e1 = e1; d.e2 = e2; d.n0 = n0; d.n1 = n1; d.n2 = n2;
     d.nodes = nodes; d.node_up = up; d.slot_up = up ? up + n_nodes : nullptr; d.root = root; d.n_tris = n_tris; d.n_objects = n_objects; d.n_lights = n_lights;
     d.materials = materials; d.lights = lights; d.abs_max = abs_max; d.margin_k = get_margin_k();
+    d.inv_order = inv_order; d.pad_unit = pad_unit;
     return d;
   }
 };

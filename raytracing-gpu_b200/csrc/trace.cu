@@ -14,6 +14,7 @@
 // traversal order.  The hierarchy only culls: every box test is conservative.
 #include "rtb_internal.h"
 #include "rtb_math.cuh"
+#include "pad.cuh"
 
 namespace rtb {
 
@@ -460,9 +461,23 @@ __device__ __forceinline__ void primary_ray(const DevCamera &cam, int px, int py
   d = vnorm(vsub(mk(cam.pos), o));
 }
 
+#ifndef RTB_RANK_TILE
+#define RTB_RANK_TILE 32      /* rank tile edge in output pixels (multiple of 8) */
+#endif
+constexpr int RANK_TILE = RTB_RANK_TILE;
+constexpr int RT_WX = RANK_TILE / 8, RT_WY = RANK_TILE / 4, RT_ITEMS = RT_WX * RT_WY;   // warp tiles per rank tile
+
+static_assert(RANK_TILE % 32 == 0 || RANK_TILE == 16 || RANK_TILE == 8, "rank tiles");
+
+}  // namespace
+#include "raster.cuh"
+namespace {
+
 // raytrace kernel body (gpu/raytracer.cu:87-129) for one sample
+// use_prim: the first ray's winner comes from the projection pass (raster.cuh prim_lookup)
 template <int TRACER, bool COUNT>
-__device__ uint32_t shade_sample(const DevScene &sc, const DevCamera &cam, int px, int py, Counters &c) {
+__device__ uint32_t shade_sample(const DevScene &sc, const FrameArgs &fa, bool use_prim, int px, int py, Counters &c) {
+  const DevCamera &cam = fa.cam;
   V3 o, d;
   primary_ray(cam, px, py, o, d);
   float nr_ = 1, r = 1;
@@ -474,7 +489,10 @@ __device__ uint32_t shade_sample(const DevScene &sc, const DevCamera &cam, int p
     first = false;
     Best b;
     uint32_t tc;
-    if (trace<TRACER, false, COUNT>(sc, o, d, b, c)) {
+    bool hit;
+    if (use_prim) { hit = prim_lookup(sc, fa, px, py, o, d, b); use_prim = false; }
+    else hit = trace<TRACER, false, COUNT>(sc, o, d, b, c);
+    if (hit) {
       V3 P, N;
       hit_record(sc, o, d, b.slot, P, N);
       const int obj = __float_as_int(__ldg(sc.e1 + b.slot).w);
@@ -503,12 +521,6 @@ constexpr int FRAME_WARPS = FRAME_THREADS / 32;
 // (Tx,Ty) belongs to rank (Tx + 3*Ty) mod N, so in tile row Ty this rank owns the columns
 // Tx0(Ty) + N*j; rows are padded to J = ceil(nTx / N) slots (a slot past the row end is an
 // empty item).  Only owned tiles are enumerated: one atomic per item, whatever N is.
-#ifndef RTB_RANK_TILE
-#define RTB_RANK_TILE 32      /* rank tile edge in output pixels (multiple of 8) */
-#endif
-constexpr int RANK_TILE = RTB_RANK_TILE;
-constexpr int RT_WX = RANK_TILE / 8, RT_WY = RANK_TILE / 4, RT_ITEMS = RT_WX * RT_WY;   // warp tiles per rank tile
-
 __device__ __forceinline__ unsigned frame_items(const FrameArgs &fa) {
   const int nTx = (fa.out_w + RANK_TILE - 1) / RANK_TILE, nTy = (fa.out_h + RANK_TILE - 1) / RANK_TILE;
   const int J = (nTx + fa.nranks - 1) / fa.nranks;
@@ -544,6 +556,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
   const int a = fa.aliasing;
   uint2 *acc = s_acc[warp];
   const unsigned total = frame_items(fa);
+  const bool use_prim = TRACER == RTB_TRACER_TREE && !COUNT && rast_active(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
     unsigned t = 0;
@@ -562,7 +575,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
       const int px = a * lx0 + sx, py = a * ly0 + sy;
       if (px < fa.cam.W && py < fa.cam.H) {
-        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa.cam, px, py, c);
+        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
         uint2 *dst = acc + (sy / a) * 8 + sx / a;
         atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
         atomicAdd(&dst->y, ch_b(col));
@@ -688,6 +701,17 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
   RTB_CUDA(cudaMemsetAsync(fa.tile_counter, 0, sizeof(unsigned int), st));
   if (count) RTB_CUDA(cudaMemsetAsync(fa.counters, 0, 8 * sizeof(unsigned long long), st));
   if (launches) *launches = 1;
+  if (fa.prim && tracer == RTB_TRACER_TREE && !count) {
+    // projection pass: records of the nearest primary candidate per sample (raster.cuh)
+    RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
+    RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
+    if (sc.n_tris) {
+      k_rast_setup<<<(sc.n_tris + 255) / 256, 256, 0, st>>>(sc, fa);
+      k_rast_items<<<sm_count * 8, 256, 0, st>>>(sc, fa);
+    }
+    RTB_CUDA(cudaGetLastError());
+    if (launches) *launches = 3;
+  }
   // RTB_KERNEL_WAVEFRONT was requested and is applicable (api.cu sets bounce_scratch only then);
   // everything else runs the persistent-warp per-sample kernel, the faster of the two
 #if !RTB_BVH4
@@ -739,6 +763,20 @@ int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t
   if (!blocks) return RTB_OK;
   if (tracer == RTB_TRACER_BRUTE) k_hit_ids<RTB_TRACER_BRUTE><<<blocks, 128, 0, st>>>(sc, cam, d_tri, d_obj);
   else k_hit_ids<RTB_TRACER_TREE><<<blocks, 128, 0, st>>>(sc, cam, d_tri, d_obj);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, cudaStream_t st) {
+  static_assert(RAST_WORDS <= RAST_STATE_WORDS, "raster state");
+  RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
+  RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
+  if (sc.n_tris) {
+    k_rast_setup<<<(sc.n_tris + 255) / 256, 256, 0, st>>>(sc, fa);
+    k_rast_items<<<148 * 8, 256, 0, st>>>(sc, fa);
+  }
+  const size_t n = (size_t)fa.cam.W * fa.cam.H;
+  if (n) k_prim_ids<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sc, fa, d_tri, d_obj);
   RTB_CUDA(cudaGetLastError());
   return RTB_OK;
 }

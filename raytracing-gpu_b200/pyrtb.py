@@ -48,7 +48,7 @@ class SceneStruct(C.Structure):
 
 class FrameOpts(C.Structure):
     _fields_ = [("aliasing", C.c_int), ("tracer", C.c_int), ("rank", C.c_int), ("nranks", C.c_int),
-                ("count_rays", C.c_int), ("reserved", C.c_int * 3)]
+                ("count_rays", C.c_int), ("frame_kernel", C.c_int), ("primary", C.c_int), ("reserved", C.c_int)]
 
 
 class Stats(C.Structure):
@@ -69,7 +69,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_render", "rtb_render_multi", "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_set_camera",
     "rtb_scene_render", "rtb_scene_render_device", "rtb_scene_sync", "rtb_scene_hit_ids", "rtb_scene_trace_rays",
     "rtb_scene_stats", "rtb_radix_sort_pairs_u32", "rtb_radix_sort_pairs_u64", "rtb_inclusive_scan_u32",
-    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_scene_dump_tree",
+    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_scene_dump_tree", "rtb_scene_raster_state",
     "rtb_device_count", "rtb_version", "rtb_scene_root", "rtb_set_margin_k", "rtb_set_schedule", "rtb_warmup", "rtb_scene_timer_start",
     "rtb_scene_timer_stop", "rtb_host_alloc", "rtb_host_free", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_memset",
     "rtb_dev_download", "rtb_scene_mem_alloc", "rtb_scene_mem_free", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close",
@@ -337,6 +337,7 @@ class DeviceScene:
         self.h = C.c_void_p()
         self.aliasing = aliasing
         self.frame_kernel = 0
+        self.primary = 0
         self.out_w, self.out_h = hs.width, hs.height
         s = hs.scaled(aliasing)
         _check(lib().rtb_scene_create(C.byref(s), device, flags, C.byref(self.h)))
@@ -344,7 +345,8 @@ class DeviceScene:
     def _opts(self, tracer, rank, nranks, count):
         o = FrameOpts()
         o.aliasing, o.tracer, o.rank, o.nranks, o.count_rays = self.aliasing, tracer, rank, nranks, int(count)
-        o.reserved[0] = self.frame_kernel     # 0: per-sample kernel (product path), 1: wavefront kernel
+        o.frame_kernel = self.frame_kernel    # 0: per-sample kernel (product path), 1: wavefront kernel
+        o.primary = self.primary              # 0: auto, 1: tree walk, 2: projection (raster.cuh)
         return o
 
     def set_camera(self, cam_struct):
@@ -394,6 +396,14 @@ class DeviceScene:
         st = Stats()
         _check(lib().rtb_scene_stats(self.h, C.byref(st)))
         return {k: getattr(st, k) for k, _ in Stats._fields_}
+
+    def raster_state(self):
+        """rtb_scene_raster_state: items, gave-up flag, rectangle area, boxes across the camera plane"""
+        out = (C.c_uint * 8)()
+        fn = lib().rtb_scene_raster_state
+        fn.argtypes = [C.c_void_p, C.c_void_p]
+        _check(fn(self.h, out))
+        return dict(items=out[0], gave_up=out[1], area=out[2] | (out[3] << 32), straddlers=out[4])
 
     def dump_tree(self):
         nn, nt = C.c_size_t(), C.c_size_t()

@@ -20,6 +20,7 @@ ap.add_argument("--count", action="store_true")
 ap.add_argument("--wave", action="store_true")
 ap.add_argument("--nosched", action="store_true")
 ap.add_argument("--flags", type=int, default=0, help="rtb_scene_create flags (2: cubic keys only)")
+ap.add_argument("--primary", type=int, default=0, help="0 auto, 1 tree walk, 2 projection")
 ap.add_argument("--scene", default=None, help="golden scene name instead of the terrain (rendered at --w x --h)")
 a = ap.parse_args()
 pyrtb.lib().rtb_set_schedule(0 if a.nosched else 1)
@@ -31,6 +32,7 @@ else:
     hs = pyrtb.HostScene.terrain(a.grid, a.w, a.h)
 ds = pyrtb.DeviceScene(hs, 3, flags=a.flags)
 ds.frame_kernel = int(a.wave)
+ds.primary = a.primary
 st = ds.stats()
 print("build %.2f ms upload %.2f ms nodes %d depth %d  builder %d key mode %d (sample-tree cost of modes 1,2,3 vs 0: %s)" %
       (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"], st["builder"], st["key_mode"],
@@ -51,4 +53,5 @@ for k in ks:
         rays = s["rays_primary"] + s["rays_shadow"] + s["rays_bounce"]
         line += "  rays %d nodes/ray %.2f tris/ray %.2f" % (rays, s["node_visits"] / rays, s["tri_tests"] / rays)
     print(line, flush=True)
+    print("raster state", ds.raster_state(), "launches", ds.stats()["kernel_launches"], flush=True)
 ds.close()
