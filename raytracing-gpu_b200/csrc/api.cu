@@ -142,6 +142,7 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   // a tree walk costs about 3 000 instructions per sample, a rectangle sample about 100
   static const unsigned area_factor = [] { const char *e = getenv("RTB_RASTER_AREA"); return e && atoi(e) > 0 ? (unsigned)atoi(e) : 20u; }();
   fa.rast_area_factor = area_factor;
+  S.rast_area_factor = area_factor;
   fa.prim = S.d_prim;
   fa.rast_items = S.d_rast_items;
   fa.rast_cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
@@ -181,8 +182,17 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
   if (!RTB_BVH4 && want_raster && S.has_tree && S.inv_order && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
       o.frame_kernel == RTB_KERNEL_PER_SAMPLE) {
-    rc = ensure_raster_resources(S, fa, st);
-    if (rc) return rc;
+    // a frame of this camera that ran the pass and still walked the tree (boxes across the camera
+    // plane, rectangles covering too much) says the next one will too: AUTO does not try again
+    const unsigned long long key[4] = {S.camera_gen, (unsigned long long)fa.cam.W << 32 | (unsigned)fa.cam.H,
+                                       (unsigned long long)o.rank << 32 | (unsigned)o.nranks, 0ull};
+    const bool same = memcmp(key, S.rast_key, sizeof key) == 0;
+    if (!(o.primary == RTB_PRIMARY_AUTO && same && S.rast_useless)) {
+      rc = ensure_raster_resources(S, fa, st);
+      if (rc) return rc;
+      memcpy(S.rast_key, key, sizeof key);
+      S.rast_useless = false;
+    }
   }
   if (!RTB_BVH4 && o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
       S.n_lights <= 255) {
@@ -250,6 +260,11 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     S.order_camera_gen = S.camera_gen;
   }
   ++S.frames_done;
+  if (fa.prim) {
+    if (!S.h_rast) RTB_CUDA(cudaMallocHost((void **)&S.h_rast, 8 * sizeof(unsigned)));     // pinned: the copy must not block the host
+    RTB_CUDA(cudaMemcpyAsync(S.h_rast, S.d_rast, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    S.rast_pending = true;
+  }
   if (o.count_rays)
     RTB_CUDA(cudaMemcpyAsync(S.counters, S.d_counters, sizeof S.counters, cudaMemcpyDeviceToHost, st));
   return RTB_OK;
@@ -257,6 +272,12 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
 
 static int finish_frame(SceneStore &S, cudaStream_t st) {
   RTB_CUDA(cudaStreamSynchronize(st));
+  if (S.rast_pending) {
+    S.rast_pending = false;
+    const unsigned long long area = (unsigned long long)S.h_rast[2] | ((unsigned long long)S.h_rast[3] << 32);
+    const unsigned long long samples = (S.rast_key[1] >> 32) * (S.rast_key[1] & 0xffffffffull) / ((S.rast_key[2] & 0xffffffffull) ? (S.rast_key[2] & 0xffffffffull) : 1ull);
+    S.rast_useless = S.h_rast[1] != 0 || area > (unsigned long long)S.rast_area_factor * samples + 65536ull;
+  }
   float ms = 0;
   if (cudaEventElapsedTime(&ms, S.ev0, S.ev1) == cudaSuccess) S.frame_ms = ms;
   else cudaGetLastError();

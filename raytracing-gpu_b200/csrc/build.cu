@@ -917,6 +917,8 @@ void SceneStore::release() {
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
   order = nullptr; up = nullptr; inv_order = nullptr;
   d_prim = nullptr; d_rast_items = nullptr; d_rast = nullptr; d_prim_count = 0; d_rast_cap = 0;
+  if (h_rast) { cudaFreeHost(h_rast); h_rast = nullptr; }
+  rast_pending = false; rast_useless = false;
   d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);
   recycle_frame_ctx(*this);

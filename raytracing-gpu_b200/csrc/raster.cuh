@@ -25,7 +25,7 @@ namespace {
 
 constexpr int RAST_TILE = 32;                 // samples
 constexpr unsigned RAST_STRADDLE_MAX = 16;
-constexpr unsigned RAST_TILES_MAX = 4096;     // per triangle
+constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
 // rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 straddler count, 8.. straddler slots
 constexpr int RAST_WORDS = 8 + RAST_STRADDLE_MAX;
 
@@ -104,7 +104,8 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   unsigned mine = 0, area = 0;
   if (any) {
     const unsigned tiles = (unsigned)(tx1 - tx0 + 1) * (unsigned)(ty1 - ty0 + 1);
-    if (tiles > RAST_TILES_MAX) { rast[1] = 1u; }
+    if (*reinterpret_cast<volatile unsigned *>(rast + 1)) { /* the frame has given up: emit nothing more */ }
+    else if (tiles > RAST_TILES_MAX) { rast[1] = 1u; }
     else {
       for (int ty = ty0; ty <= ty1; ++ty)
         for (int tx = tx0; tx <= tx1; ++tx)

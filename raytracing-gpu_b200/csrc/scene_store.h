@@ -41,6 +41,11 @@ struct SceneStore {
   uint4 *d_rast_items = nullptr;
   size_t d_rast_cap = 0;
   unsigned *d_rast = nullptr;
+  unsigned *h_rast = nullptr;           // pinned: state the last projection pass left (read back with the frame)
+  bool rast_pending = false;            // h_rast is being filled by the stream
+  unsigned long long rast_key[4] = {0, 0, 0, 0};   // camera generation, samples, ranks, factor of the frame h_rast is for
+  unsigned rast_area_factor = 20;
+  bool rast_useless = false;            // that frame walked the tree although it ran the pass: do not try again
   float *d_bounce = nullptr;            // wavefront kernel: reflected-ray scratch
   size_t d_bounce_floats = 0;
   int n_shadow_lights = 0;              // DIRECTIONAL + POINT lights

@@ -109,29 +109,32 @@ def test_multi_rank_tiles_compose_with_the_projection(gpu):
         ds.close()
 
 
+def _floor_scene(n_floor, n_small=400):
+    """a floor of n_floor strips under and behind the camera (their boxes cross the plane through the
+    camera position) and n_small triangles in front of it"""
+    tris, norms = [], []
+    # floor strips along x, each crossing z = camera z
+    for k in range(n_floor):
+        x0, x1 = -8 + 16 * k / n_floor, -8 + 16 * (k + 1) / n_floor
+        tris += [[[x0, -1, -30], [x1, -1, -30], [x1, -1, 30]], [[x0, -1, -30], [x1, -1, 30], [x0, -1, 30]]]
+        norms += [[[0, 1, 0]] * 3] * 2
+    rng = np.random.default_rng(5)
+    for _ in range(n_small):                           # small triangles in front of the camera
+        c = np.array([rng.uniform(-6, 6), rng.uniform(-0.9, 3), rng.uniform(2, 20)])
+        t = c + rng.standard_normal((3, 3)) * 0.3
+        tris.append(t.tolist()); norms.append([[0, 0, -1]] * 3)
+    v = np.array(tris, np.float32); n = np.array(norms, np.float32)
+    mats = [[0.2, 0.2, 0.2, 0.7, 0.7, 0.7, 0.3, 0.3, 0.3, 20, 1, 0, 1]]
+    lights = [[pyrtb.AMBIENT, .3, .3, .3, 0, 0, 0], [pyrtb.DIRECTIONAL, 1, 1, 1, 0.3, -1, 0.5]]
+    cam = [160, 120, 0, 1, -4, 1, 0, 0, 0, -1, 0, 70]
+    return pyrtb.HostScene.from_arrays(v, n, [len(tris)], mats, lights, cam)
+
+
 def test_boxes_that_straddle_the_camera_plane(gpu):
     """a floor under and behind the camera: its triangles' boxes cross the plane through the camera
     position; up to 16 of them are tested directly by every sample, more make the frame fall back"""
-    def scene(n_floor):
-        tris, norms = [], []
-        # floor strips along x, each crossing z = camera z
-        for k in range(n_floor):
-            x0, x1 = -8 + 16 * k / n_floor, -8 + 16 * (k + 1) / n_floor
-            tris += [[[x0, -1, -30], [x1, -1, -30], [x1, -1, 30]], [[x0, -1, -30], [x1, -1, 30], [x0, -1, 30]]]
-            norms += [[[0, 1, 0]] * 3] * 2
-        rng = np.random.default_rng(5)
-        for _ in range(400):                               # small triangles in front of the camera
-            c = np.array([rng.uniform(-6, 6), rng.uniform(-0.9, 3), rng.uniform(2, 20)])
-            t = c + rng.standard_normal((3, 3)) * 0.3
-            tris.append(t.tolist()); norms.append([[0, 0, -1]] * 3)
-        v = np.array(tris, np.float32); n = np.array(norms, np.float32)
-        mats = [[0.2, 0.2, 0.2, 0.7, 0.7, 0.7, 0.3, 0.3, 0.3, 20, 1, 0, 1]]
-        lights = [[pyrtb.AMBIENT, .3, .3, .3, 0, 0, 0], [pyrtb.DIRECTIONAL, 1, 1, 1, 0.3, -1, 0.5]]
-        cam = [160, 120, 0, 1, -4, 1, 0, 0, 0, -1, 0, 70]
-        return pyrtb.HostScene.from_arrays(v, n, [len(tris)], mats, lights, cam)
-
     for n_floor, falls_back in ((3, False), (20, True)):
-        hs = scene(n_floor)
+        hs = _floor_scene(n_floor)
         ds = pyrtb.DeviceScene(hs, 3)
         try:
             want, _ = _ids(ds, TREE)
@@ -161,5 +164,27 @@ def test_needle_soups(gpu, T):
         assert int((got != brute).sum()) <= 3 and int((got != want).sum()) <= 3
         assert np.array_equal(_frame(ds, RASTER) == _frame(ds, TREE), np.ones((120, 200, 4), bool)) or \
             int((_frame(ds, RASTER) != _frame(ds, TREE)).any(axis=-1).sum()) <= 3
+    finally:
+        ds.close()
+
+
+def test_auto_does_not_retry_a_camera_whose_frame_fell_back(gpu):
+    import ctypes as C
+    hs = _floor_scene(20, 40000)                         # big enough for AUTO, 40 boxes across the camera plane
+    ds = pyrtb.DeviceScene(hs, 3)
+    try:
+        want = _frame(ds, TREE)
+        a = ds.render()
+        assert ds.raster_state()["gave_up"] and ds.stats()["kernel_launches"] == 3
+        b = ds.render()
+        assert ds.stats()["kernel_launches"] == 1, "same camera: straight to the tree"
+        assert np.array_equal(a, want) and np.array_equal(b, want)
+        cam = pyrtb.Camera()
+        C.memmove(C.byref(cam), C.byref(hs.scaled(3).camera), C.sizeof(pyrtb.Camera))
+        ds.set_camera(cam)                                # a new camera generation is a new chance
+        ds.render()
+        assert ds.stats()["kernel_launches"] == 3
+        assert np.array_equal(_frame(ds, RASTER), want), "on request the pass runs (and falls back) every time"
+        assert ds.stats()["kernel_launches"] == 3
     finally:
         ds.close()
