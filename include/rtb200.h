@@ -119,6 +119,7 @@ typedef struct rtb_scene_handle rtb_scene_t;
 #define RTB_BUILD_NO_TREE     1u   /* skip the hierarchy (brute-force tracer only) */
 #define RTB_BUILD_CUBIC_KEYS  2u   /* keep the x,y,z-interleaved sort keys: no choice between key layouts */
 #define RTB_BUILD_RADIX_ONLY  4u   /* plain Morton radix tree: no surface-area rebuild of the clusters */
+#define RTB_BUILD_NO_LIGHT_GRIDS 16u /* shadow rays always walk the tree (no per-light projection grids) */
 #define RTB_BUILD_ONE_FRAME   8u   /* the scene will be rendered once (rtb_render passes this): scenes of more
                                       than 2^18 triangles keep the radix tree; rebuilding the clusters of
                                       10 M triangles takes 6 ms and saves 1.3 ms per 4K frame */
@@ -210,7 +211,8 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);
 /* State the projection pass of the last frame (or hit-id query) left: out[0] rectangle items,
  * out[1] != 0: it gave up (too many items or boxes across the camera plane), out[2] | out[3] << 32
  * rectangle area in samples (the frame also walks the tree when this exceeds 8 x its samples),
- * out[4] boxes across the camera plane.  All zero when no projection pass ran. */
+ * out[4] boxes across the camera plane (all zero when no projection pass ran);
+ * out[5] lights with a shadow-ray grid, out[6] their list entries / 1024, out[7] their cells / 1024. */
 int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]);
 
 /* ---- build-pipeline primitives on HOST arrays (upload, run the device kernel,

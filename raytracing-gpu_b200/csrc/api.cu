@@ -663,9 +663,11 @@ int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]) {
   if (!h || !out) { set_error("NULL argument"); return RTB_ERR_ARG; }
   SceneStore &S = h->store;
   memset(out, 0, 8 * sizeof(unsigned));
+  const unsigned grids[3] = {(unsigned)S.n_lgrids, (unsigned)(S.lgrid_entries >> 10), (unsigned)(S.lgrid_cells >> 10)};
+  memcpy(out + 5, grids, sizeof grids);
   if (!S.d_rast) return RTB_OK;
   RTB_CUDA(cudaSetDevice(S.device));
-  RTB_CUDA(cudaMemcpyAsync(out, S.d_rast, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, S.stream));
+  RTB_CUDA(cudaMemcpyAsync(out, S.d_rast, 5 * sizeof(unsigned), cudaMemcpyDeviceToHost, S.stream));
   RTB_CUDA(cudaStreamSynchronize(S.stream));
   return RTB_OK;
 }

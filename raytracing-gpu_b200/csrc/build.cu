@@ -912,8 +912,10 @@ SceneStore::~SceneStore() { release(); }
 // Stream, events and frame buffers go back to a per-device cache (recycle_frame_ctx).
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, d_prim, d_rast_items, d_rast};
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, d_prim, d_rast_items, d_rast, lgrids};
   for (void *p : ptrs) if (p) cudaFreeAsync(p, stream);
+  for (void *&p : lgrid_mem) { if (p) cudaFreeAsync(p, stream); p = nullptr; }
+  lgrids = nullptr; n_lgrids = 0; lgrid_entries = lgrid_cells = 0;
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
   order = nullptr; up = nullptr; inv_order = nullptr;
   d_prim = nullptr; d_rast_items = nullptr; d_rast = nullptr; d_prim_count = 0; d_rast_cap = 0;
@@ -1280,6 +1282,21 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   S->build_ms = ms_between(e_up1, e_b1);
   S->build_launches = launches;
   S->camera = hs->camera;
+  // shadow-ray grids: resident scenes only (a single frame does not repay them)
+  if (tree && !(flags & (RTB_BUILD_ONE_FRAME | RTB_BUILD_NO_LIGHT_GRIDS))) {
+    float bmin[3], bmax[3];
+    for (int k = 0; k < 3; ++k) { bmin[k] = ord2f(h_bounds[k]); bmax[k] = ord2f(h_bounds[3 + k]); }
+    cudaEvent_t e_g0 = nullptr, e_g1 = nullptr;
+    RTB_CUDA(cudaEventCreate(&e_g0));
+    RTB_CUDA(cudaEventCreate(&e_g1));
+    RTB_CUDA(cudaEventRecord(e_g0, st));
+    const int rc = build_light_grids(*S, hs->lights, n_light, bmin, bmax, st);
+    RTB_CUDA(cudaEventRecord(e_g1, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    S->build_ms += ms_between(e_g0, e_g1);
+    cudaEventDestroy(e_g0); cudaEventDestroy(e_g1);
+    if (rc) return rc;
+  }
   S->n_shadow_lights = 0;
   for (size_t i = 0; i < n_light; ++i)
     if (hs->lights[i].type == DIRECTIONAL || hs->lights[i].type == POINT) {

@@ -64,6 +64,19 @@ constexpr int MORTON_BITS = 63;      // 21 bits per axis
 #define RTB_SHADOW_UP 0
 #endif
 
+// A light's shadow-ray grid (lightgrid.cuh)
+constexpr int LG_LARGE_MAX = 16;
+struct LightGrid {
+  int kind;                     // 0: none (shadow rays walk the tree), 1: directional light, 2: point light
+  float3 org, ax, ay, az;       // az: the light's direction (1) / the axis from the light towards the scene (2)
+  float x0, y0, inv_cell, slack;   // cell (i, j) = x0 + [i, i + 1) / inv_cell; slack: rounding of the projection
+  int nx, ny;
+  const uint32_t *cell_start;   // [nx * ny + 1]
+  const uint2 *entries;         // (triangle slot, its rectangle inside the cell), cell by cell
+  uint32_t n_large;             // triangles every ray tests: they cover too many cells or cross the light's plane
+  uint32_t large[LG_LARGE_MAX];
+};
+
 struct DevScene {
   // triangles in leaf (Morton) order, three float4 streams (SoA):
   //   v0 = (vertex0.xyz, as_float(global triangle id in host order))
@@ -82,6 +95,7 @@ struct DevScene {
   uint32_t n_objects, n_lights;
   const float4 *materials;  // 3 float4 per object: (ka_col, kd_col, ks_col as packed RGBA8 bits; ns) (nr,0,0,0) ...
   const float4 *lights;     // 2 float4 per light: (type, packed colour, 0, 0) (v.xyz, 0)
+  const LightGrid *lgrids;  // [n_lights] shadow-ray grids, nullptr: none
   const uint32_t *inv_order; // global triangle id -> slot (raster.cuh), nullptr when the scene has no hierarchy
   float pad_unit;           // needle-padding unit the leaf boxes were built with (pad.cuh)
   float abs_max;            // largest |coordinate| of the scene bounds (conservative-margin scale)
@@ -147,6 +161,9 @@ int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int
 constexpr int RAST_STATE_WORDS = 32;      // size of FrameArgs::rast, in 32-bit words
 int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,
                       float *d_dist, cudaStream_t st);
+struct SceneStore;
+int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights, const float bmin[3],
+                      const float bmax[3], cudaStream_t st);   // trace.cu, called at the end of build_scene
 void set_margin_k(float k);   // conservative-box scale factor (tests only)
 float get_margin_k();
 

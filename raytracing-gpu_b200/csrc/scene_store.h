@@ -14,6 +14,11 @@ struct SceneStore {
   float4 *v0 = nullptr, *e1 = nullptr, *e2 = nullptr, *n0 = nullptr, *n1 = nullptr, *n2 = nullptr;
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
   uint32_t *order = nullptr;            // slot -> global triangle id
+  LightGrid *lgrids = nullptr;          // device array [n_lights] (lightgrid.cuh)
+  void *lgrid_mem[16] = {nullptr};      // cell_start / entries of up to 8 grids
+  int n_lgrids = 0;
+  unsigned long long lgrid_entries = 0, lgrid_cells = 0;
+  float lgrid_margin_k = 0;             // ray-time margin the grids were built for
   uint32_t *inv_order = nullptr;        // global triangle id -> slot
   uint32_t *up = nullptr;               // [n_nodes] parent links, then [n_tris] slot -> leaf position (rtb_internal.h)
   uint32_t n_tris = 0, n_objects = 0, n_lights = 0;
@@ -70,6 +75,7 @@ struct SceneStore {
     d.nodes = nodes; d.node_up = up; d.slot_up = up ? up + n_nodes : nullptr; d.root = root; d.n_tris = n_tris; d.n_objects = n_objects; d.n_lights = n_lights;
     d.materials = materials; d.lights = lights; d.abs_max = abs_max; d.margin_k = get_margin_k();
     d.inv_order = inv_order; d.pad_unit = pad_unit;
+    d.lgrids = (lgrids && get_margin_k() <= lgrid_margin_k) ? lgrids : nullptr;
     return d;
   }
 };

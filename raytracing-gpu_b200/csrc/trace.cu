@@ -12,9 +12,14 @@
 // Nearest hit = lexicographic minimum of (new_dist, global triangle id), which equals
 // the reference's "first strict minimum in iteration order" and does not depend on the
 // traversal order.  The hierarchy only culls: every box test is conservative.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include <vector>
 #include "rtb_internal.h"
 #include "rtb_math.cuh"
 #include "pad.cuh"
+#include "scene_store.h"
 
 namespace rtb {
 
@@ -403,6 +408,10 @@ __device__ __forceinline__ bool trace(const DevScene &sc, const V3 o, const V3 d
 #endif
 }
 
+}  // namespace
+#include "lightgrid.cuh"
+namespace {
+
 // gpu/light.cu:12-27
 __device__ __forceinline__ uint32_t apply_specular(uint32_t color, const V3 inc_o, const V3 inc_d, const V3 P,
                                                    const V3 N, uint32_t ks_col, float ns) {
@@ -435,7 +444,11 @@ __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 
       const V3 dir = type == DIRECTIONAL ? L : vsub(lv, P);
       Best b;
       if (COUNT) ++c.shadow;
-      if (!trace<TRACER, true, COUNT>(sc, P, dir, b, c, slot)) {
+      // shadow-ray grid of this light (lightgrid.cuh) when it has one; -1: this ray walks the tree
+      int occluded = -1;
+      if (TRACER == RTB_TRACER_TREE && !COUNT && sc.lgrids && sc.lgrids[i].kind) occluded = lg_any(sc, sc.lgrids[i], P, dir);
+      if (occluded < 0) occluded = trace<TRACER, true, COUNT>(sc, P, dir, b, c, slot) ? 1 : 0;
+      if (!occluded) {
         uint32_t t = color_mults(lcol, kd);
         if (type == DIRECTIONAL) {
           t = color_mul(t, vdot(L, Nrm));
@@ -654,6 +667,117 @@ float g_margin_k = 24.0f;
 
 void set_margin_k(float k) { g_margin_k = k; }
 float get_margin_k() { return g_margin_k; }
+
+// ---- shadow-ray grids (lightgrid.cuh), built once per resident scene ----
+constexpr uint32_t LG_MIN_TRIS = 1u << 15;
+constexpr int LG_MAX_GRIDS = 8;
+
+int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights, const float bmin[3],
+                      const float bmax[3], cudaStream_t st) {
+  if (RTB_BVH4 || !S.has_tree || S.n_tris < LG_MIN_TRIS || !n_lights) return RTB_OK;
+  std::vector<LightGrid> grids(n_lights);
+  memset(grids.data(), 0, grids.size() * sizeof(LightGrid));
+  const DevScene sc = S.dev();
+  const uint32_t n = S.n_tris;
+  const float eps = (get_margin_k() + 2.0f) * 1.1920929e-7f * (2.001f * S.abs_max);   // trace_tree's margin at any origin inside the scene
+  const unsigned blocks = (n + 255) / 256;
+  int built = 0, mem = 0;
+  auto unit = [](float x, float y, float z, float3 &o) {
+    const float r = sqrtf(x * x + y * y + z * z);
+    if (!(r > 0) || !(r < 1e30f)) return false;
+    o = make_float3(x / r, y / r, z / r);
+    return true;
+  };
+  for (size_t i = 0; i < n_lights && built < LG_MAX_GRIDS; ++i) {
+    const struct light &l = lights[i];
+    LightGrid g;
+    memset(&g, 0, sizeof g);
+    if (l.type == DIRECTIONAL) {
+      if (!unit(l.v.x, l.v.y, l.v.z, g.az)) continue;
+      g.kind = 1;
+      g.slack = 4e-6f * (2.0f * S.abs_max + 1e-30f);
+    } else if (l.type == POINT) {
+      g.org = make_float3(l.v.x, l.v.y, l.v.z);
+      const float cx = 0.5f * (bmin[0] + bmax[0]), cy = 0.5f * (bmin[1] + bmax[1]), cz = 0.5f * (bmin[2] + bmax[2]);
+      const float ext = fmaxf(bmax[0] - bmin[0], fmaxf(bmax[1] - bmin[1], bmax[2] - bmin[2]));
+      if (!unit(cx - l.v.x, cy - l.v.y, cz - l.v.z, g.az)) continue;
+      const float dist = sqrtf((cx - l.v.x) * (cx - l.v.x) + (cy - l.v.y) * (cy - l.v.y) + (cz - l.v.z) * (cz - l.v.z));
+      if (!(dist > 1e-3f * ext)) continue;            // a light at the centre of the scene: boxes cross its plane everywhere
+      g.kind = 2;
+      g.slack = 2e-5f;
+    } else continue;
+    // any orthonormal frame around az
+    {
+      const float ax = fabsf(g.az.x), ay = fabsf(g.az.y), az = fabsf(g.az.z);
+      float3 h = ax <= ay && ax <= az ? make_float3(1, 0, 0) : (ay <= az ? make_float3(0, 1, 0) : make_float3(0, 0, 1));
+      float3 a = make_float3(h.y * g.az.z - h.z * g.az.y, h.z * g.az.x - h.x * g.az.z, h.x * g.az.y - h.y * g.az.x);
+      if (!unit(a.x, a.y, a.z, g.ax)) continue;
+      g.ay = make_float3(g.az.y * g.ax.z - g.az.z * g.ax.y, g.az.z * g.ax.x - g.az.x * g.ax.z, g.az.x * g.ax.y - g.az.y * g.ax.x);
+    }
+    // extent of the projection
+    uint32_t *d_b = nullptr;
+    RTB_CUDA(cudaMallocAsync((void **)&d_b, 32 * 4, st));
+    const uint32_t init[4] = {0xffffffffu, 0u, 0xffffffffu, 0u};
+    uint32_t hb[4];
+    RTB_CUDA(cudaMemcpyAsync(d_b, init, sizeof init, cudaMemcpyHostToDevice, st));
+    k_lg_bounds<<<blocks, 256, 0, st>>>(sc, g, eps, d_b);
+    RTB_CUDA(cudaMemcpyAsync(hb, d_b, sizeof hb, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    float x0 = ord2f(hb[0]), x1 = ord2f(hb[1]), y0 = ord2f(hb[2]), y1 = ord2f(hb[3]);
+    if (g.kind == 2) {
+      x0 = fmaxf(x0, -LG_PERSP_LIMIT); y0 = fmaxf(y0, -LG_PERSP_LIMIT);
+      x1 = fminf(x1, LG_PERSP_LIMIT); y1 = fminf(y1, LG_PERSP_LIMIT);
+    }
+    if (!(x1 > x0) || !(y1 > y0) || !(x1 - x0 < 1e30f) || !(y1 - y0 < 1e30f)) { cudaFreeAsync(d_b, st); continue; }
+    // about one cell per two triangles: a triangle of average size then touches ~4 cells
+    static const double cells_per_tri = [] { const char *e = getenv("RTB_LG_CELLS"); return e && atof(e) > 0 ? atof(e) : 0.5; }();
+    const double target = fmin(fmax(cells_per_tri * (double)n, 1024.0), 64.0e6);
+    double cell = sqrt((double)(x1 - x0) * (double)(y1 - y0) / target);
+    cell = fmax(cell, fmax((double)(x1 - x0), (double)(y1 - y0)) / 30000.0);
+    g.x0 = x0; g.y0 = y0; g.inv_cell = (float)(1.0 / cell);
+    g.nx = (int)ceil((x1 - x0) / cell) + 1; g.ny = (int)ceil((y1 - y0) / cell) + 1;
+    const size_t cells = (size_t)g.nx * g.ny;
+    uint32_t *counts = nullptr, *cursor = nullptr, *scratch = nullptr;
+    uint2 *entries = nullptr;
+    const size_t ssw = scan_scratch_words(cells + 1);
+    RTB_CUDA(cudaMallocAsync((void **)&counts, (cells + 1) * 4, st));
+    RTB_CUDA(cudaMallocAsync((void **)&scratch, ssw * 4, st));
+    RTB_CUDA(cudaMemsetAsync(counts, 0, (cells + 1) * 4, st));
+    RTB_CUDA(cudaMemsetAsync(d_b, 0, 32 * 4, st));
+    k_lg_scatter<false><<<blocks, 256, 0, st>>>(sc, g, eps, counts, d_b, nullptr, nullptr);
+    int rc = dev_exclusive_scan_u32(counts, cells + 1, scratch, ssw, false, st, nullptr);
+    uint32_t total = 0, state[2 + LG_LARGE_MAX];
+    if (!rc) {
+      RTB_CUDA(cudaMemcpyAsync(&total, counts + cells, 4, cudaMemcpyDeviceToHost, st));
+      RTB_CUDA(cudaMemcpyAsync(state, d_b, sizeof state, cudaMemcpyDeviceToHost, st));
+      RTB_CUDA(cudaStreamSynchronize(st));
+    }
+    cudaFreeAsync(scratch, st);
+    const bool ok = !rc && !state[1] && (size_t)total <= 24ull * n + (1u << 20) && total > 0;
+    if (!ok) { cudaFreeAsync(counts, st); cudaFreeAsync(d_b, st); if (rc) return rc; continue; }
+    RTB_CUDA(cudaMallocAsync((void **)&entries, (size_t)total * sizeof(uint2), st));
+    RTB_CUDA(cudaMallocAsync((void **)&cursor, cells * 4, st));
+    RTB_CUDA(cudaMemsetAsync(cursor, 0, cells * 4, st));
+    k_lg_scatter<true><<<blocks, 256, 0, st>>>(sc, g, eps, cursor, d_b, counts, entries);
+    RTB_CUDA(cudaGetLastError());
+    cudaFreeAsync(cursor, st);
+    cudaFreeAsync(d_b, st);
+    g.cell_start = counts; g.entries = entries;
+    g.n_large = state[0] < (uint32_t)LG_LARGE_MAX ? state[0] : (uint32_t)LG_LARGE_MAX;
+    for (uint32_t k = 0; k < g.n_large; ++k) g.large[k] = state[2 + k];
+    S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
+    S.lgrid_entries += total; S.lgrid_cells += cells;
+    grids[i] = g;
+    ++built;
+  }
+  if (!built) return RTB_OK;
+  RTB_CUDA(cudaMallocAsync((void **)&S.lgrids, n_lights * sizeof(LightGrid), st));
+  RTB_CUDA(cudaMemcpyAsync(S.lgrids, grids.data(), n_lights * sizeof(LightGrid), cudaMemcpyHostToDevice, st));
+  RTB_CUDA(cudaStreamSynchronize(st));      // grids lives on this stack frame
+  S.lgrid_margin_k = get_margin_k();
+  S.n_lgrids = built;
+  return RTB_OK;
+}
 
 template <int TRACER, bool COUNT>
 static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {

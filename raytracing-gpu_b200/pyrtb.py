@@ -403,7 +403,8 @@ class DeviceScene:
         fn = lib().rtb_scene_raster_state
         fn.argtypes = [C.c_void_p, C.c_void_p]
         _check(fn(self.h, out))
-        return dict(items=out[0], gave_up=out[1], area=out[2] | (out[3] << 32), straddlers=out[4])
+        return dict(items=out[0], gave_up=out[1], area=out[2] | (out[3] << 32), straddlers=out[4], light_grids=out[5],
+                    grid_entries_k=out[6], grid_cells_k=out[7])
 
     def dump_tree(self):
         nn, nt = C.c_size_t(), C.c_size_t()

@@ -11,7 +11,8 @@ full = hs.s.light_count
 prev = None
 for nl, label in ((1, "primary only (ambient)"), (2, "+ directional shadow"), (3, "+ point shadow")):
     hs.s.light_count = nl
-    ds = pyrtb.DeviceScene(hs, 3)
+    ds = pyrtb.DeviceScene(hs, 3, flags=int(sys.argv[1]) if len(sys.argv) > 1 else 0)
+    ds.primary = int(sys.argv[2]) if len(sys.argv) > 2 else 0
     ds.render()
     ds.render()
     ms = ds.stats()["frame_ms"]
@@ -23,6 +24,7 @@ for nl, label in ((1, "primary only (ambient)"), (2, "+ directional shadow"), (3
         d = cur
     else:
         d = tuple(c - p for c, p in zip(cur, prev))
+    print(ds.raster_state())
     print("%-26s rays %10d  nodes/ray %.1f  tris/ray %.2f  frame %.2f ms (+%.2f ms, %.0f Mrays/s incremental)" %
           (label, d[0], d[1] / d[0], d[2] / d[0], ms, d[3], d[0] / d[3] / 1e3), flush=True)
     prev = cur
