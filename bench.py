@@ -255,6 +255,8 @@ def run_ours(args):
         ds.sync()
         kernel_ms.append(ds.stats()["frame_ms"])
     kernel_ms_avg = max_over_ranks(float(np.mean(kernel_ms)))
+    launches_per_frame = int(ds.stats()["kernel_launches"])      # projection pass (2) + frame kernel
+    rstate = ds.raster_state()
     per_rank_ms = [float(np.mean(kernel_ms))]
     if dist is not None:
         import torch
@@ -325,18 +327,25 @@ def run_ours(args):
         alg_bytes = primary * BYTES_PRIMARY + shadow * BYTES_SHADOW + bounce * BYTES_PRIMARY
         achieved_tflops = alg_ops / world / kern_s / 1e12        # per GPU: each rank's kernel does 1/world of the rays
         roofline = {
-            "bound": "fp32_issue", "kernel": "k_frame<tree>", "achieved": achieved_tflops, "peak": issue_peak_tflops,
+            "bound": "fp32_issue",
+            "kernel": "k_frame<tree>" if launches_per_frame == 1 else "the frame's kernels: k_rast_setup + k_rast_items + k_frame<tree>",
+            "achieved": achieved_tflops, "peak": issue_peak_tflops,
             "unit": "TFLOP/s", "frac": achieved_tflops / issue_peak_tflops, "traffic": None,
             "peak_source": "148 SMs x 128 FP32 lanes x sm_max_mhz, %s" % pk["source"],
             "note": "divergent traversal + scalar FP32: the binding ceiling is SM instruction issue, not HBM or "
-                    "tensor cores (SURVEY 8d); achieved = algorithmic un-fused FP32 ops per launch / CUDA-event "
-                    "duration of the launch",
+                    "tensor cores (SURVEY 8d); achieved = algorithmic un-fused FP32 ops per frame (SURVEY 8d per-ray "
+                    "figures x rays) / CUDA-event duration of the frame's launches",
             "algorithmic_ops_per_launch": alg_ops // world, "kernel_ms": kernel_ms_avg,
             "kernel_ms_per_rank": per_rank_ms,
             "hbm": None,
             "request_volume_gbs": alg_bytes / world / kern_s / 1e9,   # cache-less: 64 B per node visit, 48 B per triangle test
             "measured_per_ray": {"node_visits": node_visits / max(rays + bounce, 1),
-                                 "tri_tests": tri_tests / max(rays + bounce, 1)},
+                                 "tri_tests": tri_tests / max(rays + bounce, 1),
+                                 "note": "device counters of the untimed counting frame, which walks the tree for every ray"},
+            "paths": {"primary": "projection pass (raster.cuh)" if launches_per_frame > 1 and not rstate["gave_up"] else "tree walk",
+                      "shadow": "%d light grid(s) (lightgrid.cuh)" % rstate["light_grids"] if rstate["light_grids"] else "tree walk",
+                      "projection_items": rstate["items"], "projection_area_samples": rstate["area"],
+                      "light_grid_entries_k": rstate["grid_entries_k"], "launches_per_frame": launches_per_frame},
         }
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
@@ -373,7 +382,7 @@ def run_ours(args):
                                       "into rank 0's frame over NVLink" % world,
                        "l2": "inputs larger than L2 (triangles 960 MB + nodes %d MB vs 126 MB L2)" % (st0["tree_bytes"] >> 20),
                        "rays_per_frame": {"primary": primary, "shadow": shadow, "bounce": bounce}},
-            "e2e": e2e, "gpu_launches": args.steps * 1, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
+            "e2e": e2e, "gpu_launches": args.steps * launches_per_frame, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
             "build": {"upload_ms": st0["upload_ms"], "build_ms": st0["build_ms"], "nodes": st0["nodes"],
                       "leaves": st0["leaves"], "max_depth": st0["max_depth"], "build_launches": st0["build_launches"],
                       "scene_generation_s": t_gen},

@@ -188,3 +188,48 @@ def test_auto_does_not_retry_a_camera_whose_frame_fell_back(gpu):
         assert ds.stats()["kernel_launches"] == 3
     finally:
         ds.close()
+
+
+NO_LIGHT_GRIDS = 16          # include/rtb200.h RTB_BUILD_NO_LIGHT_GRIDS
+
+
+@pytest.mark.parametrize("scene", ["terrain", "terrain-low-light", "soup", "floor"])
+def test_shadow_ray_grids_give_the_tree_walk_frames(gpu, scene):
+    """per-light projection grids (csrc/lightgrid.cuh) against shadow rays that walk the tree"""
+    if scene == "terrain":
+        hs = pyrtb.HostScene.terrain(220, 640, 360)
+    elif scene == "terrain-low-light":
+        # the point light down among the hills and the directional light grazing: long shadows,
+        # boxes across the light's plane, rays whose point falls off the grid
+        hs = pyrtb.HostScene.terrain(220, 640, 360)
+        a = hs.arrays()
+        lights = a["lights"].copy()
+        for l in lights:
+            if int(l[0]) == pyrtb.POINT:
+                l[4:7] = [30.0, 12.0, 420.0]
+            elif int(l[0]) == pyrtb.DIRECTIONAL:
+                l[4:7] = [1.0, -0.12, 0.3]
+        hs = pyrtb.HostScene.from_arrays(a["vertex"], a["normal"], a["tri_counts"], a["materials"], lights, a["camera"])
+    elif scene == "soup":
+        hs = random_scene(77, 40000, 320, 200)           # needles, mirrors (bounce hits cast shadow rays too)
+    else:
+        hs = _floor_scene(6, 40000)
+    with_grids = pyrtb.DeviceScene(hs, 3)
+    without = pyrtb.DeviceScene(hs, 3, flags=NO_LIGHT_GRIDS)
+    try:
+        assert without.raster_state()["light_grids"] == 0
+        n_grids = with_grids.raster_state()["light_grids"]
+        if scene == "terrain":
+            assert n_grids == 2
+        elif scene == "terrain-low-light":
+            assert n_grids >= 1      # the light among the hills may keep the tree walk: boxes cross its plane
+        for primary in (TREE, AUTO):
+            a = _frame(with_grids, primary)
+            b = _frame(without, primary)
+            diff = int((a != b).any(axis=-1).sum())
+            # needle soups: the grid culls with each triangle's own box, the tree with leaf boxes, so the
+            # ill-conditioned acceptances of tests/test_gpu_random_scenes.py may fall differently
+            assert diff <= (3 if scene == "soup" else 0), (scene, primary, diff, n_grids)
+    finally:
+        with_grids.close()
+        without.close()

@@ -37,4 +37,13 @@ r = rast[pts[:, 0], pts[:, 1]]
 nd = len(diff)
 print("on the %d differing samples: tree == brute %d, raster == brute %d" % (nd, int((t[:nd] == bt[:nd]).sum()), int((r[:nd] == bt[:nd]).sum())))
 print("on 2000 random samples: tree == brute %d, raster == brute %d" % (int((t[nd:] == bt[nd:]).sum()), int((r[nd:] == bt[nd:]).sum())))
+# frames: projection pass + light grids (default) against tree walks for every ray
+ds.primary = 0
+full = ds.render()
 ds.close()
+ds2 = pyrtb.DeviceScene(hs, 3, flags=16)      # RTB_BUILD_NO_LIGHT_GRIDS
+ds2.primary = 1
+ref = ds2.render()
+ds2.close()
+d = (full != ref).any(axis=-1)
+print("frame pixels that differ between (projection + grids) and (tree walk for every ray): %d of %d" % (int(d.sum()), d.size))
