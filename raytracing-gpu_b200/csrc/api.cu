@@ -260,7 +260,8 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     S.order_camera_gen = S.camera_gen;
   }
   ++S.frames_done;
-  if (fa.prim) {
+  // (a handle built for one frame has no next frame to spare the attempt, and pinning memory costs milliseconds)
+  if (fa.prim && !S.one_frame) {
     if (!S.h_rast) RTB_CUDA(cudaMallocHost((void **)&S.h_rast, 8 * sizeof(unsigned)));     // pinned: the copy must not block the host
     RTB_CUDA(cudaMemcpyAsync(S.h_rast, S.d_rast, 8 * sizeof(unsigned), cudaMemcpyDeviceToHost, st));
     S.rast_pending = true;

@@ -980,6 +980,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   cudaStream_t st = S->stream;
   tl_alloc_stream = st;
   S->origin_radius = 2.0f * camera_origin_radius(hs->camera);   // x2 head-room for camera moves
+  S->one_frame = (flags & RTB_BUILD_ONE_FRAME) != 0;
   Temp tmp;
   cudaEvent_t e_up0 = S->ev0, e_up1 = S->ev1;
   cudaEvent_t e_b1 = nullptr;

@@ -47,6 +47,7 @@ struct SceneStore {
   size_t d_rast_cap = 0;
   unsigned *d_rast = nullptr;
   unsigned *h_rast = nullptr;           // pinned: state the last projection pass left (read back with the frame)
+  bool one_frame = false;               // built with RTB_BUILD_ONE_FRAME
   bool rast_pending = false;            // h_rast is being filled by the stream
   unsigned long long rast_key[4] = {0, 0, 0, 0};   // camera generation, samples, ranks, factor of the frame h_rast is for
   unsigned rast_area_factor = 20;

@@ -1,6 +1,6 @@
-"""Summarise an .ncu-rep here (no GPU): key raw metrics + hot SASS regions of the first kernel.
-usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [out.txt]"""
-import csv
+"""Summarise an .ncu-rep here (no GPU): key raw metrics + hot SASS regions of one kernel of the capture.
+usage: python tools/ncu_summary.py gpurun_out/prof.ncu-rep [out.txt] [kernel index, default 0]"""
+import re, csv
 import io
 import subprocess
 import sys
@@ -9,7 +9,8 @@ rep = sys.argv[1]
 out = open(sys.argv[2], "w") if len(sys.argv) > 2 else sys.stdout
 raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(raw)))
-hdr, units, vals = rows[0], rows[1], rows[2]
+KI = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+hdr, units, vals = rows[0], rows[1], rows[2 + KI]
 KEYS = ["Kernel Name", "gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
         "launch__occupancy_limit_registers", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__inst_executed.sum.per_cycle_elapsed",
@@ -22,6 +23,11 @@ for h, u, v in zip(hdr, units, vals):
         print("%-82s %-16s %s" % (h, u, v), file=out)
 src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(src)))
+starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"] + [len(rows)]      # one block per captured launch
+name = vals[hdr.index("Kernel Name")]                    # the source page groups launches by kernel, the raw page by time
+base = re.search(r"(\w+)\s*(<|\()", name.split("::")[-1]).group(1)
+pick = next((j for j in range(len(starts) - 1) if re.search(r"\b%s\b" % base, rows[starts[j]][1])), KI)
+rows = rows[starts[pick]:starts[pick + 1]]
 hdr, data = rows[1], [r for r in rows[2:] if len(r) > 10]
 ia, ie, it, isamp = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.index("Thread Instructions Executed"), hdr.index("# Samples")
 tot = sum(int(r[ie]) for r in data)
