@@ -125,7 +125,7 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   if (S.d_rast_cap < cap) {
     if (S.d_rast_items) cudaFreeAsync(S.d_rast_items, st);
     S.d_rast_items = nullptr; S.d_rast_cap = 0;
-    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, cap * sizeof(uint4), st));
+    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, (cap + 3 * (size_t)S.n_tris) * sizeof(uint4), st));   // items, then edge records
     S.d_rast_cap = cap;
   }
   if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, RAST_STATE_WORDS * 4, st));
@@ -145,6 +145,7 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   S.rast_area_factor = area_factor;
   fa.prim = S.d_prim;
   fa.rast_items = S.d_rast_items;
+  fa.rast_rec = reinterpret_cast<float4 *>(S.d_rast_items + S.d_rast_cap);
   fa.rast_cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
   fa.rast = S.d_rast;
   return RTB_OK;
@@ -176,7 +177,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
-  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_eps = 0; fa.rast_area_factor = 0;
+  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_eps = 0; fa.rast_area_factor = 0;
   // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);

@@ -24,6 +24,13 @@
 namespace {
 
 constexpr int RAST_TILE = 32;                 // samples
+#ifndef RTB_RAST_HULL
+#define RTB_RAST_HULL 1
+#endif
+constexpr bool RAST_HULL = RTB_RAST_HULL != 0;
+constexpr float RAST_HULL_MIN_COS = 1.0f / 16;   // flatter than this: the box only
+constexpr float RAST_RAY_C = 16.0f;              // distance between the rounded ray and the line through pos and the sample, in 2^-24 |s|
+constexpr float RAST_HULL_C = 14.0f;             // rounding of u and v in units of 2^-24 |s| |e| / |a|: twice the first-order bound
 constexpr unsigned RAST_STRADDLE_MAX = 16;
 constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
 // rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 straddler count, 8.. straddler slots
@@ -46,6 +53,24 @@ __device__ __forceinline__ bool rast_owned(const FrameArgs &fa, int tx, int ty) 
   return (Tx + 3 * Ty) % fa.nranks == fa.rank;
 }
 
+// k_rast_setup: one thread per triangle slot.  Rectangle, per-triangle edge record, items.
+//
+// Rectangle = (projection of the culling box) INTERSECTED with, for a triangle without needle
+// padding seen at a fair angle, (projection of the region of its plane where the rounded test can
+// accept).  That region: the test accepts when the COMPUTED (u, v) lies in the unit simplex.  With
+// eps = 2^-24, |d| = 1, s = origin - vertex0, h = d x e2, a = e1 . h (un-fused, as the reference):
+//   |dh| <= 2 sqrt2 eps |e2|,  |d(s . h)| <= |s| |dh| + 3 eps |s| |h| + eps |s| |h| <= 6.9 eps |s| |e2|,
+//   |da| <= 5.9 eps |e1| |e2|,  so  |du| <= 6.9 eps |s| |e2| / |a| + |u| 5.9 eps |e1| |e2| / |a| + 2 eps |u|
+// and the same for v with e1; |a| = |e1 x e2| cos(incidence).  RAST_HULL_C = 14 doubles the leading
+// constant (the |u| terms are smaller by |e| / |s|).  The true crossing point of an accepted ray
+// therefore lies in  u >= -du, v >= -dv, u + v <= 1 + du + dv + 4 eps : a triangle in the plane
+// whose corners are projected.  The cosine is (distance of pos from the plane) / |pos - point|,
+// smallest at the farthest corner; |s| is bounded by the frame's farthest origin.
+//
+// Edge record: the three edge lines of that projected triangle, pushed out by the projected size
+// of the ray's own rounding; k_rast_items tests the sample centre against them
+// before it spends a ray on it.  rec[3 slot + 0..2] = (n0x, n0y, c0, n1x) (n1y, c1, n2x, n2y)
+// (c2, X0, Y0, on): inside <=> n . (px - X0, py - Y0) + c <= 0 for the three edges.
 __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const FrameArgs fa) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   const int lane = threadIdx.x & 31;
@@ -53,12 +78,15 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   const float INF = __builtin_huge_valf();
   int x0 = 0, y0 = 0, x1 = -1, y1 = -1;        // empty rectangle
   bool straddle = false;
+  float4 r0 = make_float4(0, 0, -1, 0), r1 = make_float4(0, -1, 0, 0), r2 = make_float4(-1, 0, 0, 0);
   if (s < sc.n_tris) {
     const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
     const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
     V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
     V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
+    const V3 lo0 = lo, hi0 = hi;
     sliver_pad(v, sc.pad_unit, lo, hi);
+    bool plain = RAST_HULL && lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z;
     // ray-time margin of trace_tree at the largest origin of this frame, plus the rounding of
     // vertex0 + edge (the build boxes come from the stored vertices themselves)
     const float e = fa.rast_eps;
@@ -67,17 +95,22 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
     const V3 u = mk(fa.cam.u), vv = mk(fa.cam.v), w = mk(fa.cam.w), pos = mk(fa.cam.pos);
     const float ww = vdot(w, w), uv = vdot(u, vv);
     const float det = 1.0f - uv * uv;                      // Gram determinant of the unit vectors u, v
+    const float Lw = fa.cam.L;
+    auto project = [&](const V3 X, float &x, float &y, float &den) {
+      const V3 r = vsub(pos, X);
+      den = vdot(r, w);
+      const float t = Lw * ww / den;
+      const V3 q = vsub(vscale(r, t), vscale(w, Lw));     // offset from the plane's centre C
+      const float qu = vdot(q, u), qv = vdot(q, vv);
+      x = (qu - uv * qv) / det;
+      y = (qv - uv * qu) / det;
+    };
     float dmin = INF, dmax = -INF, xmin = INF, xmax = -INF, ymin = INF, ymax = -INF;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const V3 X = mk((k & 1) ? hi.x : lo.x, (k & 2) ? hi.y : lo.y, (k & 4) ? hi.z : lo.z);
-      const V3 r = vsub(pos, X);
-      const float den = vdot(r, w);
+      float x, y, den;
+      project(mk((k & 1) ? hi.x : lo.x, (k & 2) ? hi.y : lo.y, (k & 4) ? hi.z : lo.z), x, y, den);
       dmin = fminf(dmin, den); dmax = fmaxf(dmax, den);
-      const float t = fa.cam.L * ww / den;
-      const V3 q = vsub(vscale(r, t), vscale(w, fa.cam.L));     // offset from the plane's centre C
-      const float qu = vdot(q, u), qv = vdot(q, vv);
-      const float x = (qu - uv * qv) / det, y = (qv - uv * qu) / det;
       xmin = fminf(xmin, x); xmax = fmaxf(xmax, x); ymin = fminf(ymin, y); ymax = fmaxf(ymax, y);
     }
     // one side of the plane through pos, and not grazing it (relative to the box's own depth range)
@@ -89,8 +122,70 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       // the projection itself: a few float spacings of a coordinate that is at most ~1e5 samples
       const float cx = (float)(fa.cam.W / 2), cy = (float)(fa.cam.H / 2);
       const float sx = 0.02f + 4e-7f * fmaxf(fabsf(xmin), fabsf(xmax)), sy = 0.02f + 4e-7f * fmaxf(fabsf(ymin), fabsf(ymax));
-      const float fx0 = ceilf(xmin + cx - sx), fx1 = floorf(xmax + cx + sx);
-      const float fy0 = ceilf(ymin + cy - sy), fy1 = floorf(ymax + cy + sy);
+      float fx0 = ceilf(xmin + cx - sx), fx1 = floorf(xmax + cx + sx);
+      float fy0 = ceilf(ymin + cy - sy), fy1 = floorf(ymax + cy + sy);
+      // the accepted region in the triangle's plane (see above)
+      const V3 n = vcross(mk(b4), mk(c4)), p0 = vsub(pos, v[0]);
+      const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
+      const float far0 = fmaxf(vlen(p0), fmaxf(vlen(vsub(pos, v[1])), vlen(vsub(pos, v[2]))));
+      const float far = far0 + 0.25f * (l1 + l2);                       // the grown corners are a little farther
+      const float cosine = fabsf(vdot(n, p0)) / (ln * far);
+      // |origin - vertex| <= |origin - pos| + |pos - vertex|, origins lie within the frame's corners
+      const float smax = sqrtf(Lw * Lw + cx * cx + cy * cy) + far;
+      const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
+      const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
+      plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 0.25f && dv < 0.25f;       // NaN -> box only
+      if (plain) {
+        const float dw = du + dv + 2.4e-7f;
+        const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
+                         vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
+                         vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
+        float ax[3], ay[3];
+        float hx0 = INF, hx1 = -INF, hy0 = INF, hy1 = -INF, dnear = INF;
+        bool ok = true;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          float den;
+          project(P[k], ax[k], ay[k], den);
+          ok = ok && den * dmin > 0.0f;
+          dnear = fminf(dnear, fabsf(den));
+          hx0 = fminf(hx0, ax[k]); hx1 = fmaxf(hx1, ax[k]); hy0 = fminf(hy0, ay[k]); hy1 = fmaxf(hy1, ay[k]);
+        }
+        const float big = fmaxf(fmaxf(fabsf(hx0), fabsf(hx1)), fmaxf(fabsf(hy0), fabsf(hy1)));
+        // The ray itself is rounded: its origin by about a spacing of |o| (a thousandth of a sample:
+        // the image plane's unit is the sample) and its direction, normalize(pos - o), by an angle of
+        // about 3 eps, i.e. across the ray by 3 eps |s| at the triangle.  RAST_RAY_C = 16 eps |s| bounds
+        // both with a factor of two; a displacement of that size at depth >= dnear moves the
+        // projection by at most |delta| sqrt(L^2 + x^2) / depth (1.3: second order, dnear > 8 delta).
+        const float delta = RAST_RAY_C * 5.9604645e-8f * smax;
+        ok = ok && dnear > 0.25f * near && dnear > 8.0f * delta && big < 1e6f;
+        if (ok) {
+          const float se = 1.3f * delta * sqrtf(Lw * Lw + big * big) / dnear + 0.02f + 4e-7f * big;
+          fx0 = fmaxf(fx0, ceilf(hx0 + cx - se)); fx1 = fminf(fx1, floorf(hx1 + cx + se));
+          fy0 = fmaxf(fy0, ceilf(hy0 + cy - se)); fy1 = fminf(fy1, floorf(hy1 + cy + se));
+          const float X0 = fmaxf(fx0, 0.0f), Y0 = fmaxf(fy0, 0.0f);
+          float en[3][3];
+          bool edges = true;
+#pragma unroll
+          for (int k = 0; k < 3; ++k) {
+            const int kb = (k + 1) % 3, kc = (k + 2) % 3;
+            float nx = ay[kb] - ay[k], ny = ax[k] - ax[kb];
+            const float len = sqrtf(nx * nx + ny * ny);
+            nx /= len; ny /= len;
+            const float side = nx * (ax[kc] - ax[k]) + ny * (ay[kc] - ay[k]);
+            edges = edges && len > 1e-3f && fabsf(side) > 1e-3f;      // edge-on on screen: rectangle only
+            if (side > 0.0f) { nx = -nx; ny = -ny; }
+            const float rx = (X0 - cx) - ax[k], ry = (Y0 - cy) - ay[k];
+            const float off = se * (fabsf(nx) + fabsf(ny)) + 1e-6f * (fabsf(rx) + fabsf(ry));
+            en[k][0] = nx; en[k][1] = ny; en[k][2] = nx * rx + ny * ry - off;
+          }
+          if (edges) {
+            r0 = make_float4(en[0][0], en[0][1], en[0][2], en[1][0]);
+            r1 = make_float4(en[1][1], en[1][2], en[2][0], en[2][1]);
+            r2 = make_float4(en[2][2], X0, Y0, 1.0f);
+          }
+        }
+      }
       x0 = (int)fmaxf(fx0, 0.0f); x1 = (int)fminf(fx1, (float)(fa.cam.W - 1));
       y0 = (int)fmaxf(fy0, 0.0f); y1 = (int)fminf(fy1, (float)(fa.cam.H - 1));
     }
@@ -135,6 +230,7 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   if (!mine) return;
   unsigned k = base + incl - mine;
   if (base + total > fa.rast_cap) { rast[1] = 1u; return; }
+  fa.rast_rec[3 * (size_t)s] = r0; fa.rast_rec[3 * (size_t)s + 1] = r1; fa.rast_rec[3 * (size_t)s + 2] = r2;
   for (int ty = ty0; ty <= ty1; ++ty)
     for (int tx = tx0; tx <= tx1; ++tx)
       if (rast_owned(fa, tx, ty)) {
@@ -144,29 +240,66 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       }
 }
 
-__global__ void __launch_bounds__(256) k_rast_items(const DevScene sc, const FrameArgs fa) {
+// k_rast_items: one warp per item.  Cheap stage: the rectangle's samples against the edge record,
+// 32 at a time; the survivors go to the warp's queue in shared memory.  Whenever the queue holds
+// 32, every lane takes one (triangle, sample) pair and runs the exact test on it -- full warps for
+// the expensive stage whatever the rectangles look like.  Queue entries carry their triangle, so
+// the queue simply runs on across items.
+constexpr int RAST_WARPS = 8;
+
+__device__ __forceinline__ void rast_test(const DevScene &sc, const FrameArgs &fa, const uint2 q) {
+  const int px = (int)(q.y & 0xffffu), py = (int)(q.y >> 16);
+  const float4 a4 = __ldg(sc.v0 + q.x), b4 = __ldg(sc.e1 + q.x), c4 = __ldg(sc.e2 + q.x);
+  V3 o, d;
+  primary_ray(fa.cam, px, py, o, d);
+  float dist;
+  if (tri_candidate(o, d, a4, b4, c4, dist)) {
+    const unsigned long long key = ((unsigned long long)__float_as_uint(dist) << 32) | __float_as_uint(a4.w);
+    unsigned long long *dst = fa.prim + (size_t)py * fa.cam.W + px;
+    if (key < *dst) atomicMin(dst, key);
+  }
+}
+
+__global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene sc, const FrameArgs fa) {
+  __shared__ uint2 queue[RAST_WARPS][64];
   if (!rast_active(fa)) return;
   const unsigned n = fa.rast[0];
-  const int lane = threadIdx.x & 31;
-  const unsigned warps = gridDim.x * (256 / 32);
-  for (unsigned i = blockIdx.x * (256 / 32) + (threadIdx.x >> 5); i < n; i += warps) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const unsigned lt = (1u << lane) - 1u;
+  const unsigned warps = gridDim.x * RAST_WARPS;
+  uint2 *Q = queue[wid];
+  int qn = 0;                                   // warp-uniform
+  for (unsigned i = blockIdx.x * RAST_WARPS + wid; i < n; i += warps) {
     const uint4 it = __ldg(fa.rast_items + i);
     const int x0 = (int)(it.y & 0xffffu), y0 = (int)(it.y >> 16), x1 = (int)(it.z & 0xffffu), y1 = (int)(it.z >> 16);
     const int w = x1 - x0 + 1, cnt = w * (y1 - y0 + 1);
-    const float4 a4 = __ldg(sc.v0 + it.x), b4 = __ldg(sc.e1 + it.x), c4 = __ldg(sc.e2 + it.x);
-    const unsigned id = __float_as_uint(a4.w);
-    for (int k = lane; k < cnt; k += 32) {
-      const int py = y0 + k / w, px = x0 + k % w;
-      V3 o, d;
-      primary_ray(fa.cam, px, py, o, d);
-      float dist;
-      if (tri_candidate(o, d, a4, b4, c4, dist)) {
-        const unsigned long long key = ((unsigned long long)__float_as_uint(dist) << 32) | id;
-        unsigned long long *dst = fa.prim + (size_t)py * fa.cam.W + px;
-        if (key < *dst) atomicMin(dst, key);
+    const unsigned rw = 65536u / (unsigned)w + 1u;          // k / w == (k * rw) >> 16 for k < 1024, w <= 32
+    const float4 r0 = __ldg(fa.rast_rec + 3 * (size_t)it.x), r1 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 1),
+                 r2 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 2);
+    const bool edges = r2.w != 0.0f;
+    const float ox = (float)x0 - r2.y, oy = (float)y0 - r2.z;     // item corner relative to the record's origin
+    for (int k0 = 0; k0 < cnt; k0 += 32) {
+      const int k = k0 + lane;
+      const int ry = (int)(((unsigned)k * rw) >> 16), rx = k - ry * w;
+      bool in = k < cnt;
+      if (edges) {
+        const float dx = ox + (float)rx, dy = oy + (float)ry;
+        in = in && r0.x * dx + r0.y * dy + r0.z <= 0.0f && r0.w * dx + r1.x * dy + r1.y <= 0.0f &&
+             r1.z * dx + r1.w * dy + r2.x <= 0.0f;
+      }
+      const unsigned mask = __ballot_sync(0xffffffffu, in);
+      if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + ry) << 16));
+      qn += __popc(mask);
+      __syncwarp();
+      if (qn >= 32) {
+        qn -= 32;
+        const uint2 q = Q[qn + lane];
+        __syncwarp();
+        rast_test(sc, fa, q);
       }
     }
   }
+  if (lane < qn) rast_test(sc, fa, Q[lane]);
 }
 
 // The primary hit of sample (px, py) from the record (+ the straddlers, tested like any leaf).

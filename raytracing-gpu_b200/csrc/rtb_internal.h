@@ -126,6 +126,7 @@ struct FrameArgs {
   unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
   uint4 *rast_items;              // (slot, x0 | y0 << 16, x1 | y1 << 16, -) rectangles clipped to 32x32-sample tiles
   unsigned rast_cap;              // capacity of rast_items
+  float4 *rast_rec;               // 3 per triangle slot: edge record of the projected triangle (raster.cuh)
   unsigned *rast;                 // counters and flags (raster.cuh RAST_WORDS)
   float rast_eps;                 // box inflation: the ray-time margin at this frame's farthest origin
   unsigned rast_area_factor;      // give up when the rectangles cover more than this many times the frame
