@@ -130,6 +130,82 @@ __global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const Lig
     }
 }
 
+// Edge record of a triangle in one light's projection: rec[3 slot + 0..2] = (n0x, n0y, c0, n1x)
+// (n1y, c1, n2x, n2y) (c2, -, -, -); a ray whose point (x, y) has n . (x, y) + c > 0 for one of the
+// three edges cannot be accepted by the rounded test and skips the triangle without touching it.
+// The triangle behind the edges is the region of the triangle's plane where the rounded test can
+// accept (derivation in raster.cuh, k_rast_setup; the direction of a shadow ray is not normalised,
+// gpu/light.cu:68-120, but u and v do not depend on its length): |origin - vertex| is bounded by
+// the scene's diagonal, the incidence is that of the light's direction (1) or of the line from
+// the light to the farthest corner (2).  Needle-padded triangles, triangles seen edge-on and
+// (point lights) triangles near the light's plane get the record that accepts every point.
+__global__ void __launch_bounds__(256) k_lg_records(const DevScene sc, const LightGrid g, float smax, float4 *rec) {
+  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+  if (s >= sc.n_tris) return;
+  float4 r0 = make_float4(0, 0, -1, 0), r1 = make_float4(0, -1, 0, 0), r2 = make_float4(-1, 0, 0, 0);
+  const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
+  const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
+  V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
+  V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
+  const V3 lo0 = lo, hi0 = hi;
+  sliver_pad(v, sc.pad_unit, lo, hi);
+  bool plain = lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z;
+  const V3 n = vcross(mk(b4), mk(c4));
+  const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
+  float cosine, far = 0.0f;
+  if (g.kind == 1) cosine = fabsf(vdot(n, mk(g.az))) / ln;
+  else {
+    const V3 p0 = vsub(mk(g.org), v[0]);
+    far = fmaxf(vlen(p0), fmaxf(vlen(vsub(mk(g.org), v[1])), vlen(vsub(mk(g.org), v[2])))) + 6.0f * (l1 + l2);
+    cosine = fabsf(vdot(n, p0)) / (ln * far);
+  }
+  const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
+  const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
+  plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> no record
+  if (plain) {
+    const float dw = du + dv + 2.4e-7f;
+    const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
+                     vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
+                     vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
+    float ax[3], ay[3], den[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) lg_project(g, P[k], ax[k], ay[k], den[k]);
+    bool ok = true;
+    if (g.kind == 2) {
+      const float near = fminf(fabsf(den[0]), fminf(fabsf(den[1]), fabsf(den[2])));
+      ok = den[0] * den[1] > 0.0f && den[0] * den[2] > 0.0f && near > 1e-3f * far;
+    }
+    const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
+    ok = ok && big < 1e30f;
+    float en[3][3], longest = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int kb = (k + 1) % 3;
+      longest = fmaxf(longest, fmaxf(fabsf(ax[kb] - ax[k]), fabsf(ay[kb] - ay[k])));
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int kb = (k + 1) % 3, kc = (k + 2) % 3;
+      float nx = ay[kb] - ay[k], ny = ax[k] - ax[kb];
+      const float len = sqrtf(nx * nx + ny * ny);
+      nx /= len; ny /= len;
+      const float side = nx * (ax[kc] - ax[k]) + ny * (ay[kc] - ay[k]);
+      ok = ok && len > 0.0f && fabsf(side) > 1e-3f * longest;       // edge-on in this projection: no record
+      if (side > 0.0f) { nx = -nx; ny = -ny; }
+      // g.slack: rounding of the projection, ray side and triangle side, and of the ray's direction
+      // (lg_rect); the last term: rounding of n . (x, y) + c at coordinates of this size
+      const float off = (g.slack + 1e-6f * big) * (fabsf(nx) + fabsf(ny));
+      en[k][0] = nx; en[k][1] = ny; en[k][2] = -(nx * ax[k] + ny * ay[k]) - off;
+    }
+    if (ok) {
+      r0 = make_float4(en[0][0], en[0][1], en[0][2], en[1][0]);
+      r1 = make_float4(en[1][1], en[1][2], en[2][0], en[2][1]);
+      r2 = make_float4(en[2][2], 0, 0, 0);
+    }
+  }
+  rec[3 * (size_t)s] = r0; rec[3 * (size_t)s + 1] = r1; rec[3 * (size_t)s + 2] = r2;
+}
+
 // 1: some candidate on the ray, 0: none, -1: this ray has to walk the tree (its point is off the grid)
 __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, const V3 o, const V3 d) {
   float x, y, den;
@@ -156,6 +232,20 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
       const uint32_t r = __ldg(&g.entries[base + k].y);
       const float rx0 = (float)(r & 255u), rx1 = (float)((r >> 8) & 255u), ry0 = (float)((r >> 16) & 255u), ry1 = (float)(r >> 24);
       if (!(qx < rx0 - 0.01f || qx > rx1 + 0.01f || qy < ry0 - 0.01f || qy > ry1 + 0.01f)) mask |= 1u << k;
+    }
+    // ... then the edge records of the survivors (two 16-byte loads and three dot products each),
+    // again a loop of its own: what is left for the exact test is a fraction of the rectangle hits
+    if (g.rec) {
+      uint32_t m = mask;
+      while (m) {
+        const uint32_t k = (uint32_t)__ffs((int)m) - 1u;
+        m &= m - 1u;
+        const uint32_t slot = __ldg(&g.entries[base + k].x);
+        const float4 r0 = __ldg(g.rec + 3 * (size_t)slot), r1 = __ldg(g.rec + 3 * (size_t)slot + 1);
+        const float c2 = __ldg(&g.rec[3 * (size_t)slot + 2].x);
+        if (r0.x * x + r0.y * y + r0.z > 0.0f || r0.w * x + r1.x * y + r1.y > 0.0f || r1.z * x + r1.w * y + c2 > 0.0f)
+          mask &= ~(1u << k);
+      }
     }
     while (mask) {
       const uint32_t k = (uint32_t)__ffs((int)mask) - 1u;

@@ -28,9 +28,6 @@ constexpr int RAST_TILE = 32;                 // samples
 #define RTB_RAST_HULL 1
 #endif
 constexpr bool RAST_HULL = RTB_RAST_HULL != 0;
-constexpr float RAST_HULL_MIN_COS = 1.0f / 16;   // flatter than this: the box only
-constexpr float RAST_RAY_C = 16.0f;              // distance between the rounded ray and the line through pos and the sample, in 2^-24 |s|
-constexpr float RAST_HULL_C = 14.0f;             // rounding of u and v in units of 2^-24 |s| |e| / |a|: twice the first-order bound
 constexpr unsigned RAST_STRADDLE_MAX = 16;
 constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
 // rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 straddler count, 8.. straddler slots
@@ -128,13 +125,13 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       const V3 n = vcross(mk(b4), mk(c4)), p0 = vsub(pos, v[0]);
       const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
       const float far0 = fmaxf(vlen(p0), fmaxf(vlen(vsub(pos, v[1])), vlen(vsub(pos, v[2]))));
-      const float far = far0 + 0.25f * (l1 + l2);                       // the grown corners are a little farther
+      const float far = far0 + 6.0f * (l1 + l2);                        // the grown corners are farther (du, dv < 2 below)
       const float cosine = fabsf(vdot(n, p0)) / (ln * far);
       // |origin - vertex| <= |origin - pos| + |pos - vertex|, origins lie within the frame's corners
       const float smax = sqrtf(Lw * Lw + cx * cx + cy * cy) + far;
       const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
       const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
-      plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 0.25f && dv < 0.25f;       // NaN -> box only
+      plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> box only
       if (plain) {
         const float dw = du + dv + 2.4e-7f;
         const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),

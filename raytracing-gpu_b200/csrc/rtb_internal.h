@@ -73,6 +73,7 @@ struct LightGrid {
   int nx, ny;
   const uint32_t *cell_start;   // [nx * ny + 1]
   const uint2 *entries;         // (triangle slot, its rectangle inside the cell), cell by cell
+  const float4 *rec;            // 3 per triangle slot: edge record in this projection (lightgrid.cuh), or nullptr
   uint32_t n_large;             // triangles every ray tests: they cover too many cells or cross the light's plane
   uint32_t large[LG_LARGE_MAX];
 };

@@ -15,7 +15,7 @@ struct SceneStore {
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
   uint32_t *order = nullptr;            // slot -> global triangle id
   LightGrid *lgrids = nullptr;          // device array [n_lights] (lightgrid.cuh)
-  void *lgrid_mem[16] = {nullptr};      // cell_start / entries of up to 8 grids
+  void *lgrid_mem[24] = {nullptr};      // cell_start / entries / edge records of up to 8 grids
   int n_lgrids = 0;
   unsigned long long lgrid_entries = 0, lgrid_cells = 0;
   float lgrid_margin_k = 0;             // ray-time margin the grids were built for

@@ -681,6 +681,10 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
   const uint32_t n = S.n_tris;
   const float eps = (get_margin_k() + 2.0f) * 1.1920929e-7f * (2.001f * S.abs_max);   // trace_tree's margin at any origin inside the scene
   const unsigned blocks = (n + 255) / 256;
+  // |shadow-ray origin - vertex| <= the scene's diagonal (origins are hit points)
+  const float diag = 1.001f * sqrtf((bmax[0] - bmin[0]) * (bmax[0] - bmin[0]) + (bmax[1] - bmin[1]) * (bmax[1] - bmin[1]) +
+                                    (bmax[2] - bmin[2]) * (bmax[2] - bmin[2])) + 1e-30f;
+  static const bool lg_records = [] { const char *e = getenv("RTB_LG_RECORDS"); return !(e && atoi(e) == 0); }();
   int built = 0, mem = 0;
   auto unit = [](float x, float y, float z, float3 &o) {
     const float r = sqrtf(x * x + y * y + z * z);
@@ -763,6 +767,14 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     cudaFreeAsync(cursor, st);
     cudaFreeAsync(d_b, st);
     g.cell_start = counts; g.entries = entries;
+    if (lg_records) {
+      float4 *rec = nullptr;
+      RTB_CUDA(cudaMallocAsync((void **)&rec, (size_t)n * 3 * sizeof(float4), st));
+      k_lg_records<<<blocks, 256, 0, st>>>(sc, g, diag, rec);
+      RTB_CUDA(cudaGetLastError());
+      g.rec = rec;
+      S.lgrid_mem[mem++] = rec;
+    }
     g.n_large = state[0] < (uint32_t)LG_LARGE_MAX ? state[0] : (uint32_t)LG_LARGE_MAX;
     for (uint32_t k = 0; k < g.n_large; ++k) g.large[k] = state[2 + k];
     S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
