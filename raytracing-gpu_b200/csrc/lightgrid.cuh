@@ -30,9 +30,52 @@ __device__ __forceinline__ void lg_project(const LightGrid &g, const V3 X, float
   }
 }
 
-// The projected rectangle of triangle slot s's culling box.  false: the box has no rectangle
+// The region of triangle slot s's plane where the rounded test can accept a shadow ray of this
+// light, as a triangle in the light's projection (corners ax, ay).  Derivation: raster.cuh,
+// k_rast_setup; the direction of a shadow ray is not normalised (gpu/light.cu:68-120) but u and v do
+// not depend on its length; |origin - vertex| <= smax, the scene's diagonal (origins are hit
+// points); the incidence is that of the light's direction (1) or of the line from the light to the
+// farthest corner (2).  false: no such region (needle-padded triangle, edge-on, near the light's
+// plane) -- the triangle is culled by its box alone.
+__device__ __forceinline__ bool lg_region(const LightGrid &g, float pad_unit, float smax, const float4 a4, const float4 b4,
+                                          const float4 c4, float (&ax)[3], float (&ay)[3]) {
+  const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
+  V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
+  V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
+  const V3 lo0 = lo, hi0 = hi;
+  sliver_pad(v, pad_unit, lo, hi);
+  if (!(lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z)) return false;
+  const V3 n = vcross(mk(b4), mk(c4));
+  const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
+  float cosine, far = 0.0f;
+  if (g.kind == 1) cosine = fabsf(vdot(n, mk(g.az))) / ln;
+  else {
+    const V3 p0 = vsub(mk(g.org), v[0]);
+    far = fmaxf(vlen(p0), fmaxf(vlen(vsub(mk(g.org), v[1])), vlen(vsub(mk(g.org), v[2])))) + 6.0f * (l1 + l2);
+    cosine = fabsf(vdot(n, p0)) / (ln * far);
+  }
+  const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
+  const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
+  if (!(ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f)) return false;       // NaN -> false
+  const float dw = du + dv + 2.4e-7f;
+  const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
+                   vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
+                   vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
+  float den[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) lg_project(g, P[k], ax[k], ay[k], den[k]);
+  if (g.kind == 2) {
+    const float near = fminf(fabsf(den[0]), fminf(fabsf(den[1]), fabsf(den[2])));
+    if (!(den[0] * den[1] > 0.0f && den[0] * den[2] > 0.0f && near > 1e-3f * far)) return false;
+  }
+  const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
+  return big < 1e30f;
+}
+
+// The projected rectangle of triangle slot s's culling box, intersected with the bounds of its
+// region (lg_region) when it has one.  false: the box has no rectangle
 // (it crosses the plane through a point light) and must be tested by every ray.
-__device__ __forceinline__ bool lg_rect(const DevScene &sc, const LightGrid &g, float eps, uint32_t s, float &x0,
+__device__ __forceinline__ bool lg_rect(const DevScene &sc, const LightGrid &g, float eps, float smax, uint32_t s, float &x0,
                                         float &x1, float &y0, float &y1) {
   const float INFF = __builtin_huge_valf();
   const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
@@ -58,6 +101,13 @@ __device__ __forceinline__ bool lg_rect(const DevScene &sc, const LightGrid &g, 
   if (!(x0 > -1e30f && x1 < 1e30f && y0 > -1e30f && y1 < 1e30f)) return false;
   // the rounding of the projection itself, ray side and box side (g.slack: build_light_grids)
   x0 -= g.slack; x1 += g.slack; y0 -= g.slack; y1 += g.slack;
+  float ax[3], ay[3];
+  if (smax > 0.0f && lg_region(g, sc.pad_unit, smax, a4, b4, c4, ax, ay)) {
+    const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
+    const float sl = g.slack + 1e-6f * big;
+    x0 = fmaxf(x0, fminf(ax[0], fminf(ax[1], ax[2])) - sl); x1 = fminf(x1, fmaxf(ax[0], fmaxf(ax[1], ax[2])) + sl);
+    y0 = fmaxf(y0, fminf(ay[0], fminf(ay[1], ay[2])) - sl); y1 = fminf(y1, fmaxf(ay[0], fmaxf(ay[1], ay[2])) + sl);
+  }
   return true;
 }
 
@@ -73,13 +123,13 @@ __device__ __forceinline__ bool lg_cells(const LightGrid &g, float x0, float x1,
 }
 
 // bounds of all rectangles: out[0..3] = min x, max x, min y, max y (ordered uint)
-__global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const LightGrid g, float eps, uint32_t *out) {
+__global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t *out) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   const float INFF = __builtin_huge_valf();
   float x0 = INFF, x1 = -INFF, y0 = INFF, y1 = -INFF;
   if (s < sc.n_tris) {
     float a0, a1, b0, b1;
-    if (lg_rect(sc, g, eps, s, a0, a1, b0, b1)) { x0 = a0; x1 = a1; y0 = b0; y1 = b1; }
+    if (lg_rect(sc, g, eps, smax, s, a0, a1, b0, b1)) { x0 = a0; x1 = a1; y0 = b0; y1 = b1; }
   }
   const uint32_t m0 = __reduce_min_sync(0xffffffffu, f2ord(x0)), m1 = __reduce_max_sync(0xffffffffu, f2ord(x1));
   const uint32_t m2 = __reduce_min_sync(0xffffffffu, f2ord(y0)), m3 = __reduce_max_sync(0xffffffffu, f2ord(y1));
@@ -104,13 +154,13 @@ __device__ __forceinline__ uint32_t lg_pack(const LightGrid &g, int i, int j, fl
 }
 
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const LightGrid g, float eps, uint32_t *counts,
+__global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t *counts,
                                                     uint32_t *state, const uint32_t *cell_start, uint2 *entries) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   if (s >= sc.n_tris) return;
   float x0, x1, y0, y1;
   int i0, i1, j0, j1;
-  bool large = !lg_rect(sc, g, eps, s, x0, x1, y0, y1);
+  bool large = !lg_rect(sc, g, eps, smax, s, x0, x1, y0, y1);
   if (!large) {
     if (!lg_cells(g, x0, x1, y0, y1, i0, i1, j0, j1)) return;       // entirely outside the grid
     large = (unsigned)(i1 - i0 + 1) * (unsigned)(j1 - j0 + 1) > LG_CELLS_MAX;
@@ -132,51 +182,18 @@ __global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const Lig
 
 // Edge record of a triangle in one light's projection: rec[3 slot + 0..2] = (n0x, n0y, c0, n1x)
 // (n1y, c1, n2x, n2y) (c2, -, -, -); a ray whose point (x, y) has n . (x, y) + c > 0 for one of the
-// three edges cannot be accepted by the rounded test and skips the triangle without touching it.
-// The triangle behind the edges is the region of the triangle's plane where the rounded test can
-// accept (derivation in raster.cuh, k_rast_setup; the direction of a shadow ray is not normalised,
-// gpu/light.cu:68-120, but u and v do not depend on its length): |origin - vertex| is bounded by
-// the scene's diagonal, the incidence is that of the light's direction (1) or of the line from
-// the light to the farthest corner (2).  Needle-padded triangles, triangles seen edge-on and
-// (point lights) triangles near the light's plane get the record that accepts every point.
+// three edges of the triangle's region (lg_region) cannot be accepted by the rounded test and
+// skips the triangle without touching it.  Triangles without a region, and regions seen edge-on,
+// get the record that accepts every point.
 __global__ void __launch_bounds__(256) k_lg_records(const DevScene sc, const LightGrid g, float smax, float4 *rec) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   if (s >= sc.n_tris) return;
   float4 r0 = make_float4(0, 0, -1, 0), r1 = make_float4(0, -1, 0, 0), r2 = make_float4(-1, 0, 0, 0);
   const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
-  const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
-  V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
-  V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
-  const V3 lo0 = lo, hi0 = hi;
-  sliver_pad(v, sc.pad_unit, lo, hi);
-  bool plain = lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z;
-  const V3 n = vcross(mk(b4), mk(c4));
-  const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
-  float cosine, far = 0.0f;
-  if (g.kind == 1) cosine = fabsf(vdot(n, mk(g.az))) / ln;
-  else {
-    const V3 p0 = vsub(mk(g.org), v[0]);
-    far = fmaxf(vlen(p0), fmaxf(vlen(vsub(mk(g.org), v[1])), vlen(vsub(mk(g.org), v[2])))) + 6.0f * (l1 + l2);
-    cosine = fabsf(vdot(n, p0)) / (ln * far);
-  }
-  const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
-  const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
-  plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> no record
-  if (plain) {
-    const float dw = du + dv + 2.4e-7f;
-    const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
-                     vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
-                     vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
-    float ax[3], ay[3], den[3];
-#pragma unroll
-    for (int k = 0; k < 3; ++k) lg_project(g, P[k], ax[k], ay[k], den[k]);
-    bool ok = true;
-    if (g.kind == 2) {
-      const float near = fminf(fabsf(den[0]), fminf(fabsf(den[1]), fabsf(den[2])));
-      ok = den[0] * den[1] > 0.0f && den[0] * den[2] > 0.0f && near > 1e-3f * far;
-    }
+  float ax[3], ay[3];
+  if (lg_region(g, sc.pad_unit, smax, a4, b4, c4, ax, ay)) {
     const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
-    ok = ok && big < 1e30f;
+    bool ok = true;
     float en[3][3], longest = 0.0f;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {

@@ -724,7 +724,7 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     const uint32_t init[4] = {0xffffffffu, 0u, 0xffffffffu, 0u};
     uint32_t hb[4];
     RTB_CUDA(cudaMemcpyAsync(d_b, init, sizeof init, cudaMemcpyHostToDevice, st));
-    k_lg_bounds<<<blocks, 256, 0, st>>>(sc, g, eps, d_b);
+    k_lg_bounds<<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, d_b);
     RTB_CUDA(cudaMemcpyAsync(hb, d_b, sizeof hb, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
     float x0 = ord2f(hb[0]), x1 = ord2f(hb[1]), y0 = ord2f(hb[2]), y1 = ord2f(hb[3]);
@@ -748,7 +748,7 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     RTB_CUDA(cudaMallocAsync((void **)&scratch, ssw * 4, st));
     RTB_CUDA(cudaMemsetAsync(counts, 0, (cells + 1) * 4, st));
     RTB_CUDA(cudaMemsetAsync(d_b, 0, 32 * 4, st));
-    k_lg_scatter<false><<<blocks, 256, 0, st>>>(sc, g, eps, counts, d_b, nullptr, nullptr);
+    k_lg_scatter<false><<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, counts, d_b, nullptr, nullptr);
     int rc = dev_exclusive_scan_u32(counts, cells + 1, scratch, ssw, false, st, nullptr);
     uint32_t total = 0, state[2 + LG_LARGE_MAX];
     if (!rc) {
@@ -762,7 +762,7 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     RTB_CUDA(cudaMallocAsync((void **)&entries, (size_t)total * sizeof(uint2), st));
     RTB_CUDA(cudaMallocAsync((void **)&cursor, cells * 4, st));
     RTB_CUDA(cudaMemsetAsync(cursor, 0, cells * 4, st));
-    k_lg_scatter<true><<<blocks, 256, 0, st>>>(sc, g, eps, cursor, d_b, counts, entries);
+    k_lg_scatter<true><<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, cursor, d_b, counts, entries);
     RTB_CUDA(cudaGetLastError());
     cudaFreeAsync(cursor, st);
     cudaFreeAsync(d_b, st);
