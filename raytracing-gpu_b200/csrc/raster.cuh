@@ -149,15 +149,20 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
           hx0 = fminf(hx0, ax[k]); hx1 = fmaxf(hx1, ax[k]); hy0 = fminf(hy0, ay[k]); hy1 = fmaxf(hy1, ay[k]);
         }
         const float big = fmaxf(fmaxf(fabsf(hx0), fabsf(hx1)), fmaxf(fabsf(hy0), fabsf(hy1)));
-        // The ray itself is rounded: its origin by about a spacing of |o| (a thousandth of a sample:
-        // the image plane's unit is the sample) and its direction, normalize(pos - o), by an angle of
-        // about 3 eps, i.e. across the ray by 3 eps |s| at the triangle.  RAST_RAY_C = 16 eps |s| bounds
-        // both with a factor of two; a displacement of that size at depth >= dnear moves the
-        // projection by at most |delta| sqrt(L^2 + x^2) / depth (1.3: second order, dnear > 8 delta).
+        // The ray itself is rounded.  Its origin: three roundings at the size of |o|, about 1.5
+        // spacings of |o| per coordinate -- thousandths of a sample (the image plane's unit is the
+        // sample), and the line pivots about pos, so behind pos that shrinks by depth / L.  Its
+        // direction normalize(pos - o): the subtraction and the three divisions round each coordinate
+        // by eps relative (the length is a common factor), an angle of about 2 eps, i.e. 2 eps |s| across
+        // the ray at the triangle.  RAST_RAY_C = 8 eps |s| bounds the sum with a factor of three; a
+        // displacement of that size at depth >= dnear moves the projection by at most
+        // |delta| sqrt(L^2 + x^2) / depth (1.3: second order, dnear > 8 delta).
         const float delta = RAST_RAY_C * 5.9604645e-8f * smax;
         ok = ok && dnear > 0.25f * near && dnear > 8.0f * delta && big < 1e6f;
         if (ok) {
-          const float se = 1.3f * delta * sqrtf(Lw * Lw + big * big) / dnear + 0.02f + 4e-7f * big;
+          const float sr = 1.3f * delta * sqrtf(Lw * Lw + big * big) / dnear;      // a distance: any direction
+          const float sb = 0.02f + 4e-7f * big;                                    // per coordinate
+          const float se = sr + sb;
           fx0 = fmaxf(fx0, ceilf(hx0 + cx - se)); fx1 = fminf(fx1, floorf(hx1 + cx + se));
           fy0 = fmaxf(fy0, ceilf(hy0 + cy - se)); fy1 = fminf(fy1, floorf(hy1 + cy + se));
           const float X0 = fmaxf(fx0, 0.0f), Y0 = fmaxf(fy0, 0.0f);
@@ -173,7 +178,7 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
             edges = edges && len > 1e-3f && fabsf(side) > 1e-3f;      // edge-on on screen: rectangle only
             if (side > 0.0f) { nx = -nx; ny = -ny; }
             const float rx = (X0 - cx) - ax[k], ry = (Y0 - cy) - ay[k];
-            const float off = se * (fabsf(nx) + fabsf(ny)) + 1e-6f * (fabsf(rx) + fabsf(ry));
+            const float off = sr + sb * (fabsf(nx) + fabsf(ny)) + 1e-6f * (fabsf(rx) + fabsf(ry));
             en[k][0] = nx; en[k][1] = ny; en[k][2] = nx * rx + ny * ry - off;
           }
           if (edges) {
