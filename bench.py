@@ -350,7 +350,8 @@ def run_ours(args):
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(traffic_file):
             try:
-                roofline["traffic"] = json.load(open(traffic_file)).get("k_frame_dram_bytes_per_launch")
+                tj = json.load(open(traffic_file))
+                roofline["traffic"] = tj.get("frame_dram_bytes", tj.get("k_frame_dram_bytes_per_launch"))
             except Exception:
                 pass
         if roofline["traffic"] and world == 1:
@@ -358,7 +359,7 @@ def run_ours(args):
             gbs = roofline["traffic"] / kern_s / 1e9
             roofline["hbm"] = {"achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
                                "note": "dram__bytes_read+write of one ncu --set full capture (profiles/traffic.json) / "
-                                       "live launch duration: HBM does not bind this kernel"}
+                                       "live duration of the frame's launches: HBM does not bind these kernels"}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
