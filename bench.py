@@ -171,6 +171,8 @@ def run_ours(args):
         import torch
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # the version banner goes to stdout, where the one JSON line belongs
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     if pyrtb.device_count() <= local_rank:
         raise SystemExit("bench.py needs a GPU per rank: librtb200 has no CPU fallback")

@@ -182,7 +182,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
   if (!RTB_BVH4 && want_raster && S.has_tree && S.inv_order && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
-      o.frame_kernel == RTB_KERNEL_PER_SAMPLE) {
+      o.frame_kernel == RTB_KERNEL_PER_SAMPLE && fa.cam.W <= 65535 && fa.cam.H <= 65535) {      // items hold 16-bit sample corners
     // a frame of this camera that ran the pass and still walked the tree (boxes across the camera
     // plane, rectangles covering too much) says the next one will too: AUTO does not try again
     const unsigned long long key[4] = {S.camera_gen, (unsigned long long)fa.cam.W << 32 | (unsigned)fa.cam.H,
@@ -586,7 +586,8 @@ int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_o
   }
   // opts->primary == RTB_PRIMARY_RASTER: the ids the projection pass records (tests); a frame that
   // falls back to the tree reports -2 everywhere so that a test cannot pass by accident
-  if (o.primary == RTB_PRIMARY_RASTER && o.tracer == RTB_TRACER_TREE && S.has_tree && S.inv_order) {
+  if (o.primary == RTB_PRIMARY_RASTER && o.tracer == RTB_TRACER_TREE && S.has_tree && S.inv_order && S.camera.width <= 65535 &&
+      S.camera.height <= 65535) {
     FrameArgs fa;
     memset(&fa, 0, sizeof fa);
     fa.cam = camera_frame(S.camera);
