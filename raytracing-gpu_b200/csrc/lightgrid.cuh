@@ -140,17 +140,21 @@ __global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const Ligh
 
 // FILL = false: counts[cell] += 1 per covered cell, state[0] = number of large triangles (listed in
 // state[2..]), state[1] != 0: give up.  FILL = true: entries[cell_start[cell] + cursor[cell]++] = slot.
-// An entry is (slot, the rectangle clipped to the cell in 1/255 of the cell, rounded outwards): a
-// ray first checks that its point is inside that rectangle, 4 compares on 8 sequential bytes,
-// before it touches the triangle itself (3 scattered 16-byte loads and the exact test).
+// An entry is (slot, the rectangle clipped to the cell in 1/127 of the cell, rounded outwards), the
+// rectangle as four 7-bit bytes x0, 127 - x1, y0, 127 - y1: a ray turns its point into the bytes
+// floor(qx), 127 - ceil(qx), floor(qy), 127 - ceil(qy) with bit 7 set in each, and "inside" is
+// "every byte of the entry <= the ray's byte", i.e. no byte of (ray - entry) loses its bit 7: one
+// subtraction, one AND, one compare on 4 sequential bytes, before the ray touches the triangle's
+// edge record or the triangle itself (scattered 16-byte loads and the exact test).
+constexpr float LG_Q = 127.0f;
 __device__ __forceinline__ uint32_t lg_pack(const LightGrid &g, int i, int j, float x0, float x1, float y0, float y1) {
   const float cx = g.x0 + (float)i / g.inv_cell, cy = g.y0 + (float)j / g.inv_cell;
   auto q = [&](float v, float c, bool up) {
-    float t = (v - c) * g.inv_cell * 255.0f;
+    float t = (v - c) * g.inv_cell * LG_Q;
     t = up ? ceilf(t + 0.02f) : floorf(t - 0.02f);
-    return (uint32_t)fminf(fmaxf(t, 0.0f), 255.0f);
+    return (uint32_t)fminf(fmaxf(t, 0.0f), LG_Q);
   };
-  return q(x0, cx, false) | (q(x1, cx, true) << 8) | (q(y0, cy, false) << 16) | (q(y1, cy, true) << 24);
+  return q(x0, cx, false) | ((127u - q(x1, cx, true)) << 8) | (q(y0, cy, false) << 16) | ((127u - q(y1, cy, true)) << 24);
 }
 
 template <bool FILL>
@@ -236,19 +240,21 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
     if (consider<true>(sc, o, d, (int)g.large[k], b)) return 1;
   const size_t c = (size_t)(int)fj * g.nx + (int)fi;
   const uint32_t e0 = __ldg(g.cell_start + c), e1 = __ldg(g.cell_start + c + 1);
-  // the ray's point inside its cell, in the entries' units
-  const float qx = ((x - g.x0) * g.inv_cell - fi) * 255.0f, qy = ((y - g.y0) * g.inv_cell - fj) * 255.0f;
-  // Two phases per chunk of 32 entries, because the lanes of a warp walk different lists in
-  // lockstep: first only the cheap rectangle checks (a bit per entry that survives), then the
-  // exact tests of the survivors.  With one loop the warp paid a full triangle test in three of
-  // four iterations for the few lanes that had a survivor there (13 of 32 lanes active, ncu).
+  // the ray's point inside its cell as the four bytes the entries compare with (lg_pack); 0.01:
+  // rounding of the point's own position inside the cell
+  const float qx = ((x - g.x0) * g.inv_cell - fi) * LG_Q, qy = ((y - g.y0) * g.inv_cell - fj) * LG_Q;
+  auto byte = [](float v) { return (uint32_t)fminf(fmaxf(v, 0.0f), LG_Q); };
+  const uint32_t P = (byte(floorf(qx + 0.01f)) | ((127u - byte(ceilf(qx - 0.01f))) << 8) | (byte(floorf(qy + 0.01f)) << 16) |
+                      ((127u - byte(ceilf(qy - 0.01f))) << 24)) | 0x80808080u;
+  // Three phases per chunk of 32 entries, because the lanes of a warp walk different lists in
+  // lockstep: first only the cheap rectangle checks (a bit per entry that survives), ...
   for (uint32_t base = e0; base < e1; base += 32) {
     const uint32_t cnt = min(32u, e1 - base);
     uint32_t mask = 0;
+#pragma unroll 4
     for (uint32_t k = 0; k < cnt; ++k) {
       const uint32_t r = __ldg(&g.entries[base + k].y);
-      const float rx0 = (float)(r & 255u), rx1 = (float)((r >> 8) & 255u), ry0 = (float)((r >> 16) & 255u), ry1 = (float)(r >> 24);
-      if (!(qx < rx0 - 0.01f || qx > rx1 + 0.01f || qy < ry0 - 0.01f || qy > ry1 + 0.01f)) mask |= 1u << k;
+      if (((P - r) & 0x80808080u) == 0x80808080u) mask |= 1u << k;
     }
     // ... then the edge records of the survivors (two 16-byte loads and three dot products each),
     // again a loop of its own: what is left for the exact test is a fraction of the rectangle hits
