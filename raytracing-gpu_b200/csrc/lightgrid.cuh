@@ -122,9 +122,12 @@ __device__ __forceinline__ bool lg_cells(const LightGrid &g, float x0, float x1,
   return true;
 }
 
-// bounds of all rectangles: out[0..3] = min x, max x, min y, max y (ordered uint)
-__global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t *out) {
-  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+// bounds of the rectangles of every stride-th triangle: out[0..3] = min x, max x, min y, max y
+// (ordered uint).  The grid does not have to cover every rectangle: k_lg_scatter clips to the grid
+// and a ray whose point is off the grid walks the tree, so big scenes look at a sample.
+__global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t stride,
+                                                   uint32_t *out) {
+  const uint32_t s = (blockIdx.x * 256 + threadIdx.x) * stride;
   const float INFF = __builtin_huge_valf();
   float x0 = INFF, x1 = -INFF, y0 = INFF, y1 = -INFF;
   if (s < sc.n_tris) {

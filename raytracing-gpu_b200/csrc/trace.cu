@@ -724,10 +724,16 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     const uint32_t init[4] = {0xffffffffu, 0u, 0xffffffffu, 0u};
     uint32_t hb[4];
     RTB_CUDA(cudaMemcpyAsync(d_b, init, sizeof init, cudaMemcpyHostToDevice, st));
-    k_lg_bounds<<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, d_b);
+    // every 16th triangle from 2^20 on (slots are in spatial order: a regular sample of the surface)
+    const uint32_t bstride = n >= (1u << 20) ? 16u : 1u;
+    k_lg_bounds<<<(n / bstride + 256) / 256, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, bstride, d_b);
     RTB_CUDA(cudaMemcpyAsync(hb, d_b, sizeof hb, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
     float x0 = ord2f(hb[0]), x1 = ord2f(hb[1]), y0 = ord2f(hb[2]), y1 = ord2f(hb[3]);
+    if (bstride > 1 && x1 > x0 && y1 > y0) {      // room for what the sample missed
+      const float mx = 0.01f * (x1 - x0), my = 0.01f * (y1 - y0);
+      x0 -= mx; x1 += mx; y0 -= my; y1 += my;
+    }
     if (g.kind == 2) {
       x0 = fmaxf(x0, -LG_PERSP_LIMIT); y0 = fmaxf(y0, -LG_PERSP_LIMIT);
       x1 = fminf(x1, LG_PERSP_LIMIT); y1 = fminf(y1, LG_PERSP_LIMIT);
