@@ -92,15 +92,16 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
     const V3 u = mk(fa.cam.u), vv = mk(fa.cam.v), w = mk(fa.cam.w), pos = mk(fa.cam.pos);
     const float ww = vdot(w, w), uv = vdot(u, vv);
     const float det = 1.0f - uv * uv;                      // Gram determinant of the unit vectors u, v
-    const float Lw = fa.cam.L;
+    const float Lw = fa.cam.L, inv_det = 1.0f / det;
     auto project = [&](const V3 X, float &x, float &y, float &den) {
       const V3 r = vsub(pos, X);
       den = vdot(r, w);
-      const float t = Lw * ww / den;
+      // fast division and a reciprocal: a few more spacings of x, inside the slack below (4e-7 |x|)
+      const float t = __fdividef(Lw * ww, den);
       const V3 q = vsub(vscale(r, t), vscale(w, Lw));     // offset from the plane's centre C
       const float qu = vdot(q, u), qv = vdot(q, vv);
-      x = (qu - uv * qv) / det;
-      y = (qv - uv * qu) / det;
+      x = (qu - uv * qv) * inv_det;
+      y = (qv - uv * qu) * inv_det;
     };
     float dmin = INF, dmax = -INF, xmin = INF, xmax = -INF, ymin = INF, ymax = -INF;
 #pragma unroll
@@ -118,20 +119,38 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       // px - W/2 = x (integer division as in primary_ray: W / 2, H / 2).  Slack for the rounding of
       // the projection itself: a few float spacings of a coordinate that is at most ~1e5 samples
       const float cx = (float)(fa.cam.W / 2), cy = (float)(fa.cam.H / 2);
-      const float sx = 0.02f + 4e-7f * fmaxf(fabsf(xmin), fabsf(xmax)), sy = 0.02f + 4e-7f * fmaxf(fabsf(ymin), fabsf(ymax));
+      const float sx = 0.02f + 1e-6f * fmaxf(fabsf(xmin), fabsf(xmax)), sy = 0.02f + 1e-6f * fmaxf(fabsf(ymin), fabsf(ymax));
       float fx0 = ceilf(xmin + cx - sx), fx1 = floorf(xmax + cx + sx);
       float fy0 = ceilf(ymin + cy - sy), fy1 = floorf(ymax + cy + sy);
+      // nothing of the box on this rank's part of the screen: no region, no record, no items
+      if (plain) {
+        const int bx0 = (int)fmaxf(fx0, 0.0f), bx1 = (int)fminf(fx1, (float)(fa.cam.W - 1));
+        const int by0 = (int)fmaxf(fy0, 0.0f), by1 = (int)fminf(fy1, (float)(fa.cam.H - 1));
+        plain = bx1 >= bx0 && by1 >= by0;
+        if (plain && fa.nranks > 1) {
+          const int t0 = bx0 / RAST_TILE, t1 = bx1 / RAST_TILE, u0 = by0 / RAST_TILE, u1 = by1 / RAST_TILE;
+          if ((t1 - t0 + 1) * (u1 - u0 + 1) <= 16) {
+            bool mine = false;
+            for (int ty = u0; ty <= u1; ++ty)
+              for (int tx = t0; tx <= t1; ++tx) mine = mine || rast_owned(fa, tx, ty);
+            plain = mine;
+          }
+        }
+      }
       // the accepted region in the triangle's plane (see above)
-      const V3 n = vcross(mk(b4), mk(c4)), p0 = vsub(pos, v[0]);
-      const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
-      const float far0 = fmaxf(vlen(p0), fmaxf(vlen(vsub(pos, v[1])), vlen(vsub(pos, v[2]))));
-      const float far = far0 + 6.0f * (l1 + l2);                        // the grown corners are farther (du, dv < 2 below)
-      const float cosine = fabsf(vdot(n, p0)) / (ln * far);
-      // |origin - vertex| <= |origin - pos| + |pos - vertex|, origins lie within the frame's corners
-      const float smax = sqrtf(Lw * Lw + cx * cx + cy * cy) + far;
-      const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
-      const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
-      plain = plain && ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> box only
+      float du = 0.0f, dv = 0.0f, smax = 0.0f;
+      if (plain) {
+        const V3 n = vcross(mk(b4), mk(c4)), p0 = vsub(pos, v[0]);
+        const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
+        const float far0 = fmaxf(vlen(p0), fmaxf(vlen(vsub(pos, v[1])), vlen(vsub(pos, v[2]))));
+        const float far = far0 + 6.0f * (l1 + l2);                        // the grown corners are farther (du, dv < 2 below)
+        const float cosine = fabsf(vdot(n, p0)) / (ln * far);
+        // |origin - vertex| <= |origin - pos| + |pos - vertex|, origins lie within the frame's corners
+        smax = sqrtf(Lw * Lw + cx * cx + cy * cy) + far;
+        du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
+        dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
+        plain = ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> box only
+      }
       if (plain) {
         const float dw = du + dv + 2.4e-7f;
         const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
@@ -161,7 +180,7 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
         ok = ok && dnear > 0.25f * near && dnear > 8.0f * delta && big < 1e6f;
         if (ok) {
           const float sr = 1.3f * delta * sqrtf(Lw * Lw + big * big) / dnear;      // a distance: any direction
-          const float sb = 0.02f + 4e-7f * big;                                    // per coordinate
+          const float sb = 0.02f + 1e-6f * big;                                    // per coordinate
           const float se = sr + sb;
           fx0 = fmaxf(fx0, ceilf(hx0 + cx - se)); fx1 = fminf(fx1, floorf(hx1 + cx + se));
           fy0 = fmaxf(fy0, ceilf(hy0 + cy - se)); fy1 = fminf(fy1, floorf(hy1 + cy + se));
