@@ -233,3 +233,42 @@ def test_shadow_ray_grids_give_the_tree_walk_frames(gpu, scene):
     finally:
         with_grids.close()
         without.close()
+
+
+ONE_FRAME = 8                # include/rtb200.h RTB_BUILD_ONE_FRAME
+
+
+def test_one_frame_builds_make_light_grids_only_when_the_frame_repays_them(gpu):
+    """rtb_render() builds for one frame: light grids from 4 samples per triangle on, and the same bytes"""
+    hs = pyrtb.HostScene.terrain(200, 640, 360)          # 80 000 triangles, 2.07 M samples at 3x3
+    ref = pyrtb.DeviceScene(hs, 3, flags=NO_LIGHT_GRIDS)
+    one = pyrtb.DeviceScene(hs, 3, flags=ONE_FRAME)
+    try:
+        assert one.raster_state()["light_grids"] == 2
+        want = _frame(ref, TREE)
+        assert np.array_equal(one.render(), want)
+        assert np.array_equal(pyrtb.render_oneshot(hs, 3), want)
+    finally:
+        ref.close(); one.close()
+    small = pyrtb.HostScene.terrain(200, 96, 54)         # 46 656 samples: a tree walk per shadow ray is cheaper
+    ds = pyrtb.DeviceScene(small, 3, flags=ONE_FRAME)
+    ref = pyrtb.DeviceScene(small, 3, flags=NO_LIGHT_GRIDS)
+    try:
+        assert ds.raster_state()["light_grids"] == 0
+        assert np.array_equal(ds.render(), _frame(ref, TREE))
+    finally:
+        ds.close(); ref.close()
+
+
+def test_grid_extent_from_a_sample_of_the_triangles(gpu):
+    """from 2^20 triangles on the grids' extent comes from every 16th rectangle: rays whose point
+    falls off the grid walk the tree, triangles beyond it are clipped -- same frame"""
+    hs = pyrtb.HostScene.terrain(750, 480, 270)          # 1 125 000 triangles
+    a = pyrtb.DeviceScene(hs, 3)
+    b = pyrtb.DeviceScene(hs, 3, flags=NO_LIGHT_GRIDS)
+    try:
+        assert a.raster_state()["light_grids"] == 2
+        for primary in (TREE, AUTO):
+            assert np.array_equal(_frame(a, primary), _frame(b, primary))
+    finally:
+        a.close(); b.close()
