@@ -267,6 +267,8 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
 // the expensive stage whatever the rectangles look like.  Queue entries carry their triangle, so
 // the queue simply runs on across items.
 constexpr int RAST_WARPS = 8;
+// k / w == (k * c_rast_rw[w]) >> 16 for k < 1024, w <= 32: 65536 / w + 1 (the division costs 20 instructions per item)
+__constant__ unsigned c_rast_rw[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
 
 __device__ __forceinline__ void rast_test(const DevScene &sc, const FrameArgs &fa, const uint2 q) {
   const int px = (int)(q.y & 0xffffu), py = (int)(q.y >> 16);
@@ -294,7 +296,7 @@ __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene s
     const uint4 it = __ldg(fa.rast_items + i);
     const int x0 = (int)(it.y & 0xffffu), y0 = (int)(it.y >> 16), x1 = (int)(it.z & 0xffffu), y1 = (int)(it.z >> 16);
     const int w = x1 - x0 + 1, cnt = w * (y1 - y0 + 1);
-    const unsigned rw = 65536u / (unsigned)w + 1u;          // k / w == (k * rw) >> 16 for k < 1024, w <= 32
+    const unsigned rw = c_rast_rw[w];
     const float4 r0 = __ldg(fa.rast_rec + 3 * (size_t)it.x), r1 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 1),
                  r2 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 2);
     const bool edges = r2.w != 0.0f;
