@@ -1262,14 +1262,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     k_single_node<<<1, 1, 0, st>>>(n, S->nodes);
     ++launches;
   }
-  if (overlap) {
-    RTB_CUDA(cudaStreamWaitEvent(st, side.normals, 0));
-    k_permute<false, true><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2,
-                                              S->n0, S->n1, S->n2);
-    ++launches;
-  }
   uint32_t h_bounds[8];
-  RTB_CUDA(cudaEventRecord(e_b1, st));
   RTB_CUDA(cudaMemcpyAsync(h_bounds, d_bounds, sizeof h_bounds, cudaMemcpyDeviceToHost, st));
   RTB_CUDA(cudaStreamSynchronize(st));
   RTB_CUDA(cudaGetLastError());
@@ -1279,28 +1272,30 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   S->pad_unit = SLIVER_K * 1.1920929e-7f * (amax + S->origin_radius);     // as k_emit / k_sah_clusters compute it
   S->n_tris = n; S->n_objects = (uint32_t)n_obj; S->n_lights = (uint32_t)n_light;
   S->has_tree = tree;
-  S->upload_ms = ms_between(e_up0, e_up1);
-  S->build_ms = ms_between(e_up1, e_b1);
-  S->build_launches = launches;
   S->camera = hs->camera;
   // shadow-ray grids: resident scenes, and single frames with enough samples per triangle to repay
-  // them (C5: 2.4 ms of build per light per 10 M triangles against 80 ps saved per shadow ray, i.e.
-  // from about 3 samples per triangle; 7.5 there: one-shot render() 43.7 -> 38 ms)
+  // them (C5: 1.9 ms of build per light per 10 M triangles against 80 ps saved per shadow ray, i.e.
+  // from about 3 samples per triangle; 7.5 there: one-shot render() 43.7 -> 38 ms).  They need the
+  // positions only, so they are built here, while the normals of a big scene are still crossing PCIe.
   const bool one_frame_pays = (unsigned long long)hs->camera.width * (unsigned long long)hs->camera.height >= 4ull * n;
   if (tree && !(flags & RTB_BUILD_NO_LIGHT_GRIDS) && (!(flags & RTB_BUILD_ONE_FRAME) || one_frame_pays)) {
     float bmin[3], bmax[3];
     for (int k = 0; k < 3; ++k) { bmin[k] = ord2f(h_bounds[k]); bmax[k] = ord2f(h_bounds[3 + k]); }
-    cudaEvent_t e_g0 = nullptr, e_g1 = nullptr;
-    RTB_CUDA(cudaEventCreate(&e_g0));
-    RTB_CUDA(cudaEventCreate(&e_g1));
-    RTB_CUDA(cudaEventRecord(e_g0, st));
     const int rc = build_light_grids(*S, hs->lights, n_light, bmin, bmax, st);
-    RTB_CUDA(cudaEventRecord(e_g1, st));
-    RTB_CUDA(cudaStreamSynchronize(st));
-    S->build_ms += ms_between(e_g0, e_g1);
-    cudaEventDestroy(e_g0); cudaEventDestroy(e_g1);
     if (rc) return rc;
   }
+  if (overlap) {
+    RTB_CUDA(cudaStreamWaitEvent(st, side.normals, 0));
+    k_permute<false, true><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2,
+                                              S->n0, S->n1, S->n2);
+    ++launches;
+  }
+  RTB_CUDA(cudaEventRecord(e_b1, st));
+  RTB_CUDA(cudaStreamSynchronize(st));
+  RTB_CUDA(cudaGetLastError());
+  S->upload_ms = ms_between(e_up0, e_up1);
+  S->build_ms = ms_between(e_up1, e_b1);
+  S->build_launches = launches;
   S->n_shadow_lights = 0;
   for (size_t i = 0; i < n_light; ++i)
     if (hs->lights[i].type == DIRECTIONAL || hs->lights[i].type == POINT) {
