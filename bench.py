@@ -24,6 +24,8 @@ import time
 
 import numpy as np
 
+_JSON_OUT = sys.stdout      # main() points it at the real stdout and sends everything else to stderr
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "raytracing-gpu_b200"))
 
@@ -157,7 +159,7 @@ def run_reference(args):
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }), flush=True)
+    }), file=_JSON_OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------
@@ -391,7 +393,7 @@ def run_ours(args):
                       "scene_generation_s": t_gen},
             "frame_checksum": checksum,
         }
-        print(json.dumps(out), flush=True)
+        print(json.dumps(out), file=_JSON_OUT, flush=True)
     barrier()
     pinned.free()
     ds.close()
@@ -413,6 +415,12 @@ def main():
         args.warmup = 3
     if args.ref_samples <= 0:
         args.ref_samples = 4 * (os.cpu_count() or 1)
+    # stdout carries exactly one line, the JSON: everything libraries print there (NCCL's version
+    # banner under torchrun, for one) goes to stderr instead
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -272,3 +272,17 @@ def test_grid_extent_from_a_sample_of_the_triangles(gpu):
             assert np.array_equal(_frame(a, primary), _frame(b, primary))
     finally:
         a.close(); b.close()
+
+
+def test_frames_wider_than_the_item_corners_walk_the_tree(gpu):
+    """items hold 16-bit sample corners: a 70 000-sample-wide frame keeps the tree walk, on request too"""
+    hs = pyrtb.HostScene.terrain(200, 70000, 2)
+    ds = pyrtb.DeviceScene(hs, 1)
+    try:
+        got, _ = _ids(ds, RASTER)
+        want, _ = _ids(ds, TREE)
+        assert np.array_equal(got, want), "the request is ignored, not half honoured"
+        assert np.array_equal(_frame(ds, RASTER), _frame(ds, TREE))
+        assert ds.stats()["kernel_launches"] == 1
+    finally:
+        ds.close()
