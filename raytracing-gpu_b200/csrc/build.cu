@@ -1262,6 +1262,10 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     k_single_node<<<1, 1, 0, st>>>(n, S->nodes);
     ++launches;
   }
+  // RTB_BUILD_TRACE=1: phase times of the build on stderr (tree | light grids | wait for normals + permute)
+  static const bool trace_build = [] { const char *e = getenv("RTB_BUILD_TRACE"); return e && atoi(e) != 0; }();
+  cudaEvent_t e_t[3] = {nullptr, nullptr, nullptr};
+  if (trace_build) { for (auto &e : e_t) cudaEventCreate(&e); cudaEventRecord(e_t[0], st); }
   uint32_t h_bounds[8];
   RTB_CUDA(cudaMemcpyAsync(h_bounds, d_bounds, sizeof h_bounds, cudaMemcpyDeviceToHost, st));
   RTB_CUDA(cudaStreamSynchronize(st));
@@ -1284,8 +1288,10 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     const int rc = build_light_grids(*S, hs->lights, n_light, bmin, bmax, st);
     if (rc) return rc;
   }
+  if (trace_build) cudaEventRecord(e_t[1], st);
   if (overlap) {
     RTB_CUDA(cudaStreamWaitEvent(st, side.normals, 0));
+    if (trace_build) cudaEventRecord(e_t[2], st);
     k_permute<false, true><<<gN, BT, 0, st>>>(raw_v, raw_n, S->order, n, d_first, (uint32_t)n_obj, S->v0, S->e1, S->e2,
                                               S->n0, S->n1, S->n2);
     ++launches;
@@ -1295,6 +1301,12 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   RTB_CUDA(cudaGetLastError());
   S->upload_ms = ms_between(e_up0, e_up1);
   S->build_ms = ms_between(e_up1, e_b1);
+  if (trace_build) {
+    fprintf(stderr, "rtb build trace: upload %.2f | tree %.2f | light grids %.2f | normals arrived +%.2f | permute normals %.2f ms\n",
+            S->upload_ms, ms_between(e_up1, e_t[0]), ms_between(e_t[0], e_t[1]), overlap ? ms_between(e_t[1], e_t[2]) : 0.0f,
+            overlap ? ms_between(e_t[2], e_b1) : ms_between(e_t[1], e_b1));
+    for (auto &e : e_t) cudaEventDestroy(e);
+  }
   S->build_launches = launches;
   S->n_shadow_lights = 0;
   for (size_t i = 0; i < n_light; ++i)
