@@ -122,7 +122,8 @@ typedef struct rtb_scene_handle rtb_scene_t;
 #define RTB_BUILD_NO_LIGHT_GRIDS 16u /* shadow rays always walk the tree (no per-light projection grids) */
 #define RTB_BUILD_ONE_FRAME   8u   /* the scene will be rendered once (rtb_render passes this): scenes of more
                                       than 2^18 triangles keep the radix tree; rebuilding the clusters of
-                                      10 M triangles takes 6 ms and saves 1.3 ms per 4K frame */
+                                      10 M triangles takes 6 ms and saves 1.3 ms per 4K frame; light grids
+                                      only from 4 samples per triangle on (camera.width * height >= 4 T) */
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags,
                      rtb_scene_t **out);
