@@ -218,7 +218,17 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   const bool any = x1 >= x0 && y1 >= y0;
   const int tx0 = x0 / RAST_TILE, tx1 = x1 / RAST_TILE, ty0 = y0 / RAST_TILE, ty1 = y1 / RAST_TILE;
   unsigned mine = 0, area = 0;
-  if (any) {
+  // A rectangle of at most 32 x 32 samples inside one rank tile stays one item even across the
+  // 32-sample tile lines (tiles only exist to cut big triangles into warp-sized work and to give
+  // every rank its own part): a third fewer items on C5.
+  const int rt = fa.nranks == 1 ? (1 << 30) : RANK_TILE * fa.aliasing;      // rank tile edge in samples
+  const bool single = any && x1 - x0 < RAST_TILE && y1 - y0 < RAST_TILE && x0 / rt == x1 / rt && y0 / rt == y1 / rt;
+  if (single) {
+    if (!*reinterpret_cast<volatile unsigned *>(rast + 1) && rast_owned(fa, tx0, ty0)) {
+      mine = 1;
+      area = (unsigned)((x1 - x0 + 1) * (y1 - y0 + 1));
+    }
+  } else if (any) {
     const unsigned tiles = (unsigned)(tx1 - tx0 + 1) * (unsigned)(ty1 - ty0 + 1);
     if (*reinterpret_cast<volatile unsigned *>(rast + 1)) { /* the frame has given up: emit nothing more */ }
     else if (tiles > RAST_TILES_MAX) { rast[1] = 1u; }
@@ -252,6 +262,10 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   unsigned k = base + incl - mine;
   if (base + total > fa.rast_cap) { rast[1] = 1u; return; }
   fa.rast_rec[3 * (size_t)s] = r0; fa.rast_rec[3 * (size_t)s + 1] = r1; fa.rast_rec[3 * (size_t)s + 2] = r2;
+  if (single) {
+    fa.rast_items[k] = make_uint4(s, (unsigned)x0 | ((unsigned)y0 << 16), (unsigned)x1 | ((unsigned)y1 << 16), 0u);
+    return;
+  }
   for (int ty = ty0; ty <= ty1; ++ty)
     for (int tx = tx0; tx <= tx1; ++tx)
       if (rast_owned(fa, tx, ty)) {
