@@ -6,9 +6,12 @@
 // a ray is a POINT and a triangle's culling box is a rectangle, so the candidates of a ray are the
 // triangles whose rectangle covers that point: a uniform grid in the light's projection, built
 // once per scene (lights are part of the scene), each cell listing the triangles whose box
-// (vertex bounds + needle padding + ray-time margin, the boxes the tree culls with) touches it.
-// A ray looks up one cell and runs the exact per-ray test on its list: ~10 triangle tests
-// instead of ~30-40 node visits on the 10 M-triangle terrain.  Triangles that cover too many
+// (vertex bounds + needle padding + ray-time margin, the boxes the tree culls with) touches it --
+// for a triangle without needle padding the box's rectangle is cut down to the bounds of the
+// region the rounded test can reach (lg_region), and an edge record per (light, triangle) holds
+// that region's three edge lines.  A ray looks up one cell, checks the entries' rectangles, then
+// the survivors' edge records, and runs the exact per-ray test on what is left: ~10 byte compares,
+// ~5 records and ~2 triangle tests instead of ~30-40 node visits on the 10 M-triangle terrain.  Triangles that cover too many
 // cells, and (point lights) boxes across the plane through the light, are tested by every ray;
 // too many of those, or a list volume out of proportion, and the light keeps the tree walk.  Rays
 // whose point falls outside the grid walk the tree as well.

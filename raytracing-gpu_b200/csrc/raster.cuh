@@ -2,20 +2,24 @@
 //
 // Every primary ray passes through the camera position (gpu/raytracer.cu:97-105: origin on the
 // image plane, direction towards `pos`), and sample (px, py) is a regular grid on that plane.
-// So "which rays can the rounded Moeller-Trumbore test accept for this triangle" is a screen
-// rectangle: the projection through `pos` of the triangle's culling box, the very box the
-// hierarchy culls with (vertex bounds + needle padding of pad.cuh + the ray-time margin of
-// trace_tree).  One pass over the triangles emits (triangle, 32x32-sample tile) items, one warp
-// per item runs the exact per-ray test of tri_candidate on the rectangle's samples, and
-// atomicMin on (new_dist bits << 32 | triangle id) keeps the reference's winner: lexicographic
-// minimum of (new_dist, id), gpu/hit.cu:66-76.  k_frame then starts every sample from that record
-// instead of walking the tree for its first ray; shadow and bounce rays still walk the tree.
+// So "which rays can the rounded Moeller-Trumbore test accept for this triangle" is a set of
+// samples on the screen: inside the projection through `pos` of the triangle's culling box, the
+// very box the hierarchy culls with (vertex bounds + needle padding of pad.cuh + the ray-time
+// margin of trace_tree), and, for a triangle without needle padding, inside the projection of
+// the region of its plane that the rounding of u and v can reach (k_rast_setup).  One pass over
+// the triangles emits (triangle, rectangle) items and a per-triangle edge record, one warp per
+// item tests the rectangle's sample centres against the record and queues the survivors, full
+// warps run the exact per-ray test of tri_candidate on them, and atomicMin on
+// (new_dist bits << 32 | triangle id) keeps the reference's winner: lexicographic minimum of
+// (new_dist, id), gpu/hit.cu:66-76.  k_frame then starts every sample from that record instead
+// of walking the tree for its first ray; bounce rays still walk the tree (shadow rays: lightgrid.cuh).
 //
-// Same candidates as the tree: a ray the tree would test against a triangle pierces that
-// triangle's inflated box, and a line through `pos` that pierces a convex box projects inside
-// the hull of the box's projected corners, as long as the box lies entirely on one side of the
-// plane through `pos` parallel to the image plane.  Boxes that straddle that plane (their
-// projection is unbounded) go to a short list every sample tests directly; more than
+// Never fewer candidates than the reference's exhaustive search accepts: a ray the tree would
+// test against a triangle pierces that triangle's inflated box, and a line through `pos` that
+// pierces a convex box projects inside the hull of the box's projected corners, as long as the
+// box lies entirely on one side of the plane through `pos` parallel to the image plane; the
+// region argument is above k_rast_setup and in DESIGN.md section 4.  Boxes that straddle that
+// plane (their projection is unbounded) go to a short list every sample tests directly; more than
 // RAST_STRADDLE_MAX of them, a triangle that spans more than RAST_TILES_MAX tiles, more items
 // than the list holds or more rectangle area than RAST_AREA_FACTOR x the frame make the frame
 // fall back to the tree for its primary rays (flag in device memory, no host round trip).
