@@ -78,3 +78,30 @@ def test_product_sources_never_touch_the_oracle():
                 text = open(os.path.join(base, f), errors="replace").read()
                 assert "oracle" not in text.lower() or f == "pyrtb.py" and "oracle" not in text.lower(), \
                     "%s mentions the oracle" % os.path.join(base, f)
+
+
+def test_ctypes_mirrors_match_the_header_layout(tmp_path):
+    """rtb_frame_opts and rtb_stats as gcc lays them out from include/rtb200.h against the ctypes
+    structures tests and bench.py pass through the C ABI (a field added on one side only would
+    shift everything after it silently)"""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if not gcc:
+        pytest.skip("no gcc")
+    fo = [n for n, _ in pyrtb.FrameOpts._fields_]
+    st = [n for n, _ in pyrtb.Stats._fields_]
+    prog = ['#include <stdio.h>', '#include <stddef.h>', '#include "rtb200.h"', 'int main(void) {',
+            '  printf("%zu %zu\\n", sizeof(rtb_frame_opts), sizeof(rtb_stats));']
+    prog += ['  printf("%%zu\\n", offsetof(rtb_frame_opts, %s));' % n for n in fo]
+    prog += ['  printf("%%zu\\n", offsetof(rtb_stats, %s));' % n for n in st]
+    prog += ['  return 0; }']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(prog))
+    exe = tmp_path / "layout"
+    subprocess.run([gcc, "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)], check=True)
+    out = subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.split()
+    assert int(out[0]) == C.sizeof(pyrtb.FrameOpts) and int(out[1]) == C.sizeof(pyrtb.Stats)
+    got = [int(x) for x in out[2:]]
+    want = [getattr(pyrtb.FrameOpts, n).offset for n in fo] + [getattr(pyrtb.Stats, n).offset for n in st]
+    assert got == want
