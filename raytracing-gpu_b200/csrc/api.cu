@@ -109,7 +109,9 @@ static int check_frame(const SceneStore &S, const rtb_frame_opts *o, int out_h, 
 
 static bool g_schedule = true;   // rtb_set_schedule (tests, A/B)
 
-constexpr uint32_t RASTER_AUTO_MIN_TRIS = 1u << 15;
+// The projection pass is the default for the first ray of every sample whatever the scene's size:
+// its cull is a bound (region.cuh), the hierarchy's padded boxes are a heuristic.
+constexpr uint32_t RASTER_AUTO_MIN_TRIS = 1u;
 
 // Buffers of the projection pass, owned by the scene handle (stream-ordered pool: a one-shot
 // render gets them in microseconds), and the box inflation of this frame.
@@ -129,16 +131,30 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
     S.d_rast_cap = cap;
   }
   if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, RAST_STATE_WORDS * 4, st));
-  // largest |coordinate| of a primary-ray origin: the four corners of the sample grid
-  float omax = 0;
-  for (int k = 0; k < 4; ++k) {
-    const float fx = (float)(((k & 1) ? fa.cam.W - 1 : 0) - fa.cam.W / 2), fy = (float)(((k & 2) ? fa.cam.H - 1 : 0) - fa.cam.H / 2);
-    const float ox = fa.cam.C.x + fa.cam.u.x * fx + fa.cam.v.x * fy, oy = fa.cam.C.y + fa.cam.u.y * fx + fa.cam.v.y * fy,
-                oz = fa.cam.C.z + fa.cam.u.z * fx + fa.cam.v.z * fy;
-    omax = fmaxf(omax, fmaxf(fabsf(ox), fmaxf(fabsf(oy), fabsf(oz))));
+  // the camera in double precision and the rounding scales of this frame's rays (region::CamFrame)
+  {
+    region::CamFrame &cf = fa.camf;
+    const double u[3] = {fa.cam.u.x, fa.cam.u.y, fa.cam.u.z}, v[3] = {fa.cam.v.x, fa.cam.v.y, fa.cam.v.z};
+    const double pos[3] = {fa.cam.pos.x, fa.cam.pos.y, fa.cam.pos.z}, Cc[3] = {fa.cam.C.x, fa.cam.C.y, fa.cam.C.z};
+    const int W = fa.cam.W, H = fa.cam.H;
+    const double X = (double)(W / 2 > W - 1 - W / 2 ? W / 2 : W - 1 - W / 2), Y = (double)(H / 2 > H - 1 - H / 2 ? H / 2 : H - 1 - H / 2);
+    double mo = 0;
+    for (int k = 0; k < 3; ++k) {
+      cf.pos[k] = pos[k]; cf.u[k] = u[k]; cf.v[k] = v[k];
+      cf.D0[k] = pos[k] - Cc[k];
+      const double m = fabs(Cc[k]) + fabs(u[k]) * X + fabs(v[k]) * Y;
+      mo += m * m;
+    }
+    cf.Mo = sqrt(mo);
+    double dmax = 0;
+    for (int c = 0; c < 4; ++c) {
+      const double x = (c & 1) ? (double)(W - 1 - W / 2) : -(double)(W / 2), y = (c & 2) ? (double)(H - 1 - H / 2) : -(double)(H / 2);
+      double d2 = 0;
+      for (int k = 0; k < 3; ++k) { const double d = cf.D0[k] - u[k] * x - v[k] * y; d2 += d * d; }
+      dmax = fmax(dmax, sqrt(d2));
+    }
+    cf.Dmax = dmax * (1.0 + 1e-6) + 8.0 * region::EPS24 * cf.Mo;
   }
-  // the ray-time margin of trace_tree at that origin, two more float spacings for vertex0 + edge
-  fa.rast_eps = (get_margin_k() + 2.0f) * 1.1920929e-7f * (omax * 1.001f + S.abs_max);
   // a tree walk costs about 3 000 instructions per sample, a rectangle sample about 100
   static const unsigned area_factor = [] { const char *e = getenv("RTB_RASTER_AREA"); return e && atoi(e) > 0 ? (unsigned)atoi(e) : 20u; }();
   fa.rast_area_factor = area_factor;
@@ -177,11 +193,11 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
-  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_eps = 0; fa.rast_area_factor = 0;
+  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_area_factor = 0;
   // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
-  if (!RTB_BVH4 && want_raster && S.has_tree && S.inv_order && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
+  if (!RTB_BVH4 && want_raster && (S.inv_order || !S.has_tree) && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
       o.frame_kernel == RTB_KERNEL_PER_SAMPLE && fa.cam.W <= 65535 && fa.cam.H <= 65535) {      // items hold 16-bit sample corners
     // a frame of this camera that ran the pass and still walked the tree (boxes across the camera
     // plane, rectangles covering too much) says the next one will too: AUTO does not try again
@@ -586,14 +602,24 @@ int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_o
   }
   // opts->primary == RTB_PRIMARY_RASTER: the ids the projection pass records (tests); a frame that
   // falls back to the tree reports -2 everywhere so that a test cannot pass by accident
-  if (o.primary == RTB_PRIMARY_RASTER && o.tracer == RTB_TRACER_TREE && S.has_tree && S.inv_order && S.camera.width <= 65535 &&
-      S.camera.height <= 65535) {
+  if (!RTB_BVH4 && o.primary != RTB_PRIMARY_TREE && o.tracer == RTB_TRACER_TREE && (S.inv_order || !S.has_tree) && S.n_tris >= RASTER_AUTO_MIN_TRIS &&
+      S.camera.width <= 65535 && S.camera.height <= 65535) {
     FrameArgs fa;
     memset(&fa, 0, sizeof fa);
     fa.cam = camera_frame(S.camera);
     fa.aliasing = o.aliasing; fa.out_w = out_w; fa.out_h = out_h; fa.rank = 0; fa.nranks = 1;
     rc = ensure_raster_resources(S, fa, S.stream);
-    if (!rc) rc = launch_prim_ids(S.dev(), fa, d_tri, d_obj, S.stream);
+    if (!rc) rc = launch_prim_ids(S.dev(), fa, d_tri, d_obj, S.sm_count, S.stream);
+    if (!rc && o.primary == RTB_PRIMARY_AUTO) {
+      // AUTO reports what a frame would use: the tree walk when the projection pass gave up
+      unsigned st8[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      cudaError_t e2 = cudaMemcpyAsync(st8, S.d_rast, sizeof st8, cudaMemcpyDeviceToHost, S.stream);
+      if (e2 == cudaSuccess) e2 = cudaStreamSynchronize(S.stream);
+      if (e2 != cudaSuccess) rc = cuda_fail(e2, "raster state readback", __FILE__, __LINE__);
+      const unsigned long long area = (unsigned long long)st8[2] | ((unsigned long long)st8[3] << 32);
+      if (!rc && (st8[1] || area > (unsigned long long)fa.rast_area_factor * n + 65536ull))
+        rc = launch_hit_ids(S.dev(), camera_frame(S.camera), o.tracer, d_tri, d_obj, S.stream);
+    }
   } else
     rc = launch_hit_ids(S.dev(), camera_frame(S.camera), o.tracer, d_tri, d_obj, S.stream);
   cudaError_t e = cudaSuccess;

@@ -3,39 +3,33 @@
 // Every primary ray passes through the camera position (gpu/raytracer.cu:97-105: origin on the
 // image plane, direction towards `pos`), and sample (px, py) is a regular grid on that plane.
 // So "which rays can the rounded Moeller-Trumbore test accept for this triangle" is a set of
-// samples on the screen: inside the projection through `pos` of the triangle's culling box, the
-// very box the hierarchy culls with (vertex bounds + needle padding of pad.cuh + the ray-time
-// margin of trace_tree), and, for a triangle without needle padding, inside the projection of
-// the region of its plane that the rounding of u and v can reach (k_rast_setup).  One pass over
-// the triangles emits (triangle, rectangle) items and a per-triangle edge record, one warp per
-// item tests the rectangle's sample centres against the record and queues the survivors, full
-// warps run the exact per-ray test of tri_candidate on them, and atomicMin on
-// (new_dist bits << 32 | triangle id) keeps the reference's winner: lexicographic minimum of
-// (new_dist, id), gpu/hit.cu:66-76.  k_frame then starts every sample from that record instead
-// of walking the tree for its first ray; bounce rays still walk the tree (shadow rays: lightgrid.cuh).
+// samples on the screen, and region.cuh bounds it rigorously: the numerators of u, v and 1 - u - v
+// are linear in (px, py) (homogeneous edge functions through `pos`), the rounding of the
+// reference's operation sequence moves them by at most E_k, so every accepted sample lies inside
+// three offset lines (region::primary_lines has the derivation; tests/test_region_cpu.py replays
+// it in float32 on the host, triangles seen edge-on, across the camera plane and degenerate ones
+// included).  One pass over the triangles emits (triangle, rectangle) items and a per-triangle
+// edge record, one warp per item tests the rectangle's sample centres against the record and
+// queues the survivors, full warps run the exact per-ray test of tri_candidate on them, and
+// atomicMin on (new_dist bits << 32 | triangle id) keeps the reference's winner: lexicographic
+// minimum of (new_dist, id), gpu/hit.cu:66-76.  k_frame then starts every sample from that record
+// instead of walking the tree for its first ray; bounce rays still walk the tree (shadow rays:
+// lightgrid.cuh).
 //
-// Never fewer candidates than the reference's exhaustive search accepts: a ray the tree would
-// test against a triangle pierces that triangle's inflated box, and a line through `pos` that
-// pierces a convex box projects inside the hull of the box's projected corners, as long as the
-// box lies entirely on one side of the plane through `pos` parallel to the image plane; the
-// region argument is above k_rast_setup and in DESIGN.md section 4.  Boxes that straddle that
-// plane (their projection is unbounded) go to a short list every sample tests directly; more than
-// RAST_STRADDLE_MAX of them, a triangle that spans more than RAST_TILES_MAX tiles, more items
-// than the list holds or more rectangle area than RAST_AREA_FACTOR x the frame make the frame
-// fall back to the tree for its primary rays (flag in device memory, no host round trip).
+// The cull never drops a candidate of the reference's exhaustive search (gpu/hit.cu:84-114), so
+// the primary hit ids are the reference's for every scene -- no boxes, no padding heuristics, no
+// special list for triangles across the camera plane.  A triangle that spans more than
+// RAST_TILES_MAX tiles, more items than the list holds or more rectangle area than
+// RAST_AREA_FACTOR x the frame make the frame fall back to the tree for its primary rays (flag in
+// device memory, no host round trip).
 #pragma once
 
 namespace {
 
 constexpr int RAST_TILE = 32;                 // samples
-#ifndef RTB_RAST_HULL
-#define RTB_RAST_HULL 1
-#endif
-constexpr bool RAST_HULL = RTB_RAST_HULL != 0;
-constexpr unsigned RAST_STRADDLE_MAX = 16;
 constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
-// rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 straddler count, 8.. straddler slots
-constexpr int RAST_WORDS = 8 + RAST_STRADDLE_MAX;
+// rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 triangles with two regions
+constexpr int RAST_WORDS = 8;
 
 __device__ __forceinline__ bool rast_active(const FrameArgs &fa) {
   if (!fa.prim) return false;
@@ -54,199 +48,50 @@ __device__ __forceinline__ bool rast_owned(const FrameArgs &fa, int tx, int ty) 
   return (Tx + 3 * Ty) % fa.nranks == fa.rank;
 }
 
-// k_rast_setup: one thread per triangle slot.  Rectangle, per-triangle edge record, items.
-//
-// Rectangle = (projection of the culling box) INTERSECTED with, for a triangle without needle
-// padding seen at a fair angle, (projection of the region of its plane where the rounded test can
-// accept).  That region: the test accepts when the COMPUTED (u, v) lies in the unit simplex.  With
-// eps = 2^-24, |d| = 1, s = origin - vertex0, h = d x e2, a = e1 . h (un-fused, as the reference):
-//   |dh| <= 2 sqrt2 eps |e2|,  |d(s . h)| <= |s| |dh| + 3 eps |s| |h| + eps |s| |h| <= 6.9 eps |s| |e2|,
-//   |da| <= 5.9 eps |e1| |e2|,  so  |du| <= 6.9 eps |s| |e2| / |a| + |u| 5.9 eps |e1| |e2| / |a| + 2 eps |u|
-// and the same for v with e1; |a| = |e1 x e2| cos(incidence).  RAST_HULL_C = 14 doubles the leading
-// constant (the |u| terms are smaller by |e| / |s|).  The true crossing point of an accepted ray
-// therefore lies in  u >= -du, v >= -dv, u + v <= 1 + du + dv + 4 eps : a triangle in the plane
-// whose corners are projected.  The cosine is (distance of pos from the plane) / |pos - point|,
-// smallest at the farthest corner; |s| is bounded by the frame's farthest origin.
-//
-// Edge record: the three edge lines of that projected triangle, pushed out by the projected size
-// of the ray's own rounding; k_rast_items tests the sample centre against them
-// before it spends a ray on it.  rec[3 slot + 0..2] = (n0x, n0y, c0, n1x) (n1y, c1, n2x, n2y)
-// (c2, X0, Y0, on): inside <=> n . (px - X0, py - Y0) + c <= 0 for the three edges.
+// k_rast_setup: one thread per triangle slot.  Region of the screen where the rounded test can
+// accept (region::primary_cull, double precision: ~150 flops per triangle, the kernel is bound by
+// its gathers), the sample rectangle around it, the float edge record k_rast_items tests sample
+// centres against, and the items: one if the rectangle is at most 32 x 32 samples inside one rank
+// tile, else one per 32 x 32-sample tile the region can touch (region::row_range per tile row, so a
+// long thin region costs its length, not its bounding box).
 __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const FrameArgs fa) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   const int lane = threadIdx.x & 31;
   unsigned *rast = fa.rast;
-  const float INF = __builtin_huge_valf();
-  int x0 = 0, y0 = 0, x1 = -1, y1 = -1;        // empty rectangle
-  bool straddle = false;
-  float4 r0 = make_float4(0, 0, -1, 0), r1 = make_float4(0, -1, 0, 0), r2 = make_float4(-1, 0, 0, 0);
+  region::PrimaryCull c;
+  c.kind = 0;
   if (s < sc.n_tris) {
     const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
-    const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
-    V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
-    V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
-    const V3 lo0 = lo, hi0 = hi;
-    sliver_pad(v, sc.pad_unit, lo, hi);
-    bool plain = RAST_HULL && lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z;
-    // ray-time margin of trace_tree at the largest origin of this frame, plus the rounding of
-    // vertex0 + edge (the build boxes come from the stored vertices themselves)
-    const float e = fa.rast_eps;
-    lo = mk(lo.x - e, lo.y - e, lo.z - e);
-    hi = mk(hi.x + e, hi.y + e, hi.z + e);
-    const V3 u = mk(fa.cam.u), vv = mk(fa.cam.v), w = mk(fa.cam.w), pos = mk(fa.cam.pos);
-    const float ww = vdot(w, w), uv = vdot(u, vv);
-    const float det = 1.0f - uv * uv;                      // Gram determinant of the unit vectors u, v
-    const float Lw = fa.cam.L, inv_det = 1.0f / det;
-    auto project = [&](const V3 X, float &x, float &y, float &den) {
-      const V3 r = vsub(pos, X);
-      den = vdot(r, w);
-      // fast division and a reciprocal: a few more spacings of x, inside the slack below (4e-7 |x|)
-      const float t = __fdividef(Lw * ww, den);
-      const V3 q = vsub(vscale(r, t), vscale(w, Lw));     // offset from the plane's centre C
-      const float qu = vdot(q, u), qv = vdot(q, vv);
-      x = (qu - uv * qv) * inv_det;
-      y = (qv - uv * qu) * inv_det;
-    };
-    float dmin = INF, dmax = -INF, xmin = INF, xmax = -INF, ymin = INF, ymax = -INF;
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      float x, y, den;
-      project(mk((k & 1) ? hi.x : lo.x, (k & 2) ? hi.y : lo.y, (k & 4) ? hi.z : lo.z), x, y, den);
-      dmin = fminf(dmin, den); dmax = fmaxf(dmax, den);
-      xmin = fminf(xmin, x); xmax = fmaxf(xmax, x); ymin = fminf(ymin, y); ymax = fmaxf(ymax, y);
-    }
-    // one side of the plane through pos, and not grazing it (relative to the box's own depth range)
-    const float near = fminf(fabsf(dmin), fabsf(dmax));
-    straddle = !(dmin * dmax > 0.0f) || !(near > 1e-3f * (dmax - dmin)) || !(det > 1e-6f) ||
-               !(xmin > -1e9f && xmax < 1e9f && ymin > -1e9f && ymax < 1e9f);
-    if (!straddle) {
-      // px - W/2 = x (integer division as in primary_ray: W / 2, H / 2).  Slack for the rounding of
-      // the projection itself: a few float spacings of a coordinate that is at most ~1e5 samples
-      const float cx = (float)(fa.cam.W / 2), cy = (float)(fa.cam.H / 2);
-      const float sx = 0.02f + 1e-6f * fmaxf(fabsf(xmin), fabsf(xmax)), sy = 0.02f + 1e-6f * fmaxf(fabsf(ymin), fabsf(ymax));
-      float fx0 = ceilf(xmin + cx - sx), fx1 = floorf(xmax + cx + sx);
-      float fy0 = ceilf(ymin + cy - sy), fy1 = floorf(ymax + cy + sy);
-      // nothing of the box on this rank's part of the screen: no region, no record, no items
-      if (plain) {
-        const int bx0 = (int)fmaxf(fx0, 0.0f), bx1 = (int)fminf(fx1, (float)(fa.cam.W - 1));
-        const int by0 = (int)fmaxf(fy0, 0.0f), by1 = (int)fminf(fy1, (float)(fa.cam.H - 1));
-        plain = bx1 >= bx0 && by1 >= by0;
-        if (plain && fa.nranks > 1) {
-          const int t0 = bx0 / RAST_TILE, t1 = bx1 / RAST_TILE, u0 = by0 / RAST_TILE, u1 = by1 / RAST_TILE;
-          if ((t1 - t0 + 1) * (u1 - u0 + 1) <= 16) {
-            bool mine = false;
-            for (int ty = u0; ty <= u1; ++ty)
-              for (int tx = t0; tx <= t1; ++tx) mine = mine || rast_owned(fa, tx, ty);
-            plain = mine;
-          }
-        }
-      }
-      // the accepted region in the triangle's plane (see above)
-      float du = 0.0f, dv = 0.0f, smax = 0.0f;
-      if (plain) {
-        const V3 n = vcross(mk(b4), mk(c4)), p0 = vsub(pos, v[0]);
-        const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
-        const float far0 = fmaxf(vlen(p0), fmaxf(vlen(vsub(pos, v[1])), vlen(vsub(pos, v[2]))));
-        const float far = far0 + 6.0f * (l1 + l2);                        // the grown corners are farther (du, dv < 2 below)
-        const float cosine = fabsf(vdot(n, p0)) / (ln * far);
-        // |origin - vertex| <= |origin - pos| + |pos - vertex|, origins lie within the frame's corners
-        smax = sqrtf(Lw * Lw + cx * cx + cy * cy) + far;
-        du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
-        dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
-        plain = ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f;       // NaN -> box only
-      }
-      if (plain) {
-        const float dw = du + dv + 2.4e-7f;
-        const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
-                         vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
-                         vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
-        float ax[3], ay[3];
-        float hx0 = INF, hx1 = -INF, hy0 = INF, hy1 = -INF, dnear = INF;
-        bool ok = true;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          float den;
-          project(P[k], ax[k], ay[k], den);
-          ok = ok && den * dmin > 0.0f;
-          dnear = fminf(dnear, fabsf(den));
-          hx0 = fminf(hx0, ax[k]); hx1 = fmaxf(hx1, ax[k]); hy0 = fminf(hy0, ay[k]); hy1 = fmaxf(hy1, ay[k]);
-        }
-        const float big = fmaxf(fmaxf(fabsf(hx0), fabsf(hx1)), fmaxf(fabsf(hy0), fabsf(hy1)));
-        // The ray itself is rounded.  Its origin: three roundings at the size of |o|, about 1.5
-        // spacings of |o| per coordinate -- thousandths of a sample (the image plane's unit is the
-        // sample), and the line pivots about pos, so behind pos that shrinks by depth / L.  Its
-        // direction normalize(pos - o): the subtraction and the three divisions round each coordinate
-        // by eps relative (the length is a common factor), an angle of about 2 eps, i.e. 2 eps |s| across
-        // the ray at the triangle.  RAST_RAY_C = 8 eps |s| bounds the sum with a factor of three; a
-        // displacement of that size at depth >= dnear moves the projection by at most
-        // |delta| sqrt(L^2 + x^2) / depth (1.3: second order, dnear > 8 delta).
-        const float delta = RAST_RAY_C * 5.9604645e-8f * smax;
-        ok = ok && dnear > 0.25f * near && dnear > 8.0f * delta && big < 1e6f;
-        if (ok) {
-          const float sr = 1.3f * delta * sqrtf(Lw * Lw + big * big) / dnear;      // a distance: any direction
-          const float sb = 0.02f + 1e-6f * big;                                    // per coordinate
-          const float se = sr + sb;
-          fx0 = fmaxf(fx0, ceilf(hx0 + cx - se)); fx1 = fminf(fx1, floorf(hx1 + cx + se));
-          fy0 = fmaxf(fy0, ceilf(hy0 + cy - se)); fy1 = fminf(fy1, floorf(hy1 + cy + se));
-          const float X0 = fmaxf(fx0, 0.0f), Y0 = fmaxf(fy0, 0.0f);
-          float en[3][3];
-          bool edges = true;
-#pragma unroll
-          for (int k = 0; k < 3; ++k) {
-            const int kb = (k + 1) % 3, kc = (k + 2) % 3;
-            float nx = ay[kb] - ay[k], ny = ax[k] - ax[kb];
-            const float len = sqrtf(nx * nx + ny * ny);
-            nx /= len; ny /= len;
-            const float side = nx * (ax[kc] - ax[k]) + ny * (ay[kc] - ay[k]);
-            edges = edges && len > 1e-3f && fabsf(side) > 1e-3f;      // edge-on on screen: rectangle only
-            if (side > 0.0f) { nx = -nx; ny = -ny; }
-            const float rx = (X0 - cx) - ax[k], ry = (Y0 - cy) - ay[k];
-            const float off = sr + sb * (fabsf(nx) + fabsf(ny)) + 1e-6f * (fabsf(rx) + fabsf(ry));
-            en[k][0] = nx; en[k][1] = ny; en[k][2] = nx * rx + ny * ry - off;
-          }
-          if (edges) {
-            r0 = make_float4(en[0][0], en[0][1], en[0][2], en[1][0]);
-            r1 = make_float4(en[1][1], en[1][2], en[2][0], en[2][1]);
-            r2 = make_float4(en[2][2], X0, Y0, 1.0f);
-          }
-        }
-      }
-      x0 = (int)fmaxf(fx0, 0.0f); x1 = (int)fminf(fx1, (float)(fa.cam.W - 1));
-      y0 = (int)fmaxf(fy0, 0.0f); y1 = (int)fminf(fy1, (float)(fa.cam.H - 1));
-    }
+    const float v0[3] = {a4.x, a4.y, a4.z}, e1[3] = {b4.x, b4.y, b4.z}, e2[3] = {c4.x, c4.y, c4.z};
+    region::primary_cull(fa.camf, fa.cam.W, fa.cam.H, v0, e1, e2, c);
   }
-  if (straddle) {
-    const unsigned k = atomicAdd(&rast[4], 1u);
-    if (k < RAST_STRADDLE_MAX) rast[8 + k] = s; else rast[1] = 1u;
-  }
-  const bool any = x1 >= x0 && y1 >= y0;
-  const int tx0 = x0 / RAST_TILE, tx1 = x1 / RAST_TILE, ty0 = y0 / RAST_TILE, ty1 = y1 / RAST_TILE;
+  const bool any = c.kind != 0;
+  const int x0 = c.x0, y0 = c.y0, x1 = c.x1, y1 = c.y1;
+  const int ty0 = any ? y0 / RAST_TILE : 0, ty1 = any ? y1 / RAST_TILE : -1;
   unsigned mine = 0, area = 0;
-  // A rectangle of at most 32 x 32 samples inside one rank tile stays one item even across the
-  // 32-sample tile lines (tiles only exist to cut big triangles into warp-sized work and to give
-  // every rank its own part): a third fewer items on C5.
   const int rt = fa.nranks == 1 ? (1 << 30) : RANK_TILE * fa.aliasing;      // rank tile edge in samples
   const bool single = any && x1 - x0 < RAST_TILE && y1 - y0 < RAST_TILE && x0 / rt == x1 / rt && y0 / rt == y1 / rt;
+  const bool gave_up = *reinterpret_cast<volatile unsigned *>(rast + 1) != 0;     // the frame has given up: emit nothing more
   if (single) {
-    if (!*reinterpret_cast<volatile unsigned *>(rast + 1) && rast_owned(fa, tx0, ty0)) {
+    if (!gave_up && rast_owned(fa, x0 / RAST_TILE, y0 / RAST_TILE)) {
       mine = 1;
       area = (unsigned)((x1 - x0 + 1) * (y1 - y0 + 1));
     }
-  } else if (any) {
-    const unsigned tiles = (unsigned)(tx1 - tx0 + 1) * (unsigned)(ty1 - ty0 + 1);
-    if (*reinterpret_cast<volatile unsigned *>(rast + 1)) { /* the frame has given up: emit nothing more */ }
-    else if (tiles > RAST_TILES_MAX) { rast[1] = 1u; }
-    else {
-      for (int ty = ty0; ty <= ty1; ++ty)
-        for (int tx = tx0; tx <= tx1; ++tx)
-          if (rast_owned(fa, tx, ty)) {
-            ++mine;
-            const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
-            const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
-            area += (unsigned)((cx1 - cx0 + 1) * (cy1 - cy0 + 1));
-          }
+  } else if (any && !gave_up) {
+    for (int ty = ty0; ty <= ty1 && mine <= RAST_TILES_MAX; ++ty) {
+      int ta, tb;
+      if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
+      const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
+      for (int tx = ta; tx <= tb; ++tx)
+        if (rast_owned(fa, tx, ty)) {
+          ++mine;
+          const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
+          area += (unsigned)((cx1 - cx0 + 1) * (cy1 - cy0 + 1));
+        }
     }
+    if (mine > RAST_TILES_MAX) { rast[1] = 1u; mine = 0; area = 0; }
   }
+  if (c.kind == 2) atomicAdd(&rast[4], 1u);
   // one atomic per warp for the item slots and for the area
   unsigned incl = mine;
 #pragma unroll
@@ -265,18 +110,25 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   if (!mine) return;
   unsigned k = base + incl - mine;
   if (base + total > fa.rast_cap) { rast[1] = 1u; return; }
-  fa.rast_rec[3 * (size_t)s] = r0; fa.rast_rec[3 * (size_t)s + 1] = r1; fa.rast_rec[3 * (size_t)s + 2] = r2;
+  const float *rv = c.rec.v;
+  fa.rast_rec[3 * (size_t)s] = make_float4(rv[0], rv[1], rv[2], rv[3]);
+  fa.rast_rec[3 * (size_t)s + 1] = make_float4(rv[4], rv[5], rv[6], rv[7]);
+  fa.rast_rec[3 * (size_t)s + 2] = make_float4(rv[8], rv[9], rv[10], rv[11]);
   if (single) {
     fa.rast_items[k] = make_uint4(s, (unsigned)x0 | ((unsigned)y0 << 16), (unsigned)x1 | ((unsigned)y1 << 16), 0u);
     return;
   }
-  for (int ty = ty0; ty <= ty1; ++ty)
-    for (int tx = tx0; tx <= tx1; ++tx)
-      if (rast_owned(fa, tx, ty)) {
+  const unsigned end = k + mine;
+  for (int ty = ty0; ty <= ty1; ++ty) {
+    int ta, tb;
+    if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
+    const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
+    for (int tx = ta; tx <= tb; ++tx)
+      if (rast_owned(fa, tx, ty) && k < end) {
         const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
-        const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
         fa.rast_items[k++] = make_uint4(s, (unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), 0u);
       }
+  }
 }
 
 // k_rast_items: one warp per item.  Cheap stage: the rectangle's samples against the edge record,
@@ -317,17 +169,12 @@ __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene s
     const unsigned rw = c_rast_rw[w];
     const float4 r0 = __ldg(fa.rast_rec + 3 * (size_t)it.x), r1 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 1),
                  r2 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 2);
-    const bool edges = r2.w != 0.0f;
     const float ox = (float)x0 - r2.y, oy = (float)y0 - r2.z;     // item corner relative to the record's origin
     for (int k0 = 0; k0 < cnt; k0 += 32) {
       const int k = k0 + lane;
       const int ry = (int)(((unsigned)k * rw) >> 16), rx = k - ry * w;
-      bool in = k < cnt;
-      if (edges) {
-        const float dx = ox + (float)rx, dy = oy + (float)ry;
-        in = in && r0.x * dx + r0.y * dy + r0.z <= 0.0f && r0.w * dx + r1.x * dy + r1.y <= 0.0f &&
-             r1.z * dx + r1.w * dy + r2.x <= 0.0f;
-      }
+      const bool in = k < cnt && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
+                                                         ox + (float)rx, oy + (float)ry);
       const unsigned mask = __ballot_sync(0xffffffffu, in);
       if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + ry) << 16));
       qn += __popc(mask);
@@ -343,7 +190,7 @@ __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene s
   if (lane < qn) rast_test(sc, fa, Q[lane]);
 }
 
-// The primary hit of sample (px, py) from the record (+ the straddlers, tested like any leaf).
+// The primary hit of sample (px, py) from the record.
 __device__ __forceinline__ bool prim_lookup(const DevScene &sc, const FrameArgs &fa, int px, int py, const V3 o,
                                             const V3 d, Best &best) {
   const unsigned long long key = fa.prim[(size_t)py * fa.cam.W + px];
@@ -351,10 +198,8 @@ __device__ __forceinline__ bool prim_lookup(const DevScene &sc, const FrameArgs 
   if (key != ~0ull) {
     best.dist = __uint_as_float((unsigned)(key >> 32));
     best.id = (int)(unsigned)key;
-    best.slot = (int)__ldg(sc.inv_order + best.id);
+    best.slot = sc.inv_order ? (int)__ldg(sc.inv_order + best.id) : best.id;      // no hierarchy: slot == id
   }
-  const unsigned ns = fa.rast[4];
-  for (unsigned k = 0; k < ns; ++k) consider<false>(sc, o, d, (int)fa.rast[8 + k], best);
   return best.slot >= 0;
 }
 

@@ -6,6 +6,7 @@
 #include <stddef.h>
 #include <string>
 #include "rtb200.h"
+#include "region.cuh"
 
 namespace rtb {
 
@@ -129,7 +130,7 @@ struct FrameArgs {
   unsigned rast_cap;              // capacity of rast_items
   float4 *rast_rec;               // 3 per triangle slot: edge record of the projected triangle (raster.cuh)
   unsigned *rast;                 // counters and flags (raster.cuh RAST_WORDS)
-  float rast_eps;                 // box inflation: the ray-time margin at this frame's farthest origin
+  region::CamFrame camf;          // the camera in double precision + the rounding scales of this frame (region.cuh)
   unsigned rast_area_factor;      // give up when the rectangles cover more than this many times the frame
   // wavefront kernel only
   float *bounce_scratch;          // per resident warp: 7 x S floats (origin, direction, nr_ of reflected rays)
@@ -159,7 +160,7 @@ int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys
                       cudaStream_t st, int *result_in_alt);
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
                    cudaStream_t st);
-int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, cudaStream_t st);
+int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, int sm_count, cudaStream_t st);
 constexpr int RAST_STATE_WORDS = 32;      // size of FrameArgs::rast, in 32-bit words
 int launch_trace_rays(const DevScene &sc, int tracer, int any_hit, const float *d_rays, size_t n, int32_t *d_tri,
                       float *d_dist, cudaStream_t st);

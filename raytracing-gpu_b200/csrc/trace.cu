@@ -910,13 +910,13 @@ int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t
   return RTB_OK;
 }
 
-int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, cudaStream_t st) {
+int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, int sm_count, cudaStream_t st) {
   static_assert(RAST_WORDS <= RAST_STATE_WORDS, "raster state");
   RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
   RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
   if (sc.n_tris) {
     k_rast_setup<<<(sc.n_tris + 255) / 256, 256, 0, st>>>(sc, fa);
-    k_rast_items<<<148 * 8, 256, 0, st>>>(sc, fa);
+    k_rast_items<<<sm_count * 8, 256, 0, st>>>(sc, fa);
   }
   const size_t n = (size_t)fa.cam.W * fa.cam.H;
   if (n) k_prim_ids<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(sc, fa, d_tri, d_obj);
