@@ -78,18 +78,22 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       area = (unsigned)((x1 - x0 + 1) * (y1 - y0 + 1));
     }
   } else if (any && !gave_up) {
+    // "area" = the samples k_rast_items will look at: it walks these items row by row over the
+    // region's span (region::record_span), so a thin region costs its length, not its rectangle
+    unsigned touched = 0;
     for (int ty = ty0; ty <= ty1 && mine <= RAST_TILES_MAX; ++ty) {
       int ta, tb;
       if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
-      const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
+      touched += (unsigned)(tb - ta + 1);
       for (int tx = ta; tx <= tb; ++tx)
-        if (rast_owned(fa, tx, ty)) {
-          ++mine;
-          const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
-          area += (unsigned)((cx1 - cx0 + 1) * (cy1 - cy0 + 1));
-        }
+        if (rast_owned(fa, tx, ty)) ++mine;
     }
-    if (mine > RAST_TILES_MAX) { rast[1] = 1u; mine = 0; area = 0; }
+    if (mine > RAST_TILES_MAX) { rast[1] = 1u; mine = 0; }
+    if (mine) {
+      const double rect = (double)(x1 - x0 + 1) * (double)(y1 - y0 + 1);
+      const double work = fmin(c.R.work, rect) * (double)mine / (double)touched + 32.0 * (double)mine;
+      area = (unsigned)fmin(work, 67108864.0);
+    }
   }
   if (c.kind == 2) atomicAdd(&rast[4], 1u);
   // one atomic per warp for the item slots and for the area
@@ -137,6 +141,7 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
 // the expensive stage whatever the rectangles look like.  Queue entries carry their triangle, so
 // the queue simply runs on across items.
 constexpr int RAST_WARPS = 8;
+constexpr int RAST_SCAN_MAX = 96;             // rectangles of more samples are walked row by row
 // k / w == (k * c_rast_rw[w]) >> 16 for k < 1024, w <= 32: 65536 / w + 1 (the division costs 20 instructions per item)
 __constant__ unsigned c_rast_rw[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
 
@@ -170,20 +175,45 @@ __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene s
     const float4 r0 = __ldg(fa.rast_rec + 3 * (size_t)it.x), r1 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 1),
                  r2 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 2);
     const float ox = (float)x0 - r2.y, oy = (float)y0 - r2.z;     // item corner relative to the record's origin
-    for (int k0 = 0; k0 < cnt; k0 += 32) {
-      const int k = k0 + lane;
-      const int ry = (int)(((unsigned)k * rw) >> 16), rx = k - ry * w;
-      const bool in = k < cnt && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
-                                                         ox + (float)rx, oy + (float)ry);
-      const unsigned mask = __ballot_sync(0xffffffffu, in);
-      if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + ry) << 16));
-      qn += __popc(mask);
-      __syncwarp();
-      if (qn >= 32) {
-        qn -= 32;
-        const uint2 q = Q[qn + lane];
+    if (cnt <= RAST_SCAN_MAX) {
+      // small rectangle: its samples 32 at a time
+      for (int k0 = 0; k0 < cnt; k0 += 32) {
+        const int k = k0 + lane;
+        const int ry = (int)(((unsigned)k * rw) >> 16), rx = k - ry * w;
+        const bool in = k < cnt && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
+                                                           ox + (float)rx, oy + (float)ry);
+        const unsigned mask = __ballot_sync(0xffffffffu, in);
+        if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + ry) << 16));
+        qn += __popc(mask);
         __syncwarp();
-        rast_test(sc, fa, q);
+        if (qn >= 32) {
+          qn -= 32;
+          const uint2 q = Q[qn + lane];
+          __syncwarp();
+          rast_test(sc, fa, q);
+        }
+      }
+    } else {
+      // big rectangle (a tile of a big or a thin region): one row per lane, each lane walks the span
+      // of its row that the record can pass (region::record_span, a superset; record_inside decides)
+      const int h = y1 - y0 + 1;                  // <= 32
+      int a = 1, b = 0;
+      if (lane < h) region::record_span(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, ox, w, oy + (float)lane, a, b);
+      const int longest = __reduce_max_sync(0xffffffffu, b - a + 1);
+      for (int j = 0; j < longest; ++j) {
+        const int rx = a + j;
+        const bool in = rx <= b && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
+                                                           ox + (float)rx, oy + (float)lane);
+        const unsigned mask = __ballot_sync(0xffffffffu, in);
+        if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + lane) << 16));
+        qn += __popc(mask);
+        __syncwarp();
+        if (qn >= 32) {
+          qn -= 32;
+          const uint2 q = Q[qn + lane];
+          __syncwarp();
+          rast_test(sc, fa, q);
+        }
       }
     }
   }

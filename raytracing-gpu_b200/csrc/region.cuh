@@ -39,6 +39,7 @@ struct Region {
   // unit outward normals of the (first) region: inside <=> n_k . (x, y) + c_k <= 0 for k = 0..2.
   // kind 2: the second region is  n_k . (x, y) + c_k >= -m  for k = 0..2.
   double nx[3], ny[3], c[3], m;
+  double work;              // samples a scan of the region(s) looks at: polygon area + a rim along the outline
 };
 
 struct Poly { double x[8], y[8]; int n; };
@@ -61,6 +62,18 @@ RTB_RG void clip(Poly &p, double a, double b, double c) {
   p = q;
 }
 
+// area of the convex polygon plus one unit along its outline (bounded by the box's perimeter)
+RTB_RG double poly_work(const Poly &p) {
+  if (p.n < 1) return 0.0;
+  double a2 = 0.0, x0 = p.x[0], x1 = p.x[0], y0 = p.y[0], y1 = p.y[0];
+  for (int i = 0; i < p.n; ++i) {
+    const int j = i + 1 == p.n ? 0 : i + 1;
+    a2 += p.x[i] * p.y[j] - p.x[j] * p.y[i];
+    x0 = fmin(x0, p.x[i]); x1 = fmax(x1, p.x[i]); y0 = fmin(y0, p.y[i]); y1 = fmax(y1, p.y[i]);
+  }
+  return 0.5 * fabs(a2) + 2.0 * ((x1 - x0) + (y1 - y0)) + 1.0;
+}
+
 RTB_RG void grow(const Poly &p, double &x0, double &x1, double &y0, double &y1) {
   for (int i = 0; i < p.n; ++i) {
     x0 = fmin(x0, p.x[i]); x1 = fmax(x1, p.x[i]);
@@ -81,6 +94,7 @@ RTB_RG void build(const Lines &L, double dx0, double dx1, double dy0, double dy1
   R.kind = 0;
   R.x0 = BIG; R.x1 = -BIG; R.y0 = BIG; R.y1 = -BIG;
   R.m = 0.0;
+  R.work = 0.0;
   double len[3];
   for (int k = 0; k < 3; ++k) len[k] = sqrt(L.cx[k] * L.cx[k] + L.cy[k] * L.cy[k]);
   bool plus = false, minus = false, done = false;
@@ -111,6 +125,7 @@ RTB_RG void build(const Lines &L, double dx0, double dx1, double dy0, double dy1
         if (x1 < dx0 || x0 > dx1 || y1 < dy0 || y0 > dy1) return;             // off the domain (NaN falls through)
         if (x0 >= dx0 && x1 <= dx1 && y0 >= dy0 && y1 <= dy1) {
           R.x0 = x0; R.x1 = x1; R.y0 = y0; R.y1 = y1;
+          R.work = 0.5 * fabs((bx - ax) * (cy - ay) - (cx - ax) * (by - ay)) + 2.0 * ((x1 - x0) + (y1 - y0)) + 1.0;
           plus = p_only; minus = m_only; done = true;
         }
       }
@@ -121,9 +136,11 @@ RTB_RG void build(const Lines &L, double dx0, double dx1, double dy0, double dy1
     side_polygon(L, 1.0, dx0, dx1, dy0, dy1, p);
     plus = p.n > 0;
     grow(p, R.x0, R.x1, R.y0, R.y1);
+    R.work += poly_work(p);
     side_polygon(L, -1.0, dx0, dx1, dy0, dy1, p);
     minus = p.n > 0;
     grow(p, R.x0, R.x1, R.y0, R.y1);
+    R.work += poly_work(p);
   }
   if (!plus && !minus) return;
   R.kind = plus && minus ? 2 : 1;

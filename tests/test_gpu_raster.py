@@ -163,8 +163,8 @@ def test_needle_soups(gpu, T):
     try:
         got, _ = _ids(ds, RASTER)
         brute, _ = ds.hit_ids(pyrtb.TRACER_BRUTE)
-        if (got == -2).all():
-            assert T >= 40000, "only the big soup covers the frame more than 20 times"
+        if (got == -2).all():                             # a soup that covers the frame > 20 times keeps the tree walk
+            assert ds.raster_state()["area"] > 20 * 600 * 360
             return
         assert np.array_equal(got, brute)
         want, _ = _ids(ds, TREE)
