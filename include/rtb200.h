@@ -233,6 +233,16 @@ int rtb_dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, size_t n,
                                  int key_bits, void *stream);
 int rtb_dev_inclusive_scan_u32(uint32_t *d_data, size_t n, void *stream);
 
+/* No counterpart in the reference: added for callers that
+ * cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+ * Same result as rtb_dev_inclusive_scan_u32, but the scan's tile sums live in a file-scope device
+ * array (129 KB per GPU that loads the library, until exit) instead of pool scratch: the call
+ * makes no cudaMalloc / cudaFree / pool allocation.  n <= RTB_SCAN_STATIC_MAX, else RTB_ERR_LIMIT.
+ * The current device must be d_data's.  All calls share the array: calls that overlap on the GPU
+ * (two streams, two threads) race -- one call at a time per device. */
+#define RTB_SCAN_STATIC_MAX ((size_t)1 << 26)
+int rtb_dev_inclusive_scan_u32_static(uint32_t *d_data, size_t n, void *stream);
+
 /* Dump the flattened hierarchy for structural tests: nodes (64 B each) and the
  * leaf-ordered triangle permutation.  Pass NULL buffers to query counts. */
 int rtb_scene_dump_tree(rtb_scene_t *h, void *nodes_out, size_t *n_nodes,

@@ -7,6 +7,7 @@
 // three launches per pass (tile histograms -> scan -> stable ranked scatter staged
 // through shared memory so the global writes are runs of consecutive addresses), all
 // scratch supplied by the caller.
+#include <mutex>
 #include "rtb_internal.h"
 
 namespace rtb {
@@ -282,3 +283,54 @@ int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_key
 }
 
 }  // namespace rtb
+
+// ------------------------------------------------------------------------------------
+// rtb_dev_inclusive_scan_u32_static: the scan of rtb_dev_inclusive_scan_u32 for callers
+// that may not allocate (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  No counterpart in the reference.
+// The tile sums of every level live in ONE file-scope device array, held by
+// every GPU that loads the library until the process exits:
+//   n <= RTB_SCAN_STATIC_MAX = 2^26 elements  ->  2^15 + 2^4 + 1 sums, 33 024 words = 129 KB.
+// The array is shared by all calls and keeps the last call's contents.  Nothing in it has to
+// start at zero (k_scan_tiles writes every tile sum before k_scan_add reads it), but two calls
+// that overlap on the GPU (different streams, or different host threads without ordering)
+// race on it: one call at a time per device.
+// In host code `g_scan_static` is only a stand-in for the symbol, NOT a device address; the
+// address comes from cudaGetSymbolAddress, once per device, with that device current.
+// ------------------------------------------------------------------------------------
+namespace rtb {
+namespace {
+constexpr size_t SCAN_STATIC_MAX = (size_t)1 << 26;
+constexpr size_t SCAN_STATIC_WORDS = 33024;
+static __device__ __align__(256) uint32_t g_scan_static[SCAN_STATIC_WORDS];
+constexpr int SCAN_STATIC_DEVICES = 64;
+std::mutex g_scan_static_mu;
+uint32_t *g_scan_static_ptr[SCAN_STATIC_DEVICES] = {nullptr};
+}  // namespace
+}  // namespace rtb
+
+extern "C" int rtb_dev_inclusive_scan_u32_static(uint32_t *d_data, size_t n, void *stream) {
+  using namespace rtb;
+  if (!n) return RTB_OK;
+  if (!d_data) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  if (n > SCAN_STATIC_MAX) {
+    set_error("rtb_dev_inclusive_scan_u32_static: %zu elements exceed the static scratch's limit of %zu "
+              "(RTB_SCAN_STATIC_MAX); use rtb_dev_inclusive_scan_u32", n, SCAN_STATIC_MAX);
+    return RTB_ERR_LIMIT;
+  }
+  if (scan_scratch_words(n) > SCAN_STATIC_WORDS) { set_error("static scan scratch too small"); return RTB_ERR_LIMIT; }
+  int device = -1;
+  RTB_CUDA(cudaGetDevice(&device));
+  if (device < 0 || device >= SCAN_STATIC_DEVICES) { set_error("device %d out of range", device); return RTB_ERR_LIMIT; }
+  uint32_t *scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_scan_static_mu);
+    if (!g_scan_static_ptr[device]) {
+      void *p = nullptr;
+      RTB_CUDA(cudaGetSymbolAddress(&p, g_scan_static));       // this device's copy of the array
+      g_scan_static_ptr[device] = (uint32_t *)p;
+    }
+    scratch = g_scan_static_ptr[device];
+  }
+  return dev_exclusive_scan_u32(d_data, n, scratch, SCAN_STATIC_WORDS, true, (cudaStream_t)stream, nullptr);
+}
