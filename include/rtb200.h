@@ -209,10 +209,16 @@ typedef struct rtb_stats {
 
 int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);
 
-/* State the projection pass of the last frame (or hit-id query) left: out[0] rectangle items,
- * out[1] != 0: it gave up (too many items or boxes across the camera plane), out[2] | out[3] << 32
- * rectangle area in samples (the frame also walks the tree when this exceeds 8 x its samples),
- * out[4] boxes across the camera plane (all zero when no projection pass ran);
+/* Measurement aid (bench.py): with profiling on, every frame records CUDA events between its
+ * kernels; rtb_scene_kernel_ms waits for the last frame and returns out[0] clears + k_rast_setup,
+ * out[1] k_rast_items, out[2] the frame kernel, out[3] the whole frame, in milliseconds. */
+int rtb_scene_profile(rtb_scene_t *h, int on);
+int rtb_scene_kernel_ms(rtb_scene_t *h, double out[4]);
+
+/* State the projection pass of the last frame (or hit-id query) left: out[0] items,
+ * out[1] != 0: it gave up (too many items, a triangle over too many tiles), out[2] | out[3] << 32
+ * samples the items cover (the frame walks the tree when this exceeds 20 x its samples),
+ * out[4] triangles whose accept region has two parts (region.cuh; all zero when no pass ran);
  * out[5] lights with a shadow-ray grid, out[6] their list entries / 1024, out[7] their cells / 1024. */
 int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]);
 

@@ -130,7 +130,7 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
     RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, (cap + 3 * (size_t)S.n_tris) * sizeof(uint4), st));   // items, then edge records
     S.d_rast_cap = cap;
   }
-  if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, RAST_STATE_WORDS * 4, st));
+  if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, (RAST_STATE_WORDS + (1u << 16)) * 4, st));   // state words, then the big list
   // the camera in double precision and the rounding scales of this frame's rays (region::CamFrame)
   {
     region::CamFrame &cf = fa.camf;
@@ -164,6 +164,7 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   fa.rast_rec = reinterpret_cast<float4 *>(S.d_rast_items + S.d_rast_cap);
   fa.rast_cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
   fa.rast = S.d_rast;
+  fa.rast_big = S.d_rast + RAST_STATE_WORDS;
   return RTB_OK;
 }
 
@@ -193,7 +194,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
-  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_cap = 0; fa.rast_area_factor = 0;
+  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_big = nullptr; fa.rast_cap = 0; fa.rast_area_factor = 0;
   // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
@@ -266,7 +267,9 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     }
   }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
-  rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches);
+  if (S.profile && !S.kev[0])
+    for (cudaEvent_t &e : S.kev) RTB_CUDA(cudaEventCreate(&e));
+  rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches, S.profile ? S.kev : nullptr);
   if (rc) return rc;
   RTB_CUDA(cudaEventRecord(S.ev1, st));
   if (record) {
@@ -685,6 +688,30 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
       out->mode_cost |= rel << (16 * (k - 1));
     }
   out->builder = (uint64_t)S.builder;
+  return RTB_OK;
+}
+
+int rtb_scene_profile(rtb_scene_t *h, int on) {
+  if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  h->store.profile = on != 0;
+  return RTB_OK;
+}
+
+int rtb_scene_kernel_ms(rtb_scene_t *h, double out[4]) {
+  if (!h || !out) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  for (int k = 0; k < 4; ++k) out[k] = 0.0;
+  if (!S.kev[0]) { set_error("rtb_scene_profile was not switched on before the frame"); return RTB_ERR_ARG; }
+  RTB_CUDA(cudaSetDevice(S.device));
+  RTB_CUDA(cudaEventSynchronize(S.kev[3]));
+  for (int k = 0; k < 3; ++k) {
+    float ms = 0;
+    RTB_CUDA(cudaEventElapsedTime(&ms, S.kev[k], S.kev[k + 1]));
+    out[k] = ms;
+  }
+  float ms = 0;
+  RTB_CUDA(cudaEventElapsedTime(&ms, S.kev[0], S.kev[3]));
+  out[3] = ms;
   return RTB_OK;
 }
 

@@ -923,6 +923,7 @@ void SceneStore::release() {
   rast_pending = false; rast_useless = false;
   d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);
+  for (cudaEvent_t &e : kev) { if (e) cudaEventDestroy(e); e = nullptr; }
   recycle_frame_ctx(*this);
 }
 

@@ -28,8 +28,11 @@ namespace {
 
 constexpr int RAST_TILE = 32;                 // samples
 constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
-// rast[] words: 0 item count, 1 fallback flag, 2-3 rectangle area (u64), 4 triangles with two regions
+// rast[] words: 0 item count, 1 fallback flag, 2-3 samples the items cover (u64), 4 triangles with two
+// regions, 5 triangles on the big list
 constexpr int RAST_WORDS = 8;
+constexpr unsigned RAST_BIG_TILES = 128;       // a rectangle over more tiles goes to k_rast_big (one CTA per triangle)
+constexpr unsigned RAST_BIG_CAP = 1u << 16;    // slots on that list; the rest is emitted by its own thread
 
 __device__ __forceinline__ bool rast_active(const FrameArgs &fa) {
   if (!fa.prim) return false;
@@ -68,7 +71,7 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   const bool any = c.kind != 0;
   const int x0 = c.x0, y0 = c.y0, x1 = c.x1, y1 = c.y1;
   const int ty0 = any ? y0 / RAST_TILE : 0, ty1 = any ? y1 / RAST_TILE : -1;
-  unsigned mine = 0, area = 0;
+  unsigned mine = 0, area = 0, big_k = 0;
   const int rt = fa.nranks == 1 ? (1 << 30) : RANK_TILE * fa.aliasing;      // rank tile edge in samples
   const bool single = any && x1 - x0 < RAST_TILE && y1 - y0 < RAST_TILE && x0 / rt == x1 / rt && y0 / rt == y1 / rt;
   const bool gave_up = *reinterpret_cast<volatile unsigned *>(rast + 1) != 0;     // the frame has given up: emit nothing more
@@ -77,6 +80,9 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       mine = 1;
       area = (unsigned)((x1 - x0 + 1) * (y1 - y0 + 1));
     }
+  } else if (any && !gave_up && (unsigned)(ty1 - ty0 + 1) * (unsigned)(x1 / RAST_TILE - x0 / RAST_TILE + 1) > RAST_BIG_TILES &&
+             (big_k = atomicAdd(&rast[5], 1u)) < RAST_BIG_CAP) {
+    fa.rast_big[big_k] = s;                     // k_rast_big emits its items, tile rows in parallel
   } else if (any && !gave_up) {
     // "area" = the samples k_rast_items will look at: it walks these items row by row over the
     // region's span (region::record_span), so a thin region costs its length, not its rectangle
@@ -111,13 +117,16 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
     if (wa) atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)wa);
   }
   base = __shfl_sync(0xffffffffu, base, 31);
-  if (!mine) return;
-  unsigned k = base + incl - mine;
-  if (base + total > fa.rast_cap) { rast[1] = 1u; return; }
+  const bool listed = any && !single && !gave_up && !mine && big_k < RAST_BIG_CAP &&
+                      (unsigned)(ty1 - ty0 + 1) * (unsigned)(x1 / RAST_TILE - x0 / RAST_TILE + 1) > RAST_BIG_TILES;
+  if (!mine && !listed) return;
+  if (mine && base + total > fa.rast_cap) { rast[1] = 1u; return; }
   const float *rv = c.rec.v;
   fa.rast_rec[3 * (size_t)s] = make_float4(rv[0], rv[1], rv[2], rv[3]);
   fa.rast_rec[3 * (size_t)s + 1] = make_float4(rv[4], rv[5], rv[6], rv[7]);
   fa.rast_rec[3 * (size_t)s + 2] = make_float4(rv[8], rv[9], rv[10], rv[11]);
+  if (!mine) return;
+  unsigned k = base + incl - mine;
   if (single) {
     fa.rast_items[k] = make_uint4(s, (unsigned)x0 | ((unsigned)y0 << 16), (unsigned)x1 | ((unsigned)y1 << 16), 0u);
     return;
@@ -132,6 +141,65 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
         const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
         fa.rast_items[k++] = make_uint4(s, (unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), 0u);
       }
+  }
+}
+
+// k_rast_big: the triangles k_rast_setup listed because their rectangles span many tiles (a road
+// across the frame, a triangle seen edge-on whose region is a line across the screen).  One CTA
+// per triangle, one thread per tile row: region::primary_row_tiles gives the tiles of the row the
+// region can touch, every row takes its slots with one atomic.
+constexpr int RAST_BIG_THREADS = 128;
+__global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc, const FrameArgs fa) {
+  __shared__ unsigned s_touched, s_mine;
+  unsigned *rast = fa.rast;
+  const unsigned n_big = min(rast[5], RAST_BIG_CAP);
+  for (unsigned bi = blockIdx.x; bi < n_big; bi += gridDim.x) {
+    if (*reinterpret_cast<volatile unsigned *>(rast + 1)) return;
+    const uint32_t s = fa.rast_big[bi];
+    const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
+    const float v0[3] = {a4.x, a4.y, a4.z}, e1[3] = {b4.x, b4.y, b4.z}, e2[3] = {c4.x, c4.y, c4.z};
+    region::PrimaryCull c;
+    region::primary_cull(fa.camf, fa.cam.W, fa.cam.H, v0, e1, e2, c);       // as in k_rast_setup: same bits
+    if (!c.kind) continue;
+    if (threadIdx.x == 0) { s_touched = 0; s_mine = 0; }
+    __syncthreads();
+    const int ty0 = c.y0 / RAST_TILE, ty1 = c.y1 / RAST_TILE;
+    unsigned touched = 0, mine = 0;
+    for (int ty = ty0 + (int)threadIdx.x; ty <= ty1; ty += RAST_BIG_THREADS) {
+      int ta, tb;
+      if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
+      touched += (unsigned)(tb - ta + 1);
+      if (fa.nranks == 1) mine += (unsigned)(tb - ta + 1);
+      else for (int tx = ta; tx <= tb; ++tx) mine += rast_owned(fa, tx, ty) ? 1u : 0u;
+    }
+    if (touched) atomicAdd(&s_touched, touched);
+    if (mine) atomicAdd(&s_mine, mine);
+    __syncthreads();
+    const unsigned all_touched = s_touched, all_mine = s_mine;
+    __syncthreads();
+    if (!all_mine) continue;
+    if (all_mine > RAST_TILES_MAX) { if (threadIdx.x == 0) rast[1] = 1u; return; }
+    if (threadIdx.x == 0) {
+      const double rect = (double)(c.x1 - c.x0 + 1) * (double)(c.y1 - c.y0 + 1);
+      const double work = fmin(c.R.work, rect) * (double)all_mine / (double)all_touched + 32.0 * (double)all_mine;
+      atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)fmin(work, 1.0e15));
+    }
+    for (int ty = ty0 + (int)threadIdx.x; ty <= ty1; ty += RAST_BIG_THREADS) {
+      int ta, tb;
+      if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
+      unsigned cnt = 0;
+      if (fa.nranks == 1) cnt = (unsigned)(tb - ta + 1);
+      else for (int tx = ta; tx <= tb; ++tx) cnt += rast_owned(fa, tx, ty) ? 1u : 0u;
+      if (!cnt) continue;
+      unsigned k = atomicAdd(&rast[0], cnt);
+      if (k + cnt > fa.rast_cap) { rast[1] = 1u; continue; }
+      const int cy0 = max(c.y0, ty * RAST_TILE), cy1 = min(c.y1, ty * RAST_TILE + RAST_TILE - 1);
+      for (int tx = ta; tx <= tb; ++tx)
+        if (rast_owned(fa, tx, ty)) {
+          const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
+          fa.rast_items[k++] = make_uint4(s, (unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), 0u);
+        }
+    }
   }
 }
 
@@ -161,7 +229,7 @@ __device__ __forceinline__ void rast_test(const DevScene &sc, const FrameArgs &f
 __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene sc, const FrameArgs fa) {
   __shared__ uint2 queue[RAST_WARPS][64];
   if (!rast_active(fa)) return;
-  const unsigned n = fa.rast[0];
+  const unsigned n = min(fa.rast[0], fa.rast_cap);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const unsigned lt = (1u << lane) - 1u;
   const unsigned warps = gridDim.x * RAST_WARPS;
@@ -194,18 +262,36 @@ __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene s
         }
       }
     } else {
-      // big rectangle (a tile of a big or a thin region): one row per lane, each lane walks the span
-      // of its row that the record can pass (region::record_span, a superset; record_inside decides)
+      // big rectangle (a tile of a big or a thin region): lane r takes row r and finds the span of
+      // its row that the record can pass (region::record_span, a superset; record_inside decides);
+      // the spans' samples are then numbered through (prefix sums over the lanes) and taken 32 at
+      // a time, so a thin region costs its length and every round runs with full lanes
       const int h = y1 - y0 + 1;                  // <= 32
       int a = 1, b = 0;
       if (lane < h) region::record_span(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, ox, w, oy + (float)lane, a, b);
-      const int longest = __reduce_max_sync(0xffffffffu, b - a + 1);
-      for (int j = 0; j < longest; ++j) {
-        const int rx = a + j;
-        const bool in = rx <= b && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
-                                                           ox + (float)rx, oy + (float)lane);
+      const int len = max(b - a + 1, 0);
+      int P = len;                                // inclusive prefix sum of the span lengths
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, P, d);
+        if (lane >= d) P += o;
+      }
+      const int T = __shfl_sync(0xffffffffu, P, 31);
+      const int Pex = P - len;
+      for (int k0 = 0; k0 < T; k0 += 32) {
+        const int k = k0 + lane;
+        int row = 0;                              // number of rows whose spans end at or before sample k
+#pragma unroll
+        for (int step = 16; step; step >>= 1) {
+          const int pr = __shfl_sync(0xffffffffu, P, row + step - 1);
+          if (pr <= k) row += step;
+        }
+        const int ar = __shfl_sync(0xffffffffu, a, row), pe = __shfl_sync(0xffffffffu, Pex, row);
+        const int rx = ar + (k - pe);
+        const bool in = k < T && region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w,
+                                                         ox + (float)rx, oy + (float)row);
         const unsigned mask = __ballot_sync(0xffffffffu, in);
-        if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + lane) << 16));
+        if (in) Q[qn + __popc(mask & lt)] = make_uint2(it.x, (unsigned)(x0 + rx) | ((unsigned)(y0 + row) << 16));
         qn += __popc(mask);
         __syncwarp();
         if (qn >= 32) {

@@ -98,8 +98,9 @@ RTB_RG void build(const Lines &L, double dx0, double dx1, double dy0, double dy1
   double len[3];
   for (int k = 0; k < 3; ++k) len[k] = sqrt(L.cx[k] * L.cx[k] + L.cy[k] * L.cy[k]);
   bool plus = false, minus = false, done = false;
-  // Fast path: the three gradients positively span the plane (a bounded triangle), one of S+ / S- is
-  // empty and the other lies inside the domain -- its corners are the pairwise intersections.
+  // Fast path: the three gradients positively span the plane (a bounded triangle).  Then S+ and S-
+  // are both triangles (or empty) whose corners are the pairwise intersections of the offset lines;
+  // when they lie inside the domain nothing has to be clipped.
   {
     const double x01 = L.cx[0] * L.cy[1] - L.cy[0] * L.cx[1], x12 = L.cx[1] * L.cy[2] - L.cy[1] * L.cx[2],
                  x20 = L.cx[2] * L.cy[0] - L.cy[2] * L.cx[0];
@@ -112,21 +113,28 @@ RTB_RG void build(const Lines &L, double dx0, double dx1, double dy0, double dy1
       const double sg = pos ? 1.0 : -1.0;
       const double K = sg * (l0 * L.c0[0] + l1 * L.c0[1] + l2 * L.c0[2]);
       const double KE = sg * (l0 * L.E[0] + l1 * L.E[1] + l2 * L.E[2]);      // > 0
-      // S+ is non-empty iff K >= -KE, S- iff K <= KE; a margin keeps borderline cases on the general path
-      const bool p_only = K > 1.000001 * KE, m_only = K < -1.000001 * KE;
-      if (p_only || m_only) {
-        const double s = p_only ? 1.0 : -1.0;         // the region is  s F_k >= -E_k
-        const double b0 = -s * L.E[0] - L.c0[0], b1 = -s * L.E[1] - L.c0[1], b2 = -s * L.E[2] - L.c0[2];
+      // S+ = { F_k >= -E_k } is non-empty iff K >= -KE, S- = { F_k <= E_k } iff K <= KE (a hair of margin: a
+      // part that is "just empty" is kept as a point-sized triangle)
+      const bool has_p = K >= -1.000001 * KE, has_m = K <= 1.000001 * KE;
+      double x0 = BIG, x1 = -BIG, y0 = BIG, y1 = -BIG, work = 0.0;
+      for (int part = 0; part < 2; ++part) {
+        if (!(part ? has_m : has_p)) continue;
+        const double sp = part ? -1.0 : 1.0;          // the part is  sp F_k >= -E_k
+        const double b0 = -sp * L.E[0] - L.c0[0], b1 = -sp * L.E[1] - L.c0[1], b2 = -sp * L.E[2] - L.c0[2];
         const double ax = (b0 * L.cy[1] - b1 * L.cy[0]) / x01, ay = (L.cx[0] * b1 - L.cx[1] * b0) / x01;
         const double bx = (b1 * L.cy[2] - b2 * L.cy[1]) / x12, by = (L.cx[1] * b2 - L.cx[2] * b1) / x12;
         const double cx = (b2 * L.cy[0] - b0 * L.cy[2]) / x20, cy = (L.cx[2] * b0 - L.cx[0] * b2) / x20;
-        const double x0 = fmin(ax, fmin(bx, cx)), x1 = fmax(ax, fmax(bx, cx));
-        const double y0 = fmin(ay, fmin(by, cy)), y1 = fmax(ay, fmax(by, cy));
+        const double px0 = fmin(ax, fmin(bx, cx)), px1 = fmax(ax, fmax(bx, cx));
+        const double py0 = fmin(ay, fmin(by, cy)), py1 = fmax(ay, fmax(by, cy));
+        x0 = fmin(x0, px0); x1 = fmax(x1, px1); y0 = fmin(y0, py0); y1 = fmax(y1, py1);
+        work += 0.5 * fabs((bx - ax) * (cy - ay) - (cx - ax) * (by - ay)) + 2.0 * ((px1 - px0) + (py1 - py0)) + 1.0;
+      }
+      if (has_p || has_m) {
         if (x1 < dx0 || x0 > dx1 || y1 < dy0 || y0 > dy1) return;             // off the domain (NaN falls through)
         if (x0 >= dx0 && x1 <= dx1 && y0 >= dy0 && y1 <= dy1) {
           R.x0 = x0; R.x1 = x1; R.y0 = y0; R.y1 = y1;
-          R.work = 0.5 * fabs((bx - ax) * (cy - ay) - (cx - ax) * (by - ay)) + 2.0 * ((x1 - x0) + (y1 - y0)) + 1.0;
-          plus = p_only; minus = m_only; done = true;
+          R.work = work;
+          plus = has_p; minus = has_m; done = true;
         }
       }
     }

@@ -130,6 +130,7 @@ struct FrameArgs {
   unsigned rast_cap;              // capacity of rast_items
   float4 *rast_rec;               // 3 per triangle slot: edge record of the projected triangle (raster.cuh)
   unsigned *rast;                 // counters and flags (raster.cuh RAST_WORDS)
+  unsigned *rast_big;             // [RAST_BIG_CAP] slots of triangles whose items k_rast_big emits
   region::CamFrame camf;          // the camera in double precision + the rounding scales of this frame (region.cuh)
   unsigned rast_area_factor;      // give up when the rectangles cover more than this many times the frame
   // wavefront kernel only
@@ -152,8 +153,10 @@ int dev_inclusive_scan_u64(uint64_t *d_data, size_t n, uint64_t *d_scratch, size
 size_t scan_scratch_words(size_t n);
 
 // ---- frame kernels (trace.cu) ----
+// marks: nullptr, or 4 events recorded before the frame's first operation, after k_rast_setup, after
+// k_rast_items and after the frame kernel (rtb_scene_profile)
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
-                 unsigned long long *launches);
+                 unsigned long long *launches, cudaEvent_t *marks = nullptr);
 unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
 int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,

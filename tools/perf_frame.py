@@ -33,6 +33,7 @@ else:
 ds = pyrtb.DeviceScene(hs, 3, flags=a.flags)
 ds.frame_kernel = int(a.wave)
 ds.primary = a.primary
+ds.profile(True)
 st = ds.stats()
 print("build %.2f ms upload %.2f ms nodes %d depth %d  builder %d key mode %d (sample-tree cost of modes 1,2,3 vs 0: %s)" %
       (st["build_ms"], st["upload_ms"], st["nodes"], st["max_depth"], st["builder"], st["key_mode"],
@@ -42,11 +43,13 @@ for k in ks:
     if k is not None:
         pyrtb.lib().rtb_set_margin_k(k)
     img = ds.render()
-    t = []
+    t, km = [], []
     for _ in range(a.frames):
         img = ds.render()
         t.append(ds.stats()["frame_ms"])
-    line = "K=%s frame ms: min %.2f median %.2f  checksum %d" % (k, min(t), float(np.median(t)), int(img.astype(np.uint64).sum()))
+        km.append(ds.kernel_ms())
+    line = "K=%s frame ms: min %.2f median %.2f  [setup %.2f items %.2f frame %.2f]  checksum %d" % (
+        k, min(t), float(np.median(t)), *np.median(np.array(km), axis=0)[:3], int(img.astype(np.uint64).sum()))
     if a.count:
         ds.render(count=True)
         s = ds.stats()
