@@ -132,13 +132,31 @@ def cpu_reference_run(hs, n_samples, threads, seed):
     return int(rays[0] + rays[1]), dt, kind
 
 
+TRIANGLES = 2 * GRID * GRID
+WORKLOAD = ("C5 synthetic terrain %d triangles (grid %d, seed 0x%X), %dx%d x %dx%d SSAA, 1 ambient + 1 directional + 1 point light"
+            % (TRIANGLES, GRID, SEED, WIDTH, HEIGHT, ALIASING, ALIASING))
+
+
+class HostOnlyScene:
+    """The C5 scene from librt_host.so (host surface only: no CUDA, none of the repo's tracing code) --
+    what the reference arm uses, so that librtb200.so is never mapped into that process."""
+
+    def __init__(self, grid, width, height, seed):
+        import pyrtb                      # ctypes struct definitions only; pyrtb.lib() is never called here
+        self.L = C.CDLL(os.path.join(ROOT, "raytracing-gpu_b200", "librt_host.so"))
+        self.s = pyrtb.SceneStruct()
+        self.L.rtb_synth_terrain.argtypes = [C.c_void_p, C.c_int, C.c_uint64, C.c_int, C.c_int]
+        if self.L.rtb_synth_terrain(C.byref(self.s), grid, seed, width, height) != 0:
+            raise RuntimeError("rtb_synth_terrain failed")
+        self.triangle_count = int(self.s.triangle_count)
+
+
 def run_reference(args):
     rank, _, world = dist_env()
     if rank != 0:
         return
-    import pyrtb
     threads = os.cpu_count() or 1
-    hs = pyrtb.HostScene.terrain(GRID, WIDTH, HEIGHT, SEED)
+    hs = HostOnlyScene(GRID, WIDTH, HEIGHT, SEED)
     per_step = max(threads, args.ref_samples)
     for _ in range(args.warmup):
         cpu_reference_run(hs, max(threads // 4, 1), threads, 1)
@@ -154,12 +172,70 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total_s / max(args.steps, 1), "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C5 synthetic terrain %d triangles, %dx%d, 1 ambient + 1 directional + 1 point light"
-                   % (hs.triangle_count, WIDTH, HEIGHT), "sample": sample},
+        "config": {"workload": WORKLOAD, "sample": sample,
+                   "semantics": "the reference's CPU renderer (cpu/: 2x2 sub-samples, float colours); a sampled baseline, "
+                                "not a parity target"},
+        "native_so": "raytracing-gpu_b200/librt_host.so (scene generation only, no CUDA) + oracle/_ref/libref_cpu.so",
         "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }), file=_JSON_OUT, flush=True)
+
+
+# ------------------------------------------------------------------------------------
+# C1-C4 of BASELINE.json (the shipped scenes at their quoted sizes): our frame / render() and the
+# reference's own GPU render() (oracle/_ref/libref_gpu.so: its unmodified gpu/*.cu built for sm_100,
+# run in a child process) on the same box -- SURVEY 8(d)'s "existing kernel on the same box" bar.
+# Context for the headline, not the headline: the reference cannot run C5 (object-level tree).
+# ------------------------------------------------------------------------------------
+SMALL = [("C1", "triangle", 512, 512), ("C2a", "dir-light-shadows", 1920, 1080), ("C2b", "point-light", 1920, 1080),
+         ("C3", "susans_smooth", 1920, 1080), ("C4", "car-on-road", 3840, 2160)]
+
+
+def small_configs(args):
+    import pyrtb
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    out = {}
+    try:
+        from util import load_golden
+    except Exception as ex:
+        return {"unavailable": str(ex)}
+    ref_so = os.path.join(ROOT, "oracle", "_ref", "libref_gpu.so")
+    for cfg, name, w, h in SMALL:
+        try:
+            hs = load_golden(name)[0].with_resolution(w, h)
+            ds = pyrtb.DeviceScene(hs, ALIASING)
+            ds.render(count=True)
+            st = ds.stats()
+            ts = []
+            for _ in range(8):
+                ds.render()
+                ts.append(ds.stats()["frame_ms"])
+            ds.close()
+            img = np.empty((h, w, 4), np.uint8)
+            to = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                pyrtb.render_oneshot(hs, ALIASING, out=img)
+                to.append(1e3 * (time.perf_counter() - t0))
+            rays = st["rays_primary"] + st["rays_shadow"]
+            row = {"scene": name, "output": "%dx%d" % (w, h), "triangles": hs.triangle_count, "rays": int(rays),
+                   "frame_ms": float(np.median(ts[3:])), "mrays_s": rays / float(np.median(ts[3:])) / 1e3,
+                   "render_ms": min(to[1:]), "ref_gpu_render_ms": None}
+            if os.path.exists(ref_so):
+                try:
+                    r = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "reports", "config_table.py"), "--ref-gpu-one",
+                                        name, str(w), str(h)], capture_output=True, text=True, timeout=120)
+                    ln = [l for l in r.stdout.splitlines() if l.startswith("REFGPU")]
+                    if ln:
+                        row["ref_gpu_render_ms"] = float(ln[-1].split()[1])
+                        row["render_speedup_vs_ref_gpu"] = row["ref_gpu_render_ms"] / row["render_ms"]
+                except subprocess.TimeoutExpired:
+                    row["ref_gpu_render_ms"] = "timeout (120 s)"
+            out[cfg] = row
+        except Exception as ex:
+            out[cfg] = {"scene": name, "error": str(ex)}
+    return out
 
 
 # ------------------------------------------------------------------------------------
@@ -222,44 +298,87 @@ def run_ours(args):
     def frame(count=False):
         ds.render_device(d_frame, pitch, rank=rank, nranks=world, count=count)
 
-    # ray accounting: one untimed instrumented frame (device counters)
-    frame(count=True)
-    ds.sync()
-    st = ds.stats()
-    counts = np.array([st["rays_primary"], st["rays_shadow"], st["rays_bounce"], st["node_visits"], st["tri_tests"]],
-                      dtype=np.float64)
-    if dist is not None:
-        import torch
-        t = torch.tensor(counts, dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        counts = t.cpu().numpy()
-    primary, shadow, bounce, node_visits, tri_tests = [int(x) for x in counts]
-    rays = primary + shadow
+    # Camera path: the headline times a fly-through, one new camera per frame (a dolly along the view
+    # direction with a little side-slip), so that nothing a frame learns about its camera (the
+    # longest-first item order, the projection pass's verdict) is reused on the camera it came from.
+    cam0 = pyrtb.Camera()
+    C.memmove(C.byref(cam0), C.byref(hs.scaled(ALIASING).camera), C.sizeof(pyrtb.Camera))
+    u = np.array([cam0.u.x, cam0.u.y, cam0.u.z]); v = np.array([cam0.v.x, cam0.v.y, cam0.v.z])
+    u /= np.linalg.norm(u); v /= np.linalg.norm(v)
+    forward = -np.cross(u, v)                       # the scene lies opposite the image plane (gpu/raytracer.cu:181-182)
 
-    for _ in range(args.warmup):
+    def camera_at(k):
+        c = pyrtb.Camera()
+        C.memmove(C.byref(c), C.byref(cam0), C.sizeof(pyrtb.Camera))
+        p = np.array([cam0.position.x, cam0.position.y, cam0.position.z]) + forward * (0.25 * k) + u * (0.1 * k)
+        c.position = pyrtb.Vec3(float(p[0]), float(p[1]), float(p[2]))
+        return c
+
+    def count_rays(cam):
+        """one untimed instrumented frame (device counters); it walks the tree for every ray"""
+        ds.set_camera(cam)
+        frame(count=True)
+        ds.sync()
+        st = ds.stats()
+        cnt = np.array([st["rays_primary"], st["rays_shadow"], st["rays_bounce"], st["node_visits"], st["tri_tests"]],
+                       dtype=np.float64)
+        if dist is not None:
+            import torch
+            t = torch.tensor(cnt, dtype=torch.float64, device="cuda")
+            dist.all_reduce(t)
+            cnt = t.cpu().numpy()
+        return cnt
+
+    path = [camera_at(k) for k in range(args.steps)]
+    counts0 = count_rays(cam0)
+    counts_path = np.sum([count_rays(c) for c in path], axis=0)
+    primary, shadow, bounce, node_visits, tri_tests = [int(x) for x in counts0]
+    rays = primary + shadow                                   # per frame, static camera
+    rays_path = int(counts_path[0] + counts_path[1])          # over the K frames of the path
+
+    for k in range(args.warmup, 0, -1):                       # warm-up frames on the cameras BEFORE the path
+        ds.set_camera(camera_at(-k))
         frame()
     ds.sync()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    # ---- timed region: K frames, CUDA events on the launching stream ----
-    kernel_ms = []
+    # ---- timed region: K frames, one camera each, CUDA events on the launching stream ----
     barrier()
     ds.timer_start()
-    for _ in range(args.steps):
+    for k in range(args.steps):
+        ds.set_camera(path[k])
         frame()
     ms_total = ds.timer_stop()
     barrier()
     ms_total = max_over_ranks(ms_total)
+    # ---- the same with one camera for all frames (what round 1 reported) ----
+    ds.set_camera(cam0)
+    for _ in range(args.warmup):
+        frame()
+    ds.sync()
+    barrier()
+    ds.timer_start()
+    for _ in range(args.steps):
+        frame()
+    ms_static = ds.timer_stop()
+    barrier()
+    ms_static = max_over_ranks(ms_static)
     clocks = sampler.stop() if rank == 0 else None
-    # per-launch duration of the frame kernel (events around each launch, same stream)
-    for _ in range(min(args.steps, 10)):
+    # per-kernel durations of a frame (events between the launches, same stream), moving camera again
+    ds.profile(True)
+    kernel_ms, parts = [], []
+    for k in range(min(args.steps, 10)):
+        ds.set_camera(path[k])
         frame()
         ds.sync()
         kernel_ms.append(ds.stats()["frame_ms"])
+        parts.append(ds.kernel_ms())
+    ds.profile(False)
     kernel_ms_avg = max_over_ranks(float(np.mean(kernel_ms)))
-    launches_per_frame = int(ds.stats()["kernel_launches"])      # projection pass (2) + frame kernel
+    parts = np.mean(np.array(parts), axis=0)
+    launches_per_frame = int(ds.stats()["kernel_launches"])      # projection pass (3) + frame kernel
     rstate = ds.raster_state()
     per_rank_ms = [float(np.mean(kernel_ms))]
     if dist is not None:
@@ -268,6 +387,7 @@ def run_ours(args):
         t[rank] = per_rank_ms[0]
         dist.all_reduce(t)
         per_rank_ms = [round(float(x), 3) for x in t.cpu().tolist()]
+    ds.set_camera(cam0)
     barrier()
 
     # ---- e2e: the drop-in call with HOST buffers ----
@@ -294,8 +414,26 @@ def run_ours(args):
         e2e["resident"] = {"value": rays / res_s / 1e6, "ms_per_step": 1e3 * res_s, "h2d_bytes_per_step": 48,
                            "d2h_bytes_per_step": frame_bytes, "call": "rtb_scene_render"}
     else:
-        # all ranks render their tiles into rank 0's device frame; rank 0 downloads it
+        # the SAME call as at N = 1: the one-shot render(), here on N devices of rank 0's process
+        # (rtb_render_multi: every device uploads the scene and builds its hierarchy, renders its tiles
+        # into device 0's frame over NVLink; rank 0 downloads).  The other ranks wait.
         e2e_steps = max(2, min(args.steps, args.e2e_steps))
+        barrier()
+        e2e_s = 0.0
+        if rank == 0:
+            pyrtb.render_multi(hs, world, ALIASING, out=host_img)     # warm-up: contexts, peer access, pools
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                pyrtb.render_multi(hs, world, ALIASING, out=host_img)
+            e2e_s = (time.perf_counter() - t0) / e2e_steps
+            multi_img = host_img.copy()
+        barrier()
+        h2d = hs.triangle_count * 72 + 72 * hs.s.object_count + 28 * hs.s.light_count + 48
+        e2e = {"value": rays / e2e_s / 1e6 if rank == 0 else None, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d) * world,
+               "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * e2e_s,
+               "call": "rtb_render_multi (= render() with RT_GPUS = N): scene upload + hierarchy build on every device, "
+                       "tiles stored into device 0's frame over NVLink, download"}
+        # resident-scene variant: all ranks render their tiles into rank 0's device frame; rank 0 downloads it
         barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
@@ -305,13 +443,18 @@ def run_ours(args):
             if rank == 0:
                 pyrtb._check(L.rtb_dev_download(host_img.ctypes.data, d_frame, frame_bytes))
         barrier()
-        e2e_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
-        e2e = {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 48,
-               "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * e2e_s,
-               "call": "rtb_scene_render_device on every rank (tiles stored into rank 0's frame over NVLink) + download"}
+        res_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+        e2e["resident"] = {"value": rays / res_s / 1e6, "ms_per_step": 1e3 * res_s, "h2d_bytes_per_step": 48,
+                           "d2h_bytes_per_step": frame_bytes,
+                           "call": "rtb_scene_render_device on every rank (tiles stored into rank 0's frame over NVLink) + download"}
 
-    # frame check: the composed frame equals a single-GPU frame of the same scene
+    # frame check: the composed frame equals a single-GPU frame of the same scene (camera 0)
+    ds.set_camera(cam0)
+    frame()
+    ds.sync()
+    barrier()
     checksum = None
+    oneshot_diff = None
     if rank == 0:
         pyrtb._check(L.rtb_dev_download(host_img.ctypes.data, d_frame, frame_bytes))
         composed = host_img.copy()
@@ -319,6 +462,10 @@ def run_ours(args):
             single = ds.render()
             if not np.array_equal(single, composed):
                 raise SystemExit("multi-GPU frame differs from the single-GPU frame")
+            # the one-shot call builds the one-frame hierarchy (no cluster rebuild above 2^18 triangles)
+            oneshot_diff = int((single != multi_img).any(axis=-1).sum())
+            if oneshot_diff > 100:
+                raise SystemExit("rtb_render_multi frame differs from the single-GPU frame in %d pixels" % oneshot_diff)
         checksum = int(composed.astype(np.uint64).sum())
 
     if rank == 0:
@@ -326,44 +473,64 @@ def run_ours(args):
         sm_count = 148
         issue_peak_tflops = sm_count * 128 * pk["sm_max_mhz"] * 1e6 / 1e12     # un-fused FP32 op/s = issue slots
         step_s = ms_total / 1e3 / args.steps
+        static_s = ms_static / 1e3 / args.steps
         kern_s = kernel_ms_avg / 1e3
         alg_ops = primary * OPS_PRIMARY + shadow * OPS_SHADOW + bounce * OPS_PRIMARY
         alg_bytes = primary * BYTES_PRIMARY + shadow * BYTES_SHADOW + bounce * BYTES_PRIMARY
         achieved_tflops = alg_ops / world / kern_s / 1e12        # per GPU: each rank's kernel does 1/world of the rays
+        kernels_live = {"clears+k_rast_setup+k_rast_big": float(parts[0]), "k_rast_items": float(parts[1]),
+                        "k_frame": float(parts[2]), "frame": float(parts[3])}
+        dominant = max(("clears+k_rast_setup+k_rast_big", "k_rast_items", "k_frame"), key=lambda k: kernels_live[k])
         roofline = {
             "bound": "fp32_issue",
-            "kernel": "k_frame<tree>" if launches_per_frame == 1 else "the frame's kernels: k_rast_setup + k_rast_items + k_frame<tree>",
+            "kernel": "k_frame<tree>" if launches_per_frame == 1 else "the frame's kernels: k_rast_setup + k_rast_big + k_rast_items + k_frame<tree>",
             "achieved": achieved_tflops, "peak": issue_peak_tflops,
             "unit": "TFLOP/s", "frac": achieved_tflops / issue_peak_tflops, "traffic": None,
+            "equivalent_tree_walk_frac": achieved_tflops / issue_peak_tflops,
             "peak_source": "148 SMs x 128 FP32 lanes x sm_max_mhz, %s" % pk["source"],
-            "note": "divergent traversal + scalar FP32: the binding ceiling is SM instruction issue, not HBM or "
-                    "tensor cores (SURVEY 8d); achieved = algorithmic un-fused FP32 ops per frame (SURVEY 8d per-ray "
-                    "figures x rays) / CUDA-event duration of the frame's launches",
+            "note": "frac is NOMINAL ('equivalent tree-walk throughput'): SURVEY 8(d)'s per-ray op counts describe tree walks "
+                    "(24 node visits, 8 / 4 triangle tests), while the timed frame resolves primary rays by the projection "
+                    "pass and shadow rays by the light grids; it is algorithmic ops per frame / CUDA-event duration of the "
+                    "frame's launches / the un-fused FP32 (= issue) peak.  What the kernels actually achieve is under "
+                    "'measured' (ncu: issue-slot utilisation, lanes per instruction, DRAM bytes).  Divergent traversal + scalar "
+                    "FP32: neither HBM nor tensor cores bind (SURVEY 8d)",
             "algorithmic_ops_per_launch": alg_ops // world, "kernel_ms": kernel_ms_avg,
             "kernel_ms_per_rank": per_rank_ms,
+            "kernels_ms_live": kernels_live, "dominant_kernel": dominant,
+            "kernel_share_live": {k: kernels_live[k] / max(kernels_live["frame"], 1e-9) for k in kernels_live if k != "frame"},
             "hbm": None,
             "request_volume_gbs": alg_bytes / world / kern_s / 1e9,   # cache-less: 64 B per node visit, 48 B per triangle test
-            "measured_per_ray": {"node_visits": node_visits / max(rays + bounce, 1),
-                                 "tri_tests": tri_tests / max(rays + bounce, 1),
-                                 "note": "device counters of the untimed counting frame, which walks the tree for every ray"},
+            "tree_walk_counts_per_ray": {"node_visits": node_visits / max(rays + bounce, 1),
+                                         "tri_tests": tri_tests / max(rays + bounce, 1),
+                                         "note": "device counters of the UNTIMED counting frame, which walks the tree for every "
+                                                 "ray; the timed frame does not (see paths); the ray counts come from that frame too"},
             "paths": {"primary": "projection pass (raster.cuh)" if launches_per_frame > 1 and not rstate["gave_up"] else "tree walk",
                       "shadow": "%d light grid(s) (lightgrid.cuh)" % rstate["light_grids"] if rstate["light_grids"] else "tree walk",
-                      "projection_items": rstate["items"], "projection_area_samples": rstate["area"],
+                      "projection_items": rstate["items"], "projection_work_samples": rstate["area"],
                       "light_grid_entries_k": rstate["grid_entries_k"], "launches_per_frame": launches_per_frame},
         }
-        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(traffic_file):
+        # measured counters of the frame's kernels: one ncu --set full capture of tools/perf_frame.py on this
+        # workload, summarised by tools/ncu_json.py and committed (a number taken under ncu is never a bench value)
+        ncu_file = os.path.join(ROOT, "profiles", "r2_ncu_frame.json")
+        if os.path.exists(ncu_file):
             try:
-                tj = json.load(open(traffic_file))
-                roofline["traffic"] = tj.get("frame_dram_bytes", tj.get("k_frame_dram_bytes_per_launch"))
-            except Exception:
-                pass
+                nj = json.load(open(ncu_file))
+                roofline["measured"] = {"source": "profiles/r2_ncu_frame.json (%s)" % nj.get("source", ""), "kernels": nj["kernels"]}
+                roofline["traffic"] = int(sum(k["dram_bytes"] for k in nj["kernels"].values()))
+                dk = nj["kernels"].get("k_frame")
+                if dk:
+                    roofline["issue_active_frac_measured"] = dk["issue_active_pct"] / 100.0
+            except Exception as ex:
+                roofline["measured"] = {"error": str(ex)}
         if roofline["traffic"] and world == 1:
             # the HBM view SURVEY 8(d) asks for beside the issue roofline: DRAM bytes of the ncu capture / launch time
             gbs = roofline["traffic"] / kern_s / 1e9
             roofline["hbm"] = {"achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
-                               "note": "dram__bytes_read+write of one ncu --set full capture (profiles/traffic.json) / "
-                                       "live duration of the frame's launches: HBM does not bind these kernels"}
+                               "note": "dram__bytes_read+write of the frame's launches in the ncu capture / live duration of "
+                                       "the frame's launches: HBM does not bind these kernels"}
+        configs = None
+        if world == 1 and not args.no_ref_gpu:
+            configs = small_configs(args)
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
@@ -377,12 +544,15 @@ def run_ours(args):
             except Exception as ex:   # the checker library is test infrastructure: report, do not fail the bench
                 cpu = {"value": None, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": "unavailable: %s" % ex}
         out = {
-            "metric": METRIC, "value": rays / step_s / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "metric": METRIC, "value": rays_path / (ms_total / 1e3) / 1e6, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * step_s, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C5 synthetic terrain %d triangles (grid %d, seed 0x%X), %dx%d x %dx%d SSAA, "
-                                   "1 ambient + 1 directional + 1 point light" %
-                                   (hs.triangle_count, GRID, SEED, WIDTH, HEIGHT, ALIASING, ALIASING),
+            "static_camera": {"value": rays / static_s / 1e6, "unit": "Mrays/s", "ms_per_step": 1e3 * static_s,
+                              "note": "the same K frames with ONE camera: longest-first scheduling then replays the costs of the "
+                                      "identical previous frame; the headline moves the camera every frame"},
+            "config": {"workload": WORKLOAD,
+                       "camera": "fly-through: one new camera per timed frame (0.25 units forward + 0.1 sideways per frame, "
+                                 "rtb_scene_set_camera); rays counted per camera in untimed frames",
                        "parallelism": "interleaved 32x32-pixel tiles over %d GPU(s), scene replicated, tiles stored "
                                       "into rank 0's frame over NVLink" % world,
                        "l2": "inputs larger than L2 (triangles 960 MB + nodes %d MB vs 126 MB L2)" % (st0["tree_bytes"] >> 20),
@@ -391,7 +561,8 @@ def run_ours(args):
             "build": {"upload_ms": st0["upload_ms"], "build_ms": st0["build_ms"], "nodes": st0["nodes"],
                       "leaves": st0["leaves"], "max_depth": st0["max_depth"], "build_launches": st0["build_launches"],
                       "scene_generation_s": t_gen},
-            "frame_checksum": checksum,
+            "frame_checksum": checksum, "oneshot_vs_resident_pixels_differ": oneshot_diff,
+            "configs": configs,
         }
         print(json.dumps(out), file=_JSON_OUT, flush=True)
     barrier()
@@ -410,6 +581,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--ref-samples", type=int, default=0, help="CPU samples per step (default: one per host thread x4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-gpu", action="store_true", help="skip the C1-C4 block (ours and the reference's GPU renderer)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

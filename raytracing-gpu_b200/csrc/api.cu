@@ -198,7 +198,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
-  if (!RTB_BVH4 && want_raster && (S.inv_order || !S.has_tree) && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
+  if (want_raster && (S.inv_order || !S.has_tree) && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
       o.frame_kernel == RTB_KERNEL_PER_SAMPLE && fa.cam.W <= 65535 && fa.cam.H <= 65535) {      // items hold 16-bit sample corners
     // a frame of this camera that ran the pass and still walked the tree (boxes across the camera
     // plane, rectangles covering too much) says the next one will too: AUTO does not try again
@@ -212,7 +212,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
       S.rast_useless = false;
     }
   }
-  if (!RTB_BVH4 && o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
+  if (o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
       S.n_lights <= 255) {
     const size_t need = wave_scratch_floats(o.aliasing, S.sm_count);
     if (S.d_bounce_floats < need) {
@@ -605,7 +605,7 @@ int rtb_scene_hit_ids(rtb_scene_t *h, const rtb_frame_opts *opts, int32_t *tri_o
   }
   // opts->primary == RTB_PRIMARY_RASTER: the ids the projection pass records (tests); a frame that
   // falls back to the tree reports -2 everywhere so that a test cannot pass by accident
-  if (!RTB_BVH4 && o.primary != RTB_PRIMARY_TREE && o.tracer == RTB_TRACER_TREE && (S.inv_order || !S.has_tree) && S.n_tris >= RASTER_AUTO_MIN_TRIS &&
+  if (o.primary != RTB_PRIMARY_TREE && o.tracer == RTB_TRACER_TREE && (S.inv_order || !S.has_tree) && S.n_tris >= RASTER_AUTO_MIN_TRIS &&
       S.camera.width <= 65535 && S.camera.height <= 65535) {
     FrameArgs fa;
     memset(&fa, 0, sizeof fa);

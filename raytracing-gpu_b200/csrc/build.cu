@@ -376,9 +376,6 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
       if (holding) {
         if (r - l + 1 == n) {            // the whole scene fits in this warp
           root_info[0] = cur; root_info[1] = height;
-#if RTB_BVH4
-          if (cur >= 0) raw_parent[cur] = -1;
-#endif
           holding = false;
         } else if (l == 0 || (r != n - 1 && delta(keys, r) < delta(keys, l - 1))) { parent = (int)r; side = 0; }
         else { parent = (int)l - 1; side = 1; }
@@ -395,9 +392,6 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
         const uint32_t cnt = r - l + 1;
         const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
         const int my_h = cnt <= flat_max ? 0 : height;
-#if RTB_BVH4
-        if (cur >= 0) raw_parent[cur] = parent;
-#endif
         const float mlx = __shfl_sync(pm, lo.x, mate), mly = __shfl_sync(pm, lo.y, mate), mlz = __shfl_sync(pm, lo.z, mate);
         const float mhx = __shfl_sync(pm, hi.x, mate), mhy = __shfl_sync(pm, hi.y, mate), mhz = __shfl_sync(pm, hi.z, mate);
         const int m_ref = __shfl_sync(pm, my_ref, mate), m_h = __shfl_sync(pm, my_h, mate);
@@ -432,9 +426,6 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     const uint32_t cnt = r - l + 1;
     if (cnt == n) {
       root_info[0] = cur; root_info[1] = height;
-#if RTB_BVH4
-      if (cur >= 0) raw_parent[cur] = -1;
-#endif
       return;
     }
     const int my_ref = cnt <= (uint32_t)LEAF_MAX ? leaf_ref(l, cnt) : cur;
@@ -444,9 +435,6 @@ __global__ void __launch_bounds__(BT) k_emit(const float *raw_v, const uint32_t 
     else { parent = (int)l - 1; side = 1; }
     store_child(&raw[parent], side, lo, hi, my_ref);
     child_height[2 * parent + side] = my_h;
-#if RTB_BVH4
-    if (cur >= 0) raw_parent[cur] = parent;
-#endif
 #if RTB_EMIT_RELEASE_ATOM
     int other;
     asm volatile("atom.release.gpu.global.exch.b32 %0, [%1], %2;" : "=r"(other) : "l"(visit + parent), "r"(side == 0 ? (int)l : (int)r) : "memory");
@@ -726,30 +714,12 @@ __global__ void __launch_bounds__(T) k_sah_clusters(const float *raw_v, uint32_t
 }
 #undef BX
 
-#if !RTB_BVH4
 // live[j] = 1 when raw node j survives (its range is larger than a leaf)
 __global__ void __launch_bounds__(BT) k_live(const RawNode *raw, uint32_t n_inner, uint32_t *live) {
   const uint32_t j = blockIdx.x * BT + threadIdx.x;
   if (j < n_inner) live[j] = raw[j].cnt > LEAF_MAX ? 1u : 0u;
 }
 
-#if RTB_NODE_CH
-// (min, max) pairs -> (centre, half extent) pairs, the half extent rounded outwards so
-// that [c - h, c + h] contains [min, max].  An inverted (empty) box becomes h = -inf.
-__device__ __forceinline__ void centre_half(float lo, float hi, float &c, float &h) {
-  const float inf = __int_as_float(0x7f800000);
-  if (!(lo <= hi)) { c = 0.0f; h = -inf; return; }
-  if (lo == -inf || hi == inf) { c = 0.0f; h = inf; return; }
-  c = 0.5f * lo + 0.5f * hi;
-  h = fmaxf(hi - c, c - lo) * 1.000001f;
-}
-__device__ __forceinline__ float4 to_centre_half(float4 q) {
-  float4 r;
-  centre_half(q.x, q.y, r.x, r.y);
-  centre_half(q.z, q.w, r.z, r.w);
-  return r;
-}
-#endif
 
 // new_index = exclusive scan of live.  stats: [0] leaves, [1] max leaf size
 // node_up / slot_up: the upward links of rtb_internal.h (the root's own entry is set by the host)
@@ -774,88 +744,13 @@ __global__ void __launch_bounds__(BT) k_compact(const RawNode *raw, uint32_t n_i
     }
   }
   float4 *dst = nodes + 4ull * me;
-#if RTB_NODE_CH
-  dst[0] = to_centre_half(nd.q0);
-  dst[1] = to_centre_half(nd.q1);
-  dst[2] = to_centre_half(nd.q2);
-#else
   dst[0] = nd.q0;
   dst[1] = nd.q1;
   dst[2] = nd.q2;
-#endif
   dst[3] = make_float4(__int_as_float(nd.ref0), __int_as_float(nd.ref1), __int_as_float(nd.lo), __int_as_float(nd.cnt));
   if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
 }
-#endif
 
-#if RTB_BVH4
-// live[j] = 1 when raw node j survives as a 4-wide node: larger than a leaf and at even depth
-__global__ void __launch_bounds__(BT) k_live4(const RawNode *raw, const int *raw_parent, uint32_t n_inner,
-                                              uint32_t *live, unsigned char *keep) {
-  const uint32_t j = blockIdx.x * BT + threadIdx.x;
-  if (j >= n_inner) return;
-  unsigned char k = 0;
-  if (raw[j].cnt > LEAF_MAX) {
-    int depth = 0;
-    for (int p = raw_parent[j]; p >= 0; p = raw_parent[p]) ++depth;
-    k = (depth & 1) ? 0 : 1;
-  }
-  keep[j] = k;
-  live[j] = k;
-}
-
-__device__ __forceinline__ void put_child4(float4 *dst, int slot, V3 lo, V3 hi, int ref) {
-  float *f = reinterpret_cast<float *>(dst);
-  float *xy = f + 4 * slot;
-  xy[0] = lo.x; xy[1] = hi.x; xy[2] = lo.y; xy[3] = hi.y;
-  f[16 + 2 * slot] = lo.z;
-  f[17 + 2 * slot] = hi.z;
-  f[24 + slot] = __int_as_float(ref);
-}
-
-__device__ __forceinline__ void raw_child(const RawNode &nd, int side, V3 &lo, V3 &hi, int &ref) {
-  const float *f = reinterpret_cast<const float *>(&nd);
-  const float *xy = f + 4 * side;
-  lo = mk(xy[0], xy[2], f[8 + 2 * side]);
-  hi = mk(xy[1], xy[3], f[9 + 2 * side]);
-  ref = (&nd.ref0)[side];
-}
-
-// new_index = exclusive scan of live.  One thread per kept raw node: its grandchildren (or a
-// child that is a leaf) become the four children.  stats: [0] leaves, [1] max leaf size
-__global__ void __launch_bounds__(BT) k_compact4(const RawNode *raw, uint32_t n_inner, const uint32_t *new_index,
-                                                 const unsigned char *keep, float4 *nodes, unsigned int *stats) {
-  const uint32_t j = blockIdx.x * BT + threadIdx.x;
-  if (j >= n_inner || !keep[j]) return;
-  const RawNode nd = raw[j];
-  const float INF = __int_as_float(0x7f800000);
-  float4 *dst = nodes + (size_t)NODE_QUADS * new_index[j];
-  unsigned leaves = 0, maxleaf = 0;
-  for (int side = 0; side < 2; ++side) {
-    V3 lo, hi;
-    int ref;
-    raw_child(nd, side, lo, hi, ref);
-    int slot = 2 * side;
-    if (ref < 0) {
-      put_child4(dst, slot++, lo, hi, ref);
-      ++leaves; maxleaf = max(maxleaf, (unsigned)(~ref & 7));
-    } else {
-      const RawNode c = raw[ref];
-      for (int s2 = 0; s2 < 2; ++s2) {
-        int r2;
-        raw_child(c, s2, lo, hi, r2);
-        if (r2 >= 0) r2 = (int)new_index[r2];
-        else { ++leaves; maxleaf = max(maxleaf, (unsigned)(~r2 & 7)); }
-        put_child4(dst, slot++, lo, hi, r2);
-      }
-    }
-    for (; slot < 2 * side + 2; ++slot)
-      put_child4(dst, slot, mk(INF, INF, INF), mk(-INF, -INF, -INF), leaf_ref(0, 0));
-  }
-  dst[7] = make_float4(__int_as_float(nd.lo), __int_as_float(nd.cnt), 0.0f, 0.0f);
-  if (leaves) { atomicAdd(&stats[0], leaves); atomicMax(&stats[1], maxleaf); }
-}
-#endif
 
 // Scenes of at most LEAF_MAX triangles (and brute-force-only scenes): one node whose first
 // child is a leaf over everything with an unbounded box (nothing to cull, so nothing to pad),
@@ -864,21 +759,9 @@ __global__ void k_single_node(uint32_t n, float4 *nodes) {
   const float INF = __int_as_float(0x7f800000);
   float lx = INF, ly = INF, lz = INF, hx = -INF, hy = -INF, hz = -INF;
   if (n) { lx = ly = lz = -INF; hx = hy = hz = INF; }
-#if RTB_BVH4
-  put_child4(nodes, 0, mk(lx, ly, lz), mk(hx, hy, hz), leaf_ref(0, n));
-  for (int k = 1; k < 4; ++k) put_child4(nodes, k, mk(INF, INF, INF), mk(-INF, -INF, -INF), leaf_ref(0, 0));
-  nodes[7] = make_float4(__int_as_float(0), __int_as_float((int)n), 0.0f, 0.0f);
-  return;
-#endif
-#if RTB_NODE_CH
-  nodes[0] = to_centre_half(make_float4(lx, hx, ly, hy));
-  nodes[1] = to_centre_half(make_float4(INF, -INF, INF, -INF));
-  nodes[2] = to_centre_half(make_float4(lz, hz, INF, -INF));
-#else
   nodes[0] = make_float4(lx, hx, ly, hy);
   nodes[1] = make_float4(INF, -INF, INF, -INF);
   nodes[2] = make_float4(lz, hz, INF, -INF);
-#endif
   nodes[3] = make_float4(__int_as_float(leaf_ref(0, n)), __int_as_float(leaf_ref(0, 0)), __int_as_float(0),
                          __int_as_float((int)n));
 }
@@ -1090,12 +973,8 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   int *d_mode = nullptr;                      // [0] chosen key mode, [1..4] sample-tree costs
   S->key_mode = 0;
   for (int k = 0; k < 4; ++k) S->mode_cost[k] = 0;
-#if RTB_BVH4
-  const uint32_t cl_max = 0;                    // the 4-wide A/B layout keeps the plain radix tree
-#else
   const uint32_t cl_max =
       (flags & RTB_BUILD_RADIX_ONLY) || ((flags & RTB_BUILD_ONE_FRAME) && n > ONE_FRAME_SAH_MAX) ? 0u : SAH_CLUSTER_MAX;
-#endif
   const bool sah_only = tree && cl_max && n <= SAH_WHOLE_MAX;    // the whole scene is one cluster: no sort, no radix tree
   Cluster *d_clusters = nullptr;
   uint32_t *d_n_clusters = nullptr;
@@ -1218,13 +1097,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   }
   if (tree) {
     const uint32_t n_inner = n - 1;
-#if RTB_BVH4
-    unsigned char *keep = nullptr;
-    CK(tmp.alloc(&keep, n_inner));
-    k_live4<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, raw_parent, n_inner, live, keep);
-#else
     k_live<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live);
-#endif
     ++launches;
     CK(dev_exclusive_scan_u32(live, n_inner + 1, scan_scratch, ssw, false, st, &launches));
     uint32_t n_live = 0;
@@ -1240,15 +1113,8 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
     if (n_live == 0 || h_root[0] < 0) { set_error("hierarchy build produced no root"); return RTB_ERR_CUDA; }
     if (height > HEIGHT_MAX) { set_error("hierarchy depth %d exceeds %d", height, HEIGHT_MAX); return RTB_ERR_LIMIT; }
     CK(dev_alloc(&S->nodes, (size_t)NODE_QUADS * n_live));
-#if RTB_BVH4
-    k_compact4<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, keep, S->nodes, d_stats);
-#else
-#if RTB_SHADOW_UP
-    CK(dev_alloc(&S->up, (size_t)n_live + n));
-#endif
     k_compact<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live, S->nodes, d_stats, S->up,
                                                       S->up ? S->up + n_live : nullptr);
-#endif
     ++launches;
     uint32_t new_root = 0;
     unsigned int h_stats[2] = {0, 0};

@@ -28,42 +28,16 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 //   q3 = (as_float(ref0), as_float(ref1), as_float(first slot of range), as_float(slot count))
 // ref >= 0: index of an inner node; ref < 0: leaf, ~ref = (first_slot << 3) | count, count <= LEAF_MAX (3).
 // An empty child is a leaf with count 0 and an inverted box (+inf, -inf).
-// A/B option RTB_NODE_CH=1 stores every (min, max) pair above as (centre, half extent), half
-// extent rounded outwards (build.cu centre_half): 12 FFMA + 4 FMNMX per box instead of
-// 6 FFMA + 10 FMNMX.  Measured slower on C5 (43.05 vs 42.04 ms), so min/max is the default.
-#ifndef RTB_NODE_CH
-#define RTB_NODE_CH 0
-#endif
-// A/B option RTB_BVH4=1: the binary tree is collapsed two levels at a time into 4-wide nodes
-// of 128 bytes = 8 float4 (build.cu k_compact4).  Half the visits (22.0 instead of 43.0 per
-// ray on C5) but 140 instead of 2 x 75 instructions per visit and, at 64 registers, the seven
-// loads of a visit issue in three dependent waves: 45.7 ms against 41.6 ms.  Not the product.
-//   q0..q3 = (min.x, max.x, min.y, max.y) of child 0..3
-//   q4 = (c0.min.z, c0.max.z, c1.min.z, c1.max.z)     q5 = the same for children 2, 3
-//   q6 = (as_float(ref0..ref3))                        q7 = (as_float(first slot), as_float(slot count), 0, 0)
-// Children 0,1 are the two children of the binary node's first child (or that child itself in
-// slot 0 when it is a leaf), children 2,3 those of the second; unused slots are empty children.
-#ifndef RTB_BVH4
-#define RTB_BVH4 0
-#endif
+// Variants that were measured and dropped (4-wide nodes, centre/half-extent boxes, per-octant
+// traversal, shadow rays that climb from their leaf) are in tools/ab_variants/ with their numbers in DESIGN.md section 8.
 #ifndef RTB_LEAF_MAX
 #define RTB_LEAF_MAX 3   /* C5, speculative traversal: 2: 43.4  3: 43.3  4: 43.9  6: 45.0 ms */
 #endif
 constexpr int LEAF_MAX = RTB_LEAF_MAX;
 constexpr int HEIGHT_MAX = 96;       // binary inner-node depth limit (63 Morton bits + 32 index tie-break bits)
-#if RTB_BVH4
-constexpr int NODE_QUADS = 8;                      // float4 per node
-constexpr int STACK_MAX = 3 * (HEIGHT_MAX / 2);    // up to 3 siblings postponed per 4-wide level
-#else
 constexpr int NODE_QUADS = 4;
 constexpr int STACK_MAX = HEIGHT_MAX;
-#endif
 constexpr int MORTON_BITS = 63;      // 21 bits per axis
-// A/B option: shadow rays climb from the leaf they start on (trace.cu trace_up_any); needs the
-// upward links of DevScene.  Slower than the walk from the root on every scene measured.
-#ifndef RTB_SHADOW_UP
-#define RTB_SHADOW_UP 0
-#endif
 
 // A light's shadow-ray grid (lightgrid.cuh)
 constexpr int LG_LARGE_MAX = 16;

@@ -103,45 +103,12 @@ __device__ bool trace_brute(const DevScene &sc, const V3 o, const V3 d, Best &be
 // Conservative slab test.  The box is inflated by eps on every side; eps is a multiple of
 // the float spacing at the largest coordinate the triangle test can involve, so a ray
 // that the (rounded) Moeller-Trumbore arithmetic accepts is never culled.
-#ifndef RTB_NODE_CH
-#define RTB_NODE_CH 0
-#endif
 
 __device__ __forceinline__ float safe_rcp(float x) {
   const float tiny = 1e-30f;
   return 1.0f / (fabsf(x) > tiny ? x : copysignf(tiny, x));
 }
 
-#if RTB_NODE_CH
-// Nodes store (centre, half extent) per axis: near/far plane parameters are then two
-// dependent FMAs each and the per-axis min/max pairs disappear: 12 FFMA + 4 FMNMX per box
-// instead of 6 FFMA + 10 FMNMX.  A/B option only: slower on C5 (43.05 vs 42.04 ms).
-//   near_a = (c_a - o_a) * i_a - (h_a + eps) * |i_a|,  far_a = (c_a - o_a) * i_a + (h_a + eps) * |i_a|
-struct Slabs { float ix, iy, iz, ax, ay, az, nx, ny, nz, fx, fy, fz; };
-
-__device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
-  Slabs s;
-  s.ix = safe_rcp(d.x); s.iy = safe_rcp(d.y); s.iz = safe_rcp(d.z);
-  s.ax = fabsf(s.ix); s.ay = fabsf(s.iy); s.az = fabsf(s.iz);
-  const float ox = o.x * s.ix, oy = o.y * s.iy, oz = o.z * s.iz;
-  const float ex = eps * s.ax, ey = eps * s.ay, ez = eps * s.az;
-  s.nx = -(ox + ex); s.ny = -(oy + ey); s.nz = -(oz + ez);
-  s.fx = ex - ox; s.fy = ey - oy; s.fz = ez - oz;
-  return s;
-}
-
-// USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound)
-template <bool USE_TMAX = true, int OCT = -1>
-__device__ __forceinline__ bool slab_hit(const Slabs &s, float cx, float hx, float cy, float hy, float cz,
-                                         float hz, float tmax, float &tn) {
-  const float x0 = __fmaf_rn(-hx, s.ax, __fmaf_rn(cx, s.ix, s.nx)), x1 = __fmaf_rn(hx, s.ax, __fmaf_rn(cx, s.ix, s.fx));
-  const float y0 = __fmaf_rn(-hy, s.ay, __fmaf_rn(cy, s.iy, s.ny)), y1 = __fmaf_rn(hy, s.ay, __fmaf_rn(cy, s.iy, s.fy));
-  const float z0 = __fmaf_rn(-hz, s.az, __fmaf_rn(cz, s.iz, s.nz)), z1 = __fmaf_rn(hz, s.az, __fmaf_rn(cz, s.iz, s.fz));
-  tn = fmaxf(fmaxf(x0, y0), fmaxf(z0, 0.0f));
-  const float tf = USE_TMAX ? fminf(fminf(x1, y1), fminf(z1, tmax)) : fminf(fminf(x1, y1), z1);
-  return tn <= tf;
-}
-#else
 struct Slabs { float ix, iy, iz, ax, ay, az, bx, by, bz; };
 
 __device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
@@ -153,30 +120,19 @@ __device__ __forceinline__ Slabs make_slabs(const V3 o, const V3 d, float eps) {
 }
 
 // USE_TMAX = false for shadow rays: nothing ever shortens them (gpu/light.cu:29-36 has no far bound).
-// OCT >= 0: the signs of the direction are known at compile time (bit a set: axis a negative),
-// so the entry plane of every slab is known and the six per-axis min / max disappear:
-// 6 FFMA + 2 FMNMX3 + 1-2 FMNMX per box instead of 6 FFMA + 6 FMNMX + 2 FMNMX3 + 1-2 FMNMX.
-template <bool USE_TMAX = true, int OCT = -1>
+template <bool USE_TMAX = true>
 __device__ __forceinline__ bool slab_hit(const Slabs &s, float lox, float hix, float loy, float hiy, float loz,
                                          float hiz, float tmax, float &tn) {
   const float x0 = __fmaf_rn(lox, s.ix, -s.ax), x1 = __fmaf_rn(hix, s.ix, -s.bx);
   const float y0 = __fmaf_rn(loy, s.iy, -s.ay), y1 = __fmaf_rn(hiy, s.iy, -s.by);
   const float z0 = __fmaf_rn(loz, s.iz, -s.az), z1 = __fmaf_rn(hiz, s.iz, -s.bz);
-  float nx, fx, ny, fy, nz, fz;
-  if (OCT < 0) {
-    nx = fminf(x0, x1); fx = fmaxf(x0, x1);
-    ny = fminf(y0, y1); fy = fmaxf(y0, y1);
-    nz = fminf(z0, z1); fz = fmaxf(z0, z1);
-  } else {
-    nx = (OCT & 1) ? x1 : x0; fx = (OCT & 1) ? x0 : x1;
-    ny = (OCT & 2) ? y1 : y0; fy = (OCT & 2) ? y0 : y1;
-    nz = (OCT & 4) ? z1 : z0; fz = (OCT & 4) ? z0 : z1;
-  }
+  const float nx = fminf(x0, x1), fx = fmaxf(x0, x1);
+  const float ny = fminf(y0, y1), fy = fmaxf(y0, y1);
+  const float nz = fminf(z0, z1), fz = fmaxf(z0, z1);
   tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f));
   const float tf = USE_TMAX ? fminf(fminf(fx, fy), fminf(fz, tmax)) : fminf(fminf(fx, fy), fz);
   return tn <= tf;
 }
-#endif
 
 // The lanes of a warp leave a traversal at different times and must meet again before the next one
 // starts (the shadow rays of a sample, the next light, the next bounce).  The hardware re-converges
@@ -193,85 +149,6 @@ __device__ __forceinline__ bool rejoin(bool v) { return rejoin((int)v) != 0; }
 
 constexpr int TRAVERSAL_DONE = (int)0x80000000;   // stack sentinel: not a valid leaf reference
 
-#if RTB_BVH4
-// 4-wide nodes (rtb_internal.h): one visit tests the four grandchildren of the binary node, so
-// a ray makes about half as many visits, dependent loads and loop/stack/vote steps as on the
-// binary tree for the same box tests.  Same speculative while-while shape as below.
-template <bool ANY, bool COUNT>
-__device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c) {
-  best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
-  const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
-  const float eps = sc.margin_k * 1.1920929e-7f * amax;
-  const Slabs sl = make_slabs(o, d, eps);
-  const float inv_len = 1.0001f / sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);   // distance -> ray parameter, rounded up
-  float tmax = INF;
-  int stack[STACK_MAX + 1];
-  stack[0] = TRAVERSAL_DONE;
-  int sp = 1;
-  int cur = sc.root;
-  int pending = 0;        // leaf references are negative, 0 = none held
-  for (;;) {
-    while (cur >= 0) {
-      if (COUNT) ++c.nodes;
-      const float4 *np = sc.nodes + 8ll * cur;
-      const float4 b0 = __ldg(np), b1 = __ldg(np + 1), b2 = __ldg(np + 2), b3 = __ldg(np + 3);
-      const float4 z01 = __ldg(np + 4), z23 = __ldg(np + 5), rf = __ldg(np + 6);
-      float t0, t1, t2, t3;
-      const bool h0 = slab_hit<!ANY>(sl, b0.x, b0.y, b0.z, b0.w, z01.x, z01.y, tmax, t0);
-      const bool h1 = slab_hit<!ANY>(sl, b1.x, b1.y, b1.z, b1.w, z01.z, z01.w, tmax, t1);
-      const bool h2 = slab_hit<!ANY>(sl, b2.x, b2.y, b2.z, b2.w, z23.x, z23.y, tmax, t2);
-      const bool h3 = slab_hit<!ANY>(sl, b3.x, b3.y, b3.z, b3.w, z23.z, z23.w, tmax, t3);
-      const int r0 = __float_as_int(rf.x), r1 = __float_as_int(rf.y), r2 = __float_as_int(rf.z),
-                r3 = __float_as_int(rf.w);
-      // cur = one hit child, the others go on the stack
-      constexpr int NONE = 0x7fffffff;     // neither a node index (< 2^28) nor a leaf (negative)
-      int next = NONE;
-      if (ANY) {
-        // shadow rays only ask "anything?": storage order
-        if (h3) next = r3;
-        if (h2) { if (next != NONE) stack[sp++] = next; next = r2; }
-        if (h1) { if (next != NONE) stack[sp++] = next; next = r1; }
-        if (h0) { if (next != NONE) stack[sp++] = next; next = r0; }
-      } else {
-        // nearest entry point first; the rest in storage order.  Entry distances are >= 0, so
-        // their bit patterns order like unsigned integers; the low 2 bits carry the child index.
-        const unsigned k0 = h0 ? (__float_as_uint(t0) & ~3u) : 0xffffffffu;
-        const unsigned k1 = h1 ? (__float_as_uint(t1) & ~3u) | 1u : 0xffffffffu;
-        const unsigned k2 = h2 ? (__float_as_uint(t2) & ~3u) | 2u : 0xffffffffu;
-        const unsigned k3 = h3 ? (__float_as_uint(t3) & ~3u) | 3u : 0xffffffffu;
-        const unsigned m = min(min(k0, k1), min(k2, k3));
-        if (h3 && k3 != m) stack[sp++] = r3;
-        if (h2 && k2 != m) stack[sp++] = r2;
-        if (h1 && k1 != m) stack[sp++] = r1;
-        if (h0 && k0 != m) stack[sp++] = r0;
-        if (m != 0xffffffffu) next = (m & 2u) ? ((m & 1u) ? r3 : r2) : ((m & 1u) ? r1 : r0);
-      }
-      if (next < 0 && pending == 0) {      // first leaf: keep it, go on
-        pending = next;
-        next = NONE;
-      }
-      cur = next != NONE ? next : stack[--sp];
-      if (!__any_sync(__activemask(), pending == 0)) break;     // every lane here holds a leaf
-    }
-    while (pending != 0 || (cur < 0 && cur != TRAVERSAL_DONE)) {
-      int leaf;
-      if (pending != 0) { leaf = pending; pending = 0; }
-      else { leaf = cur; cur = stack[--sp]; }
-      const uint32_t packed = (uint32_t)~leaf;
-      const int first = (int)(packed >> 3), cnt = (int)(packed & 7u);
-      for (int k = 0; k < cnt; ++k) {
-        if (COUNT) ++c.tris;
-        if (consider<ANY>(sc, o, d, first + k, best)) {
-          if (ANY) return true;
-          tmax = (best.dist * 1.0001f + eps) * inv_len;
-        }
-      }
-    }
-    if (cur == TRAVERSAL_DONE) break;
-  }
-  return best.slot >= 0;
-}
-#else
 // Speculative "while-while" traversal (Aila-Laine): every lane descends inner nodes; the first
 // leaf it reaches is set aside and the descent goes on until every lane of the warp holds one,
 // then the warp tests triangles together.  Keeping the two phases apart keeps the lanes of a
@@ -279,7 +156,7 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, Best &bes
 // code ran at 7.5 of 32 lanes (profiles/r1_ncu_frame_v1.txt).  History on C5: if-else 53.9 ms,
 // plain while-while 47.4, speculative 44.5, one pop per step 40.5.
 // start: the node (or leaf reference) the walk begins at; sc.root for a whole-tree query.
-template <bool ANY, bool COUNT, int OCT = -1>
+template <bool ANY, bool COUNT>
 __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, const Slabs &sl, float eps, int start,
                            Best &best, Counters &c) {
   best.dist = INF; best.id = 0x7fffffff; best.slot = -1;
@@ -298,8 +175,8 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, const Sla
       const float4 *np = sc.nodes + 4ll * cur;
       const float4 q0 = __ldg(np), q1 = __ldg(np + 1), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
       float tn0, tn1;
-      const bool h0 = slab_hit<!ANY, OCT>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
-      const bool h1 = slab_hit<!ANY, OCT>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
+      const bool h0 = slab_hit<!ANY>(sl, q0.x, q0.y, q0.z, q0.w, q2.x, q2.y, tmax, tn0);
+      const bool h1 = slab_hit<!ANY>(sl, q1.x, q1.y, q1.z, q1.w, q2.z, q2.w, tmax, tn1);
       const int r0 = __float_as_int(q3.x), r1 = __float_as_int(q3.y);
       int next = h0 ? r0 : (h1 ? r1 : NONE);
       if (h0 && h1) {
@@ -333,92 +210,16 @@ __device__ bool trace_tree(const DevScene &sc, const V3 o, const V3 d, const Sla
   }
   return best.slot >= 0;
 }
-#endif   // RTB_BVH4
 
-// RTB_OCTANT=1: one copy of the traversal per direction octant (slab_hit<.., OCT>).  The rays of
-// a warp nearly always share their octant, so the switch does not diverge.
-#ifndef RTB_OCTANT
-#define RTB_OCTANT 0
-#endif
-// Shadow rays start ON a triangle.  Instead of descending from the root (one two-box visit per
-// level just to get back to where the ray starts), they climb from that triangle's leaf: the
-// leaf first, then at every ancestor the ONE sibling box; a sibling that is hit is searched with
-// the usual loop.  Every triangle is in the start leaf or under exactly one of those siblings, so
-// the set of tested candidates is a superset of what any conservative top-down walk tests and
-// the answer ("any candidate?", gpu/light.cu:29-36) is the same.  Nearby geometry comes first,
-// which is also where occluders are.  A/B option, NOT the default: measured on C5 the frame
-// takes 33.7 ms against 33.3 (susans_smooth 6.4 against 5.1): a climb step costs as much as the
-// two-box visit it replaces (parent link, child select, the walk's set-up at every sibling hit),
-// and the counted visits only drop from 36.4 to 35.9 per ray.
-template <bool COUNT>
-__device__ bool trace_up_any(const DevScene &sc, const V3 o, const V3 d, const Slabs &sl, float eps, int slot,
-                             Counters &c) {
-  // no start slot (or no links): the "climb" is one whole-tree walk from the root, same code
-  uint32_t up = 0xffffffffu;
-  int ref = sc.root;
-  if (slot >= 0 && sc.slot_up) {
-    up = __ldg(sc.slot_up + slot);
-    const float4 q3 = __ldg(sc.nodes + 4ll * (up >> 1) + 3);
-    ref = __float_as_int((up & 1u) ? q3.y : q3.x);          // the start leaf
-  }
-  bool go = true;
-  for (;;) {
-    if (go) {
-      Best b;
-      if (trace_tree<true, COUNT>(sc, o, d, sl, eps, ref, b, c)) return true;
-    }
-    if (up == 0xffffffffu) return false;                     // the root's siblings are done
-    const uint32_t node = up >> 1, side = up & 1u;
-    const float4 *np = sc.nodes + 4ll * node;
-    if (COUNT) ++c.nodes;
-    const uint32_t next_up = __ldg(sc.node_up + node);
-    const float4 qs = __ldg(np + (side ^ 1u)), q2 = __ldg(np + 2), q3 = __ldg(np + 3);
-    // the sibling is child side ^ 1: z pair (q2.x, q2.y) for child 0, (q2.z, q2.w) for child 1
-    const float lz = side ? q2.x : q2.z, hz = side ? q2.y : q2.w;
-    ref = __float_as_int(side ? q3.x : q3.y);
-    float tn;
-    go = slab_hit<false>(sl, qs.x, qs.y, qs.z, qs.w, lz, hz, INF, tn);
-    up = next_up;
-  }
-}
-
-// RTB_OCTANT=1: one copy of the traversal per direction octant (slab_hit<.., OCT>).  The rays of
-// a warp nearly always share their octant, so the switch does not diverge.  A/B only: slower.
-#ifndef RTB_OCTANT
-#define RTB_OCTANT 0
-#endif
 // start_slot >= 0 (ANY only): the ray starts on the triangle in that slot
 template <int TRACER, bool ANY, bool COUNT>
 __device__ __forceinline__ bool trace(const DevScene &sc, const V3 o, const V3 d, Best &best, Counters &c,
                                       int start_slot = -1) {
   if (TRACER == RTB_TRACER_BRUTE) return trace_brute<ANY, COUNT>(sc, o, d, best, c);
-#if RTB_BVH4
-  return trace_tree<ANY, COUNT>(sc, o, d, best, c);
-#else
   const float amax = fmaxf(fmaxf(fabsf(o.x), fabsf(o.y)), fabsf(o.z)) + sc.abs_max;
   const float eps = sc.margin_k * 1.1920929e-7f * amax;
   const Slabs sl = make_slabs(o, d, eps);
-#if RTB_SHADOW_UP
-  if (ANY) return trace_up_any<COUNT>(sc, o, d, sl, eps, start_slot, c);
-#endif
-#if RTB_OCTANT && !RTB_NODE_CH
-  // the sign of 1/d as safe_rcp computes it (-0 counts as negative)
-  const int oct = (int)(__float_as_uint(sl.ix) >> 31) | (int)((__float_as_uint(sl.iy) >> 31) << 1) |
-                  (int)((__float_as_uint(sl.iz) >> 31) << 2);
-  switch (oct) {
-    case 0: return trace_tree<ANY, COUNT, 0>(sc, o, d, sl, eps, sc.root, best, c);
-    case 1: return trace_tree<ANY, COUNT, 1>(sc, o, d, sl, eps, sc.root, best, c);
-    case 2: return trace_tree<ANY, COUNT, 2>(sc, o, d, sl, eps, sc.root, best, c);
-    case 3: return trace_tree<ANY, COUNT, 3>(sc, o, d, sl, eps, sc.root, best, c);
-    case 4: return trace_tree<ANY, COUNT, 4>(sc, o, d, sl, eps, sc.root, best, c);
-    case 5: return trace_tree<ANY, COUNT, 5>(sc, o, d, sl, eps, sc.root, best, c);
-    case 6: return trace_tree<ANY, COUNT, 6>(sc, o, d, sl, eps, sc.root, best, c);
-    default: return trace_tree<ANY, COUNT, 7>(sc, o, d, sl, eps, sc.root, best, c);
-  }
-#else
   return trace_tree<ANY, COUNT>(sc, o, d, sl, eps, sc.root, best, c);
-#endif
-#endif
 }
 
 }  // namespace
@@ -672,9 +473,7 @@ __global__ void __launch_bounds__(128) k_trace_rays(const DevScene sc, const flo
   if (dist) dist[i] = (hit && !ANY) ? b.dist : 0.0f;
 }
 
-#if !RTB_BVH4
 #include "wave.cuh"   // staged wavefront kernel: binary node layout only (A/B builds)
-#endif
 
 float g_margin_k = 24.0f;
 
@@ -689,7 +488,7 @@ constexpr int LG_MAX_GRIDS = 8;
 
 int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights, const float bmin[3],
                       const float bmax[3], cudaStream_t st) {
-  if (RTB_BVH4 || !S.has_tree || S.n_tris < LG_MIN_TRIS || !n_lights) return RTB_OK;
+  if (!S.has_tree || S.n_tris < LG_MIN_TRIS || !n_lights) return RTB_OK;
   std::vector<LightGrid> grids(n_lights);
   memset(grids.data(), 0, grids.size() * sizeof(LightGrid));
   const DevScene sc = S.dev();
@@ -828,9 +627,6 @@ static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count,
   return RTB_OK;
 }
 
-#if RTB_BVH4
-size_t wave_scratch_floats(int, int) { return 0; }
-#else
 constexpr int WAVE_MAX_BLOCKS_PER_SM = 16;
 
 size_t wave_scratch_floats(int aliasing, int sm_count) {
@@ -851,7 +647,6 @@ static int launch_wave_t(const DevScene &sc, const FrameArgs &fa, int sm_count, 
   return RTB_OK;
 }
 
-#endif
 
 static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st);
 
@@ -884,10 +679,8 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
 static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st) {
   // RTB_KERNEL_WAVEFRONT was requested and is applicable (api.cu sets bounce_scratch only then);
   // everything else runs the persistent-warp per-sample kernel, the faster of the two
-#if !RTB_BVH4
   if (tracer == RTB_TRACER_TREE && fa.bounce_scratch && fa.n_shadow_lights <= 32 && fa.aliasing <= WAVE_MAX_ALIASING)
     return count ? launch_wave_t<true>(sc, fa, sm_count, st) : launch_wave_t<false>(sc, fa, sm_count, st);
-#endif
   if (tracer == RTB_TRACER_BRUTE)
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);

@@ -3,8 +3,10 @@
 Run in the build container (needs /root/reference):  python tests/golden/make_golden.py [scene ...]
 
 Each fixture holds
-  * the parsed scene in memory order (vertex, normal, tri_counts, materials, lights, camera),
-    so the GPU box needs neither /root/reference nor the .svati text;
+  * the scene in memory order (vertex, normal, tri_counts, materials, lights, camera) as the
+    reference's own parser reads it (gpu/parser.cpp, parse_obj.cpp via oracle/_ref/libref_parser.so;
+    tests/test_parser_pin.py re-checks the committed arrays against it), so the GPU box needs neither
+    /root/reference nor the .svati text;
   * rgba: the full-resolution frame (aliasing 3) of the REFERENCE's own device sources
     compiled for the host (oracle/_ref/libref_gpusem.so via oracle/ref_driver.cpp);
   * tri/obj: per-sample primary-ray hit ids from oracle/liboracle.so, accepted only after
@@ -35,7 +37,11 @@ def main(argv):
         if os.path.exists(out) and not os.environ.get("GOLDEN_FORCE"):
             print(name, "exists, skipped")
             continue
-        hs = pyrtb.HostScene.parse(os.path.join(SCENES, name + ".svati"))
+        # scene arrays as the REFERENCE's own loader reads them (oracle/_ref/libref_parser.so), not ours
+        from test_parser_pin import ref_parse
+        ra = ref_parse(os.path.join(SCENES, name + ".svati"))
+        ra["lights"][ra["lights"][:, 0] == pyrtb.AMBIENT, 4:7] = 0      # never set by parse_a_light, never read
+        hs = pyrtb.HostScene.from_arrays(ra["vertex"], ra["normal"], ra["tri_counts"], ra["materials"], ra["lights"], ra["camera"])
         t0 = time.time()
         o = oracle_py.orc_render(hs, 3, want_ids=True)
         t1 = time.time()

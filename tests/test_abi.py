@@ -76,8 +76,7 @@ def test_product_sources_never_touch_the_oracle():
         for f in files:
             if f.endswith((".cu", ".cuh", ".cpp", ".h", ".py", "Makefile")):
                 text = open(os.path.join(base, f), errors="replace").read()
-                assert "oracle" not in text.lower() or f == "pyrtb.py" and "oracle" not in text.lower(), \
-                    "%s mentions the oracle" % os.path.join(base, f)
+                assert "oracle" not in text.lower(), "%s mentions the oracle" % os.path.join(base, f)
 
 
 def test_ctypes_mirrors_match_the_header_layout(tmp_path):

@@ -118,3 +118,42 @@ def test_padded_row_stride(gpu):
         assert np.array_equal(padded[:, :96], tight) and (padded[:, 96:] == 7).all()
     finally:
         ds.close()
+
+
+def test_unit_box_known_answer_of_the_reference(gpu):
+    """gpu/test.cu:362-375: the ray (0,0,0) -> (0,0,1) along an edge of the unit box [0,1]^3 "hits" the box
+    (hit_aabb, gpu/partitioning/aabb.cu:203-243): origin ON the boundary, two direction components exactly 0
+    (1/d = inf, 0 * inf = NaN in a naive slab test).  Replayed on the product's slab test through the tree:
+    the unit cube's 12 faces as the scene, axis-parallel rays on its faces and edges -- a box test that
+    culled any of them would lose a hit the exhaustive tracer finds (ids and distance bits must agree)."""
+    c = np.array([[0, 0, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0], [0, 0, 1], [1, 0, 1], [1, 1, 1], [0, 1, 1]], np.float32)
+    quads = [(0, 1, 2, 3), (4, 5, 6, 7), (0, 1, 5, 4), (3, 2, 6, 7), (0, 3, 7, 4), (1, 2, 6, 5)]
+    tris = []
+    for a, b, cc, d in quads:
+        tris += [[c[a], c[b], c[cc]], [c[a], c[cc], c[d]]]
+    v = np.array(tris, np.float32)
+    n = np.ones_like(v)
+    mats = [[0.2, 0.2, 0.2, 0.7, 0.7, 0.7, 0.3, 0.3, 0.3, 20, 1, 0, 1]]
+    lights = [[pyrtb.AMBIENT, .3, .3, .3, 0, 0, 0]]
+    cam = [64, 48, 0.5, 0.5, -4, 1, 0, 0, 0, -1, 0, 60]
+    hs = pyrtb.HostScene.from_arrays(v, n, [len(tris)], mats, lights, cam)
+    ds = pyrtb.DeviceScene(hs, 1)
+    try:
+        assert ds.stats()["nodes"] > 1, "the scene must have a hierarchy to cull with"
+        rays = [[0, 0, 0, 0, 0, 1]]                                     # the reference's own vector
+        for o in ([0, 0, -1], [1, 1, -1], [0, 1, -2], [0.5, 0, -1], [0, 0.5, -1], [1, 0.25, -3], [0.5, 0.5, -1]):
+            rays.append([*o, 0, 0, 1])                                  # along z, on edges / faces / through the middle
+        for o in ([-1, 0, 0], [-1, 1, 1], [-2, 0.5, 0], [-1, 0.5, 0.5]):
+            rays.append([*o, 1, 0, 0])                                  # along x
+        for o in ([0, 2, 0], [1, 3, 1], [0.5, 2, 0.5]):
+            rays.append([*o, 0, -1, 0])                                 # along -y
+        rays = np.array(rays, np.float32)
+        tb, db = ds.trace_rays(rays, pyrtb.TRACER_BRUTE)
+        tt, dt = ds.trace_rays(rays, pyrtb.TRACER_TREE)
+        assert np.array_equal(tt, tb) and np.array_equal(dt.view(np.uint32), db.view(np.uint32))
+        assert (tb >= 0).sum() >= 5, tb
+        at, _ = ds.trace_rays(rays, pyrtb.TRACER_TREE, any_hit=True)
+        ab, _ = ds.trace_rays(rays, pyrtb.TRACER_BRUTE, any_hit=True)
+        assert np.array_equal(at >= 0, ab >= 0)
+    finally:
+        ds.close()
