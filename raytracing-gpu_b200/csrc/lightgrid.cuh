@@ -2,25 +2,39 @@
 //
 // All shadow rays of a directional light are parallel, all shadow rays of a point light lie on
 // lines through the light's position (gpu/light.cu:68-120: direction -v, resp. v - P), and a
-// shadow ray only asks "any candidate on the ray" (gpu/light.cu:29-36).  Seen along the light,
-// a ray is a POINT and a triangle's culling box is a rectangle, so the candidates of a ray are the
-// triangles whose rectangle covers that point: a uniform grid in the light's projection, built
-// once per scene (lights are part of the scene), each cell listing the triangles whose box
-// (vertex bounds + needle padding + ray-time margin, the boxes the tree culls with) touches it --
-// for a triangle without needle padding the box's rectangle is cut down to the bounds of the
-// region the rounded test can reach (lg_region), and an edge record per (light, triangle) holds
-// that region's three edge lines.  A ray looks up one cell, checks the entries' rectangles, then
-// the survivors' edge records, and runs the exact per-ray test on what is left: ~10 byte compares,
-// ~5 records and ~2 triangle tests instead of ~30-40 node visits on the 10 M-triangle terrain.  Triangles that cover too many
-// cells, and (point lights) boxes across the plane through the light, are tested by every ray;
-// too many of those, or a list volume out of proportion, and the light keeps the tree walk.  Rays
-// whose point falls outside the grid walk the tree as well.
+// shadow ray only asks "any candidate on the ray" (gpu/light.cu:29-36).  Seen along the light a
+// ray is a POINT (x, y), and the set of rays the ROUNDED ray/triangle test of the reference can
+// accept for one triangle is a region of that plane bounded by three offset lines: region.cuh
+// (dir_lines / point_lines) derives it from the operation sequence of gpu/hit.cu:20-37 -- a bound,
+// not a heuristic; tests/test_region_cpu.py replays it in float32 on the host, triangles seen
+// edge-on from the light included.  Per light and triangle k_lg_records stores that region as a
+// float record (region::Record: three lines, rounded outwards) plus its bounding box; a uniform
+// grid in the light's projection, built once per scene (lights are part of the scene), lists for
+// every cell the triangles whose region can touch it (k_lg_scatter, from the same float records).
+// A ray looks up one cell, checks the entries' rectangles (four 7-bit bytes inside the cell), then
+// the survivors' records, and runs the exact per-ray test on what is left: ~10 byte compares, ~5
+// records and ~2 triangle tests instead of ~35 node visits on the 10 M-triangle terrain.
+//
+// Triangles whose region covers too many cells are tested by every ray (a short list); too many of
+// those, or a list volume out of proportion, and the light keeps the tree walk.  Rays whose point
+// falls outside the grid, or whose origin lies outside the scene's box (the bound on |origin -
+// vertex| the regions were built for), walk the tree as well.
 #pragma once
 
 namespace {
 
-constexpr unsigned LG_CELLS_MAX = 1024;      // per triangle
+constexpr unsigned LG_CELLS_MAX = 1u << 15;  // per triangle (a region that is a line across a 4 400-cell grid has ~6 000)
 constexpr float LG_PERSP_LIMIT = 4.0f;       // point lights: the grid spans |x|, |y| <= 4 on the plane at distance 1
+constexpr float LG_Q = 127.0f;               // rectangle bytes: 1 / 127 of a cell
+constexpr float LG_DILATE = 2.0e-3f;         // cells: a ray's cell index is computed in float (error < 1e-3 cells at 30 000 cells)
+constexpr float LG_BYTE_SLACK = 0.75f;       // bytes: rounding of the ray's position inside its cell (< 0.2 at 30 000 cells)
+
+// build-time view of a light: the frames region.cuh works with (doubles) and the domain the regions are clipped to
+struct LgBuild {
+  region::DirFrame df;
+  region::PointFrame pf;
+  double dom[4];               // x0, x1, y0, y1 in the light's projection
+};
 
 // x, y: position in the light's projection; den: depth along az for a point light (sign = side of the light)
 __device__ __forceinline__ void lg_project(const LightGrid &g, const V3 X, float &x, float &y, float &den) {
@@ -33,109 +47,53 @@ __device__ __forceinline__ void lg_project(const LightGrid &g, const V3 X, float
   }
 }
 
-// The region of triangle slot s's plane where the rounded test can accept a shadow ray of this
-// light, as a triangle in the light's projection (corners ax, ay).  Derivation: raster.cuh,
-// k_rast_setup; the direction of a shadow ray is not normalised (gpu/light.cu:68-120) but u and v do
-// not depend on its length; |origin - vertex| <= smax, the scene's diagonal (origins are hit
-// points); the incidence is that of the light's direction (1) or of the line from the light to the
-// farthest corner (2).  false: no such region (needle-padded triangle, edge-on, near the light's
-// plane) -- the triangle is culled by its box alone.
-__device__ __forceinline__ bool lg_region(const LightGrid &g, float pad_unit, float smax, const float4 a4, const float4 b4,
-                                          const float4 c4, float (&ax)[3], float (&ay)[3]) {
-  const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
-  V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
-  V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
-  const V3 lo0 = lo, hi0 = hi;
-  sliver_pad(v, pad_unit, lo, hi);
-  if (!(lo.x == lo0.x && lo.y == lo0.y && lo.z == lo0.z && hi.x == hi0.x && hi.y == hi0.y && hi.z == hi0.z)) return false;
-  const V3 n = vcross(mk(b4), mk(c4));
-  const float ln = vlen(n), l1 = vlen(mk(b4)), l2 = vlen(mk(c4));
-  float cosine, far = 0.0f;
-  if (g.kind == 1) cosine = fabsf(vdot(n, mk(g.az))) / ln;
-  else {
-    const V3 p0 = vsub(mk(g.org), v[0]);
-    far = fmaxf(vlen(p0), fmaxf(vlen(vsub(mk(g.org), v[1])), vlen(vsub(mk(g.org), v[2])))) + 6.0f * (l1 + l2);
-    cosine = fabsf(vdot(n, p0)) / (ln * far);
-  }
-  const float du = RAST_HULL_C * 5.9604645e-8f * smax * l2 / (ln * cosine);
-  const float dv = RAST_HULL_C * 5.9604645e-8f * smax * l1 / (ln * cosine);
-  if (!(ln > 0.0f && cosine >= RAST_HULL_MIN_COS && du < 2.0f && dv < 2.0f)) return false;       // NaN -> false
-  const float dw = du + dv + 2.4e-7f;
-  const V3 P[3] = {vsub(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), dv)),
-                   vsub(vadd(v[0], vscale(mk(b4), 1.0f + dw + dv)), vscale(mk(c4), dv)),
-                   vadd(vsub(v[0], vscale(mk(b4), du)), vscale(mk(c4), 1.0f + dw + du))};
-  float den[3];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) lg_project(g, P[k], ax[k], ay[k], den[k]);
-  if (g.kind == 2) {
-    const float near = fminf(fabsf(den[0]), fminf(fabsf(den[1]), fabsf(den[2])));
-    if (!(den[0] * den[1] > 0.0f && den[0] * den[2] > 0.0f && near > 1e-3f * far)) return false;
-  }
-  const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
-  return big < 1e30f;
+__device__ __forceinline__ float round_down(double v) {
+  float f = (float)v;
+  if ((double)f > v) f = nextafterf(f, -__builtin_huge_valf());
+  return f;
+}
+__device__ __forceinline__ float round_up(double v) {
+  float f = (float)v;
+  if ((double)f < v) f = nextafterf(f, __builtin_huge_valf());
+  return f;
 }
 
-// The projected rectangle of triangle slot s's culling box, intersected with the bounds of its
-// region (lg_region) when it has one.  false: the box has no rectangle
-// (it crosses the plane through a point light) and must be tested by every ray.
-__device__ __forceinline__ bool lg_rect(const DevScene &sc, const LightGrid &g, float eps, float smax, uint32_t s, float &x0,
-                                        float &x1, float &y0, float &y1) {
-  const float INFF = __builtin_huge_valf();
+// rec[4 slot + 0..2]: the region's record (region::Record, origin = the box's centre), rec[4 slot + 3]:
+// its bounding box (x0, x1, y0, y1), x0 > x1: no ray of this light can be accepted for the triangle.
+__global__ void __launch_bounds__(128) k_lg_records(const DevScene sc, const LightGrid g, const LgBuild lb, float4 *rec) {
+  const uint32_t s = blockIdx.x * 128 + threadIdx.x;
+  if (s >= sc.n_tris) return;
   const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
-  const V3 v[3] = {mk(a4), vadd(mk(a4), mk(b4)), vadd(mk(a4), mk(c4))};
-  V3 lo = mk(fminf(v[0].x, fminf(v[1].x, v[2].x)), fminf(v[0].y, fminf(v[1].y, v[2].y)), fminf(v[0].z, fminf(v[1].z, v[2].z)));
-  V3 hi = mk(fmaxf(v[0].x, fmaxf(v[1].x, v[2].x)), fmaxf(v[0].y, fmaxf(v[1].y, v[2].y)), fmaxf(v[0].z, fmaxf(v[1].z, v[2].z)));
-  sliver_pad(v, sc.pad_unit, lo, hi);
-  lo = mk(lo.x - eps, lo.y - eps, lo.z - eps);
-  hi = mk(hi.x + eps, hi.y + eps, hi.z + eps);
-  float dmin = INFF, dmax = -INFF;
-  x0 = y0 = INFF; x1 = y1 = -INFF;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    float x, y, den;
-    lg_project(g, mk((k & 1) ? hi.x : lo.x, (k & 2) ? hi.y : lo.y, (k & 4) ? hi.z : lo.z), x, y, den);
-    dmin = fminf(dmin, den); dmax = fmaxf(dmax, den);
-    x0 = fminf(x0, x); x1 = fmaxf(x1, x); y0 = fminf(y0, y); y1 = fmaxf(y1, y);
+  const float v0[3] = {a4.x, a4.y, a4.z}, e1[3] = {b4.x, b4.y, b4.z}, e2[3] = {c4.x, c4.y, c4.z};
+  region::Lines L;
+  region::Region R;
+  R.kind = 0;
+  const bool any = g.kind == 1 ? region::dir_lines(lb.df, v0, e1, e2, L) : region::point_lines(lb.pf, v0, e1, e2, L);
+  if (any) region::build(L, lb.dom[0], lb.dom[1], lb.dom[2], lb.dom[3], R);
+  float4 r0 = make_float4(0, 0, 0, 0), r1 = r0, r2 = r0, box = make_float4(1.0f, 0.0f, 1.0f, 0.0f);
+  if (R.kind) {
+    box = make_float4(round_down(R.x0), round_up(R.x1), round_down(R.y0), round_up(R.y1));
+    const float X0 = 0.5f * box.x + 0.5f * box.y, Y0 = 0.5f * box.z + 0.5f * box.w;
+    region::Record rc;
+    region::make_record(R, (double)X0, (double)Y0, ((double)box.y - (double)box.x) + ((double)box.w - (double)box.z), rc);
+    r0 = make_float4(rc.v[0], rc.v[1], rc.v[2], rc.v[3]);
+    r1 = make_float4(rc.v[4], rc.v[5], rc.v[6], rc.v[7]);
+    r2 = make_float4(rc.v[8], X0, Y0, rc.v[11]);
   }
-  if (g.kind == 2) {
-    const float near = fminf(fabsf(dmin), fabsf(dmax));
-    if (!(dmin * dmax > 0.0f) || !(near > 1e-3f * (dmax - dmin))) return false;
-  }
-  if (!(x0 > -1e30f && x1 < 1e30f && y0 > -1e30f && y1 < 1e30f)) return false;
-  // the rounding of the projection itself, ray side and box side (g.slack: build_light_grids)
-  x0 -= g.slack; x1 += g.slack; y0 -= g.slack; y1 += g.slack;
-  float ax[3], ay[3];
-  if (smax > 0.0f && lg_region(g, sc.pad_unit, smax, a4, b4, c4, ax, ay)) {
-    const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
-    const float sl = g.slack + 1e-6f * big;
-    x0 = fmaxf(x0, fminf(ax[0], fminf(ax[1], ax[2])) - sl); x1 = fminf(x1, fmaxf(ax[0], fmaxf(ax[1], ax[2])) + sl);
-    y0 = fmaxf(y0, fminf(ay[0], fminf(ay[1], ay[2])) - sl); y1 = fminf(y1, fmaxf(ay[0], fmaxf(ay[1], ay[2])) + sl);
-  }
-  return true;
+  rec[4 * (size_t)s] = r0; rec[4 * (size_t)s + 1] = r1; rec[4 * (size_t)s + 2] = r2; rec[4 * (size_t)s + 3] = box;
 }
 
-// cells [i0, i1] x [j0, j1] of the rectangle, clipped to the grid; false: nothing inside
-__device__ __forceinline__ bool lg_cells(const LightGrid &g, float x0, float x1, float y0, float y1, int &i0, int &i1,
-                                         int &j0, int &j1) {
-  const float fx0 = floorf((x0 - g.x0) * g.inv_cell), fx1 = floorf((x1 - g.x0) * g.inv_cell);
-  const float fy0 = floorf((y0 - g.y0) * g.inv_cell), fy1 = floorf((y1 - g.y0) * g.inv_cell);
-  if (fx1 < 0.0f || fy1 < 0.0f || fx0 > (float)(g.nx - 1) || fy0 > (float)(g.ny - 1)) return false;
-  i0 = (int)fmaxf(fx0, 0.0f); i1 = (int)fminf(fx1, (float)(g.nx - 1));
-  j0 = (int)fmaxf(fy0, 0.0f); j1 = (int)fminf(fy1, (float)(g.ny - 1));
-  return true;
-}
-
-// bounds of the rectangles of every stride-th triangle: out[0..3] = min x, max x, min y, max y
-// (ordered uint).  The grid does not have to cover every rectangle: k_lg_scatter clips to the grid
-// and a ray whose point is off the grid walks the tree, so big scenes look at a sample.
-__global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t stride,
-                                                   uint32_t *out) {
+// bounds of the boxes of every stride-th triangle: out[0..3] = min x, max x, min y, max y (ordered
+// uint).  The grid does not have to cover every region: k_lg_scatter clips to the grid and a ray
+// whose point is off the grid walks the tree, so big scenes look at a sample.
+__global__ void __launch_bounds__(256) k_lg_bounds(const float4 *rec, uint32_t n, uint32_t stride, float huge, uint32_t *out) {
   const uint32_t s = (blockIdx.x * 256 + threadIdx.x) * stride;
   const float INFF = __builtin_huge_valf();
   float x0 = INFF, x1 = -INFF, y0 = INFF, y1 = -INFF;
-  if (s < sc.n_tris) {
-    float a0, a1, b0, b1;
-    if (lg_rect(sc, g, eps, smax, s, a0, a1, b0, b1)) { x0 = a0; x1 = a1; y0 = b0; y1 = b1; }
+  if (s < n) {
+    const float4 b = __ldg(rec + 4 * (size_t)s + 3);
+    // regions that are lines across the whole domain say nothing about where the geometry is
+    if (b.x <= b.y && b.y - b.x < huge && b.w - b.z < huge) { x0 = b.x; x1 = b.y; y0 = b.z; y1 = b.w; }
   }
   const uint32_t m0 = __reduce_min_sync(0xffffffffu, f2ord(x0)), m1 = __reduce_max_sync(0xffffffffu, f2ord(x1));
   const uint32_t m2 = __reduce_min_sync(0xffffffffu, f2ord(y0)), m3 = __reduce_max_sync(0xffffffffu, f2ord(y1));
@@ -144,116 +102,158 @@ __global__ void __launch_bounds__(256) k_lg_bounds(const DevScene sc, const Ligh
   }
 }
 
-// FILL = false: counts[cell] += 1 per covered cell, state[0] = number of large triangles (listed in
-// state[2..]), state[1] != 0: give up.  FILL = true: entries[cell_start[cell] + cursor[cell]++] = slot.
-// An entry is (slot, the rectangle clipped to the cell in 1/127 of the cell, rounded outwards), the
-// rectangle as four 7-bit bytes x0, 127 - x1, y0, 127 - y1: a ray turns its point into the bytes
+// An entry is (slot, the region's rectangle inside the cell in 1/127 of the cell, rounded outwards),
+// the rectangle as four 7-bit bytes x0, 127 - x1, y0, 127 - y1: a ray turns its point into the bytes
 // floor(qx), 127 - ceil(qx), floor(qy), 127 - ceil(qy) with bit 7 set in each, and "inside" is
 // "every byte of the entry <= the ray's byte", i.e. no byte of (ray - entry) loses its bit 7: one
 // subtraction, one AND, one compare on 4 sequential bytes, before the ray touches the triangle's
-// edge record or the triangle itself (scattered 16-byte loads and the exact test).
-constexpr float LG_Q = 127.0f;
+// record or the triangle itself (scattered 16-byte loads and the exact test).
 __device__ __forceinline__ uint32_t lg_pack(const LightGrid &g, int i, int j, float x0, float x1, float y0, float y1) {
-  const float cx = g.x0 + (float)i / g.inv_cell, cy = g.y0 + (float)j / g.inv_cell;
+  const float cx = g.x0 + (float)i * g.cell, cy = g.y0 + (float)j * g.cell;
   auto q = [&](float v, float c, bool up) {
     float t = (v - c) * g.inv_cell * LG_Q;
-    t = up ? ceilf(t + 0.02f) : floorf(t - 0.02f);
+    t = up ? ceilf(t + LG_BYTE_SLACK) : floorf(t - LG_BYTE_SLACK);
     return (uint32_t)fminf(fmaxf(t, 0.0f), LG_Q);
   };
   return q(x0, cx, false) | ((127u - q(x1, cx, true)) << 8) | (q(y0, cy, false) << 16) | ((127u - q(y1, cy, true)) << 24);
 }
 
+// The cells of triangle slot s, row by row: f(i, j, x0, x1, y0, y1) for every cell the region can touch
+// (region::record_band on the float record the rays are tested against, dilated by the rounding of a
+// ray's own cell index).  Returns the number of cells, or ~0u when it exceeds LG_CELLS_MAX.
+// (jfirst, jstep): the rows j0 + jfirst, j0 + jfirst + jstep, ... only -- k_lg_big splits a triangle's rows over a CTA.
+template <typename F>
+__device__ __forceinline__ unsigned lg_cells(const LightGrid &g, const float4 *rec, uint32_t s, bool count_only, F f,
+                                             int jfirst = 0, int jstep = 1, unsigned limit = LG_CELLS_MAX, int *rows = nullptr) {
+  const float4 box = __ldg(rec + 4 * (size_t)s + 3);
+  if (!(box.x <= box.y)) return 0;
+  const float4 r0 = __ldg(rec + 4 * (size_t)s), r1 = __ldg(rec + 4 * (size_t)s + 1), r2 = __ldg(rec + 4 * (size_t)s + 2);
+  const float X0 = r2.y, Y0 = r2.z;
+  const float dil = LG_DILATE * g.cell;
+  const float fj0 = floorf((box.z - dil - g.y0) * g.inv_cell), fj1 = floorf((box.w + dil - g.y0) * g.inv_cell);
+  if (fj1 < 0.0f || fj0 > (float)(g.ny - 1)) return 0;
+  const int j0 = (int)fmaxf(fj0, 0.0f), j1 = (int)fminf(fj1, (float)(g.ny - 1));
+  const float xext = fmaxf(fabsf(box.x - X0), fabsf(box.y - X0)) + 2.0f * g.cell;
+  unsigned total = 0;
+  if (rows) *rows = j1 - j0 + 1;
+  for (int j = j0 + jfirst; j <= j1; j += jstep) {
+    const float ya = fmaxf(g.y0 + (float)j * g.cell - dil, box.z - dil), yb = fminf(g.y0 + (float)(j + 1) * g.cell + dil, box.w + dil);
+    float lo, hi;
+    if (!region::record_band(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, ya - Y0, yb - Y0, xext, lo, hi)) continue;
+    const float xa = fmaxf(X0 + lo, box.x) - dil, xb = fminf(X0 + hi, box.y) + dil;
+    if (!(xa <= xb)) continue;
+    const float fi0 = floorf((xa - g.x0) * g.inv_cell), fi1 = floorf((xb - g.x0) * g.inv_cell);
+    if (fi1 < 0.0f || fi0 > (float)(g.nx - 1)) continue;
+    const int i0 = (int)fmaxf(fi0, 0.0f), i1 = (int)fminf(fi1, (float)(g.nx - 1));
+    total += (unsigned)(i1 - i0 + 1);
+    if (total > limit) return ~0u;
+    if (!count_only)
+      for (int i = i0; i <= i1; ++i) f(i, j, xa, xb, ya, yb);
+  }
+  return total;
+}
+
+// FILL = false: counts[cell] += 1 per covered cell, state[0] = number of large triangles (listed in
+// state[2..]), state[1] != 0: give up.  FILL = true: entries[cell_start[cell] + cursor[cell]++] = (slot, rectangle).
+constexpr int LG_BIG_ROWS = 64;              // a triangle over more grid rows is listed for k_lg_big
+constexpr unsigned LG_BIG_CAP = 1u << 18;    // slots on that list (state[32..])
+constexpr int LG_STATE_WORDS = 32;
+
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const LightGrid g, float eps, float smax, uint32_t *counts,
+__global__ void __launch_bounds__(256) k_lg_scatter(const DevScene sc, const LightGrid g, const float4 *rec, uint32_t *counts,
                                                     uint32_t *state, const uint32_t *cell_start, uint2 *entries) {
   const uint32_t s = blockIdx.x * 256 + threadIdx.x;
   if (s >= sc.n_tris) return;
-  float x0, x1, y0, y1;
-  int i0, i1, j0, j1;
-  bool large = !lg_rect(sc, g, eps, smax, s, x0, x1, y0, y1);
-  if (!large) {
-    if (!lg_cells(g, x0, x1, y0, y1, i0, i1, j0, j1)) return;       // entirely outside the grid
-    large = (unsigned)(i1 - i0 + 1) * (unsigned)(j1 - j0 + 1) > LG_CELLS_MAX;
+  // triangles over many rows (regions that are lines across the grid): one CTA each, rows in parallel (k_lg_big)
+  {
+    const float4 box = __ldg(rec + 4 * (size_t)s + 3);
+    if (box.x <= box.y && (box.w - box.z) * g.inv_cell > (float)LG_BIG_ROWS) {
+      if (FILL) return;                               // k_lg_big<true> fills them
+      const unsigned k = atomicAdd(state + 24, 1u);
+      if (k < LG_BIG_CAP) state[LG_STATE_WORDS + k] = s; else state[1] = 1u;      // list full: the light keeps the tree walk
+      return;
+    }
   }
-  if (large) {
+  const unsigned cells = lg_cells(g, rec, s, true, [](int, int, float, float, float, float) {});
+  if (cells == 0) return;
+  if (cells == ~0u) {
     if (!FILL) {
       const unsigned k = atomicAdd(state, 1u);
       if (k < (unsigned)LG_LARGE_MAX) state[2 + k] = s; else state[1] = 1u;
     }
     return;
   }
-  for (int j = j0; j <= j1; ++j)
-    for (int i = i0; i <= i1; ++i) {
+  lg_cells(g, rec, s, false, [&](int i, int j, float xa, float xb, float ya, float yb) {
+    const size_t c = (size_t)j * g.nx + i;
+    const uint32_t k = atomicAdd(counts + c, 1u);
+    if (FILL) entries[cell_start[c] + k] = make_uint2(s, lg_pack(g, i, j, xa, xb, ya, yb));
+  });
+}
+
+// The listed triangles: one CTA per triangle, thread t takes the grid rows j0 + t, j0 + t + 128, ...
+// Pass 1 (all threads): cells per row -> the CTA's total decides "large" (more than LG_CELLS_MAX cells:
+// tested by every ray instead); pass 2: count or fill, exactly the cells k_lg_scatter would produce.
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_lg_big(const DevScene sc, const LightGrid g, const float4 *rec, uint32_t *counts,
+                                                uint32_t *state, const uint32_t *cell_start, uint2 *entries) {
+  __shared__ unsigned s_total;
+  const unsigned n_big = min(state[24], LG_BIG_CAP);
+  for (unsigned bi = blockIdx.x; bi < n_big; bi += gridDim.x) {
+    const uint32_t s = state[LG_STATE_WORDS + bi];
+    if (threadIdx.x == 0) s_total = 0;
+    __syncthreads();
+    const unsigned mine = lg_cells(g, rec, s, true, [](int, int, float, float, float, float) {}, (int)threadIdx.x, 128, 0xfffffff0u);
+    if (mine) atomicAdd(&s_total, mine);
+    __syncthreads();
+    const unsigned total = s_total;
+    __syncthreads();
+    if (total == 0) continue;
+    if (total > LG_CELLS_MAX) {
+      if (!FILL && threadIdx.x == 0) {
+        const unsigned k = atomicAdd(state, 1u);
+        if (k < (unsigned)LG_LARGE_MAX) state[2 + k] = s; else state[1] = 1u;
+      }
+      continue;
+    }
+    lg_cells(g, rec, s, false, [&](int i, int j, float xa, float xb, float ya, float yb) {
       const size_t c = (size_t)j * g.nx + i;
       const uint32_t k = atomicAdd(counts + c, 1u);
-      if (FILL) entries[cell_start[c] + k] = make_uint2(s, lg_pack(g, i, j, x0, x1, y0, y1));
-    }
-}
-
-// Edge record of a triangle in one light's projection: rec[3 slot + 0..2] = (n0x, n0y, c0, n1x)
-// (n1y, c1, n2x, n2y) (c2, -, -, -); a ray whose point (x, y) has n . (x, y) + c > 0 for one of the
-// three edges of the triangle's region (lg_region) cannot be accepted by the rounded test and
-// skips the triangle without touching it.  Triangles without a region, and regions seen edge-on,
-// get the record that accepts every point.
-__global__ void __launch_bounds__(256) k_lg_records(const DevScene sc, const LightGrid g, float smax, float4 *rec) {
-  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
-  if (s >= sc.n_tris) return;
-  float4 r0 = make_float4(0, 0, -1, 0), r1 = make_float4(0, -1, 0, 0), r2 = make_float4(-1, 0, 0, 0);
-  const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
-  float ax[3], ay[3];
-  if (lg_region(g, sc.pad_unit, smax, a4, b4, c4, ax, ay)) {
-    const float big = fmaxf(fmaxf(fabsf(ax[0]), fabsf(ay[0])), fmaxf(fmaxf(fabsf(ax[1]), fabsf(ay[1])), fmaxf(fabsf(ax[2]), fabsf(ay[2]))));
-    bool ok = true;
-    float en[3][3], longest = 0.0f;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const int kb = (k + 1) % 3;
-      longest = fmaxf(longest, fmaxf(fabsf(ax[kb] - ax[k]), fabsf(ay[kb] - ay[k])));
-    }
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      const int kb = (k + 1) % 3, kc = (k + 2) % 3;
-      float nx = ay[kb] - ay[k], ny = ax[k] - ax[kb];
-      const float len = sqrtf(nx * nx + ny * ny);
-      nx /= len; ny /= len;
-      const float side = nx * (ax[kc] - ax[k]) + ny * (ay[kc] - ay[k]);
-      ok = ok && len > 0.0f && fabsf(side) > 1e-3f * longest;       // edge-on in this projection: no record
-      if (side > 0.0f) { nx = -nx; ny = -ny; }
-      // g.slack: rounding of the projection, ray side and triangle side, and of the ray's direction
-      // (lg_rect); the last term: rounding of n . (x, y) + c at coordinates of this size
-      const float off = (g.slack + 1e-6f * big) * (fabsf(nx) + fabsf(ny));
-      en[k][0] = nx; en[k][1] = ny; en[k][2] = -(nx * ax[k] + ny * ay[k]) - off;
-    }
-    if (ok) {
-      r0 = make_float4(en[0][0], en[0][1], en[0][2], en[1][0]);
-      r1 = make_float4(en[1][1], en[1][2], en[2][0], en[2][1]);
-      r2 = make_float4(en[2][2], 0, 0, 0);
-    }
+      if (FILL) entries[cell_start[c] + k] = make_uint2(s, lg_pack(g, i, j, xa, xb, ya, yb));
+    }, (int)threadIdx.x, 128, 0xfffffff0u);
   }
-  rec[3 * (size_t)s] = r0; rec[3 * (size_t)s + 1] = r1; rec[3 * (size_t)s + 2] = r2;
 }
 
-// 1: some candidate on the ray, 0: none, -1: this ray has to walk the tree (its point is off the grid)
+// ---- the lookup ----
+// 1: some candidate on the ray, 0: none, -1: this ray has to walk the tree (its point is off the grid, or its
+// origin outside the box the regions were bounded for).
+//
+// Three loops per chunk of 32 entries, because the lanes of a warp walk different lists in lockstep and a
+// single loop made the warp pay the most expensive branch in almost every iteration: (1) the entries'
+// rectangle words against the point, (2) the records of the survivors, (3) the exact test on what is left,
+// leaving at the first accepted candidate.  A warp-cooperative variant (survivors of all 32 rays through
+// shared-memory queues so that stages 2 and 3 run 32 at a time) was built and measured: lanes per
+// instruction 27 instead of 23, but 11.9 G instead of 8.3 G warp-instructions and 18.6 instead of 11.9 ms
+// on C5 -- a record test is ~35 instructions, the queue traffic around it costs more than the idle lanes
+// (profiles/r2_ncu_kframe_coop.txt).
 __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, const V3 o, const V3 d) {
+  if (!(o.x >= g.bmin.x && o.x <= g.bmax.x && o.y >= g.bmin.y && o.y <= g.bmax.y && o.z >= g.bmin.z && o.z <= g.bmax.z)) return -1;
   float x, y, den;
   lg_project(g, o, x, y, den);
-  const float fi = floorf((x - g.x0) * g.inv_cell), fj = floorf((y - g.y0) * g.inv_cell);
-  if (!(fi >= 0.0f && fj >= 0.0f && fi <= (float)(g.nx - 1) && fj <= (float)(g.ny - 1))) return -1;
-  if (g.kind == 2 && !(fabsf(den) > 1e-6f * (fabsf(o.x - g.org.x) + fabsf(o.y - g.org.y) + fabsf(o.z - g.org.z)))) return -1;
+  const float fx = (x - g.x0) * g.inv_cell, fy = (y - g.y0) * g.inv_cell;
+  const float fi = floorf(fx), fj = floorf(fy);
+  if (!(fi >= 0.0f && fj >= 0.0f && fi <= (float)(g.nx - 1) && fj <= (float)(g.ny - 1))) return -1;      // NaN too
+  if (g.kind == 2 && !(fabsf(den) > 1e-6f * (fabsf(o.x - g.org.x) + fabsf(o.y - g.org.y) + fabsf(o.z - g.org.z)) &&
+                       fabsf(x) <= LG_PERSP_LIMIT && fabsf(y) <= LG_PERSP_LIMIT)) return -1;
   Best b;
   b.dist = INF; b.id = 0x7fffffff; b.slot = -1;
   for (uint32_t k = 0; k < g.n_large; ++k)
     if (consider<true>(sc, o, d, (int)g.large[k], b)) return 1;
   const size_t c = (size_t)(int)fj * g.nx + (int)fi;
   const uint32_t e0 = __ldg(g.cell_start + c), e1 = __ldg(g.cell_start + c + 1);
-  // the ray's point inside its cell as the four bytes the entries compare with (lg_pack); 0.01:
-  // rounding of the point's own position inside the cell
-  const float qx = ((x - g.x0) * g.inv_cell - fi) * LG_Q, qy = ((y - g.y0) * g.inv_cell - fj) * LG_Q;
+  // the ray's point inside its cell as the four bytes the entries compare with (lg_pack)
+  const float qx = (fx - fi) * LG_Q, qy = (fy - fj) * LG_Q;
   auto byte = [](float v) { return (uint32_t)fminf(fmaxf(v, 0.0f), LG_Q); };
-  const uint32_t P = (byte(floorf(qx + 0.01f)) | ((127u - byte(ceilf(qx - 0.01f))) << 8) | (byte(floorf(qy + 0.01f)) << 16) |
-                      ((127u - byte(ceilf(qy - 0.01f))) << 24)) | 0x80808080u;
-  // Three phases per chunk of 32 entries, because the lanes of a warp walk different lists in
-  // lockstep: first only the cheap rectangle checks (a bit per entry that survives), ...
+  const uint32_t P = (byte(floorf(qx)) | ((127u - byte(ceilf(qx))) << 8) | (byte(floorf(qy)) << 16) | ((127u - byte(ceilf(qy))) << 24)) | 0x80808080u;
   for (uint32_t base = e0; base < e1; base += 32) {
     const uint32_t cnt = min(32u, e1 - base);
     uint32_t mask = 0;
@@ -262,19 +262,13 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
       const uint32_t r = __ldg(&g.entries[base + k].y);
       if (((P - r) & 0x80808080u) == 0x80808080u) mask |= 1u << k;
     }
-    // ... then the edge records of the survivors (two 16-byte loads and three dot products each),
-    // again a loop of its own: what is left for the exact test is a fraction of the rectangle hits
-    if (g.rec) {
-      uint32_t m = mask;
-      while (m) {
-        const uint32_t k = (uint32_t)__ffs((int)m) - 1u;
-        m &= m - 1u;
-        const uint32_t slot = __ldg(&g.entries[base + k].x);
-        const float4 r0 = __ldg(g.rec + 3 * (size_t)slot), r1 = __ldg(g.rec + 3 * (size_t)slot + 1);
-        const float c2 = __ldg(&g.rec[3 * (size_t)slot + 2].x);
-        if (r0.x * x + r0.y * y + r0.z > 0.0f || r0.w * x + r1.x * y + r1.y > 0.0f || r1.z * x + r1.w * y + c2 > 0.0f)
-          mask &= ~(1u << k);
-      }
+    uint32_t m = mask;
+    while (m) {
+      const uint32_t k = (uint32_t)__ffs((int)m) - 1u;
+      m &= m - 1u;
+      const size_t s = (size_t)__ldg(&g.entries[base + k].x);
+      const float4 r0 = __ldg(g.rec + 4 * s), r1 = __ldg(g.rec + 4 * s + 1), r2 = __ldg(g.rec + 4 * s + 2);
+      if (!region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, x - r2.y, y - r2.z)) mask &= ~(1u << k);
     }
     while (mask) {
       const uint32_t k = (uint32_t)__ffs((int)mask) - 1u;

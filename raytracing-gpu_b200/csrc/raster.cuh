@@ -209,7 +209,10 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
 // the expensive stage whatever the rectangles look like.  Queue entries carry their triangle, so
 // the queue simply runs on across items.
 constexpr int RAST_WARPS = 8;
-constexpr int RAST_SCAN_MAX = 96;             // rectangles of more samples are walked row by row
+#ifndef RTB_RAST_SCAN_MAX
+#define RTB_RAST_SCAN_MAX 96
+#endif
+constexpr int RAST_SCAN_MAX = RTB_RAST_SCAN_MAX;   // rectangles of more samples are walked row by row
 // k / w == (k * c_rast_rw[w]) >> 16 for k < 1024, w <= 32: 65536 / w + 1 (the division costs 20 instructions per item)
 __constant__ unsigned c_rast_rw[33] = {0, 65537, 32769, 21846, 16385, 13108, 10923, 9363, 8193, 7282, 6554, 5958, 5462, 5042, 4682, 4370, 4097, 3856, 3641, 3450, 3277, 3121, 2979, 2850, 2731, 2622, 2521, 2428, 2341, 2260, 2185, 2115, 2049};
 

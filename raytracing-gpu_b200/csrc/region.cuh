@@ -297,6 +297,45 @@ RTB_RG void record_span(float r0x, float r0y, float r0z, float r0w, float r1x, f
   a = (int)fa; b = (int)fb;
 }
 
+// The x range (relative to the record's origin) in which record_inside can pass for SOME dy of the
+// band [dy0, dy1]: what the light grids use to list the cells of a region from the very record the
+// rays are tested against.  A superset: every edge takes the dy of the band that suits it best, and
+// the bounds are widened by the rounding of this evaluation and of record_inside's (xext = the
+// largest |dx| of interest).  false: no point of the band passes.
+RTB_RG bool record_band(float r0x, float r0y, float r0z, float r0w, float r1x, float r1y, float r1z, float r1w,
+                        float r2x, float flag, float dy0, float dy1, float xext, float &lo, float &hi) {
+  const float BIGF = 3.0e38f;
+  lo = -BIGF; hi = BIGF;
+  if (flag == 0.0f) return true;
+  const float nx[3] = {r0x, r0w, r1z}, ny[3] = {r0y, r1x, r1w}, c[3] = {r0z, r1y, r2x};
+  float lo1 = -BIGF, hi1 = BIGF, lo2 = -BIGF, hi2 = BIGF;
+  bool ok1 = true, ok2 = flag < 0.0f;
+  for (int k = 0; k < 3; ++k) {
+    const float t0 = ny[k] * dy0, t1 = ny[k] * dy1;
+    const float tmin = fminf(t0, t1), tmax = fmaxf(t0, t1);
+    const float err = 1.0e-6f * (fabsf(nx[k]) * xext + fmaxf(fabsf(t0), fabsf(t1)) + fabsf(c[k])) + 1e-30f;
+    // first part: nx dx <= -c - ny dy for some dy;   second part: nx dx >= flag - c - ny dy for some dy
+    const float b1 = -c[k] - tmin + err, b2 = flag - c[k] - tmax - err;
+    if (nx[k] != 0.0f) {
+      const float inv = 1.0f / nx[k];
+      const float v1 = b1 * inv, v2 = b2 * inv;
+      const float w1 = 4.0e-7f * fabsf(v1) + 1e-30f, w2 = 4.0e-7f * fabsf(v2) + 1e-30f;
+      if (nx[k] > 0.0f) { hi1 = fminf(hi1, v1 + w1); lo2 = fmaxf(lo2, v2 - w2); }
+      else { lo1 = fmaxf(lo1, v1 - w1); hi2 = fminf(hi2, v2 + w2); }
+    } else {
+      if (b1 < 0.0f) ok1 = false;
+      if (b2 > 0.0f) ok2 = false;
+    }
+  }
+  ok1 = ok1 && lo1 <= hi1;
+  ok2 = ok2 && lo2 <= hi2;
+  if (!ok1 && !ok2) return false;
+  lo = BIGF; hi = -BIGF;
+  if (ok1) { lo = fminf(lo, lo1); hi = fmaxf(hi, hi1); }
+  if (ok2) { lo = fminf(lo, lo2); hi = fmaxf(hi, hi2); }
+  return true;
+}
+
 }  // namespace region
 }  // namespace rtb
 

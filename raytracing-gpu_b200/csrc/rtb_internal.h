@@ -44,12 +44,13 @@ constexpr int LG_LARGE_MAX = 16;
 struct LightGrid {
   int kind;                     // 0: none (shadow rays walk the tree), 1: directional light, 2: point light
   float3 org, ax, ay, az;       // az: the light's direction (1) / the axis from the light towards the scene (2)
-  float x0, y0, inv_cell, slack;   // cell (i, j) = x0 + [i, i + 1) / inv_cell; slack: rounding of the projection
+  float x0, y0, inv_cell, cell; // cell (i, j) = (x0, y0) + [i, i + 1) x [j, j + 1) * cell
   int nx, ny;
+  float3 bmin, bmax;            // the scene's box (a hair inflated): the regions bound |origin - vertex| by its diagonal
   const uint32_t *cell_start;   // [nx * ny + 1]
-  const uint2 *entries;         // (triangle slot, its rectangle inside the cell), cell by cell
-  const float4 *rec;            // 3 per triangle slot: edge record in this projection (lightgrid.cuh), or nullptr
-  uint32_t n_large;             // triangles every ray tests: they cover too many cells or cross the light's plane
+  const uint2 *entries;         // (triangle slot, its region's rectangle inside the cell), cell by cell
+  const float4 *rec;            // 4 per triangle slot: region record (3) + bounding box in this projection (lightgrid.cuh)
+  uint32_t n_large;             // triangles every ray tests: their regions cover too many cells
   uint32_t large[LG_LARGE_MAX];
 };
 

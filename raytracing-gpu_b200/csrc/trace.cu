@@ -238,6 +238,21 @@ __device__ __forceinline__ uint32_t apply_specular(uint32_t color, const V3 inc_
   return color_add(color, color_mul(ks_col, Ls));
 }
 
+// A shadow ray through the hierarchy (or the exhaustive loop): what every shadow ray of a scene without
+// light grids does, and the rays a grid cannot answer.  One out-of-line copy: the frame kernel's hot
+// path (grid lookups) stays small enough for the instruction cache.
+struct WalkArgs { const float4 *v0, *e1, *e2, *nodes; int root; uint32_t n_tris; float abs_max, margin_k; };
+
+template <int TRACER>
+__device__ __noinline__ bool shadow_walk(const WalkArgs w, const V3 P, const V3 dir) {
+  DevScene sc;                    // only the fields a traversal reads (arguments by value: see lightgrid.cuh lg_exact32)
+  sc.v0 = w.v0; sc.e1 = w.e1; sc.e2 = w.e2; sc.nodes = w.nodes; sc.root = w.root; sc.n_tris = w.n_tris;
+  sc.abs_max = w.abs_max; sc.margin_k = w.margin_k;
+  Best b;
+  Counters c = {0, 0, 0, 0, 0};
+  return trace<TRACER, true, false>(sc, P, dir, b, c);
+}
+
 // gpu/light.cu:50-127
 template <int TRACER, bool COUNT>
 __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 P, const V3 Nrm, Counters &c) {
@@ -253,15 +268,20 @@ __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 
     if (type == AMBIENT) {
       color = color_add(color, color_mults(lcol, ka));
     } else if (type == DIRECTIONAL || type == POINT) {
-      // one shadow-ray call site for both light kinds: the traversal is inlined once, not twice
+      // one shadow-ray call site for both light kinds
       const V3 L = vscale(lv, -1);
       const V3 dir = type == DIRECTIONAL ? L : vsub(lv, P);
-      Best b;
       if (COUNT) ++c.shadow;
       // shadow-ray grid of this light (lightgrid.cuh) when it has one; -1: this ray walks the tree
       int occluded = -1;
       if (TRACER == RTB_TRACER_TREE && !COUNT && sc.lgrids && sc.lgrids[i].kind) occluded = lg_any(sc, sc.lgrids[i], P, dir);
-      if (occluded < 0) occluded = trace<TRACER, true, COUNT>(sc, P, dir, b, c, slot) ? 1 : 0;
+      if (occluded < 0) {
+        if (COUNT) { Best b; occluded = trace<TRACER, true, true>(sc, P, dir, b, c) ? 1 : 0; }      // the counting frame: inline, counters live
+        else {
+          const WalkArgs w = {sc.v0, sc.e1, sc.e2, sc.nodes, sc.root, sc.n_tris, sc.abs_max, sc.margin_k};
+          occluded = shadow_walk<TRACER>(w, P, dir) ? 1 : 0;
+        }
+      }
       occluded = rejoin(occluded);
       if (!occluded) {
         uint32_t t = color_mults(lcol, kd);
@@ -486,19 +506,40 @@ float get_margin_k() { return g_margin_k; }
 constexpr uint32_t LG_MIN_TRIS = 1u << 15;
 constexpr int LG_MAX_GRIDS = 8;
 
+// device scratch of one light's grid build, freed on every way out (kept blocks excepted)
+struct LgScratch {
+  cudaStream_t st;
+  void *p[8] = {nullptr};
+  int n = 0;
+  template <typename T> int alloc(T **out, size_t bytes) {
+    *out = nullptr;
+    RTB_CUDA(cudaMallocAsync((void **)out, bytes, st));
+    p[n++] = *out;
+    return RTB_OK;
+  }
+  void keep(void *q) { for (int k = 0; k < n; ++k) if (p[k] == q) p[k] = nullptr; }
+  ~LgScratch() { for (int k = 0; k < n; ++k) if (p[k]) cudaFreeAsync(p[k], st); }
+};
+
 int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights, const float bmin[3],
                       const float bmax[3], cudaStream_t st) {
-  if (!S.has_tree || S.n_tris < LG_MIN_TRIS || !n_lights) return RTB_OK;
+  if (!S.has_tree || S.n_tris < LG_MIN_TRIS || S.n_tris >= (1u << 27) || !n_lights) return RTB_OK;
   std::vector<LightGrid> grids(n_lights);
   memset(grids.data(), 0, grids.size() * sizeof(LightGrid));
   const DevScene sc = S.dev();
   const uint32_t n = S.n_tris;
-  const float eps = (get_margin_k() + 2.0f) * 1.1920929e-7f * (2.001f * S.abs_max);   // trace_tree's margin at any origin inside the scene
   const unsigned blocks = (n + 255) / 256;
-  // |shadow-ray origin - vertex| <= the scene's diagonal (origins are hit points)
-  const float diag = 1.001f * sqrtf((bmax[0] - bmin[0]) * (bmax[0] - bmin[0]) + (bmax[1] - bmin[1]) * (bmax[1] - bmin[1]) +
-                                    (bmax[2] - bmin[2]) * (bmax[2] - bmin[2])) + 1e-30f;
-  static const bool lg_records = [] { const char *e = getenv("RTB_LG_RECORDS"); return !(e && atoi(e) == 0); }();
+  // Shadow-ray origins are hit points: inside the scene's box up to the rounding of the hit point
+  // (lg_any_warp sends everything else to the tree).  The regions bound |origin - vertex| and |origin| with it.
+  double lo[3], hi[3], diag2 = 0, pmax2 = 0;
+  for (int k = 0; k < 3; ++k) {
+    const double pad = 1e-5 * (fabs((double)bmin[k]) + fabs((double)bmax[k]) + ((double)bmax[k] - (double)bmin[k])) + 1e-30;
+    lo[k] = (double)bmin[k] - pad; hi[k] = (double)bmax[k] + pad;
+    diag2 += (hi[k] - lo[k]) * (hi[k] - lo[k]);
+    const double m = fmax(fabs(lo[k]), fabs(hi[k]));
+    pmax2 += m * m;
+  }
+  const double diag = sqrt(diag2) * (1.0 + 1e-6), pmax = sqrt(pmax2) * (1.0 + 1e-6);
   int built = 0, mem = 0;
   auto unit = [](float x, float y, float z, float3 &o) {
     const float r = sqrtf(x * x + y * y + z * z);
@@ -510,21 +551,21 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     const struct light &l = lights[i];
     LightGrid g;
     memset(&g, 0, sizeof g);
+    LgBuild lb;
+    memset(&lb, 0, sizeof lb);
+    const float cx = 0.5f * (bmin[0] + bmax[0]), cy = 0.5f * (bmin[1] + bmax[1]), cz = 0.5f * (bmin[2] + bmax[2]);
     if (l.type == DIRECTIONAL) {
       if (!unit(l.v.x, l.v.y, l.v.z, g.az)) continue;
       g.kind = 1;
-      g.slack = 4e-6f * (2.0f * S.abs_max + 1e-30f);
     } else if (l.type == POINT) {
       g.org = make_float3(l.v.x, l.v.y, l.v.z);
-      const float cx = 0.5f * (bmin[0] + bmax[0]), cy = 0.5f * (bmin[1] + bmax[1]), cz = 0.5f * (bmin[2] + bmax[2]);
       const float ext = fmaxf(bmax[0] - bmin[0], fmaxf(bmax[1] - bmin[1], bmax[2] - bmin[2]));
       if (!unit(cx - l.v.x, cy - l.v.y, cz - l.v.z, g.az)) continue;
       const float dist = sqrtf((cx - l.v.x) * (cx - l.v.x) + (cy - l.v.y) * (cy - l.v.y) + (cz - l.v.z) * (cz - l.v.z));
-      if (!(dist > 1e-3f * ext)) continue;            // a light at the centre of the scene: boxes cross its plane everywhere
+      if (!(dist > 1e-3f * ext)) continue;            // a light at the centre of the scene: half of it is off the grid
       g.kind = 2;
-      g.slack = 2e-5f;
     } else continue;
-    // any orthonormal frame around az
+    // any orthonormal frame around az (float: the frame the rays are projected with)
     {
       const float ax = fabsf(g.az.x), ay = fabsf(g.az.y), az = fabsf(g.az.z);
       float3 h = ax <= ay && ax <= az ? make_float3(1, 0, 0) : (ay <= az ? make_float3(0, 1, 0) : make_float3(0, 0, 1));
@@ -532,15 +573,57 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
       if (!unit(a.x, a.y, a.z, g.ax)) continue;
       g.ay = make_float3(g.az.y * g.ax.z - g.az.z * g.ax.y, g.az.z * g.ax.x - g.az.x * g.ax.z, g.az.x * g.ax.y - g.az.y * g.ax.x);
     }
-    // extent of the projection
+    g.bmin = make_float3((float)lo[0], (float)lo[1], (float)lo[2]);
+    g.bmax = make_float3((float)hi[0], (float)hi[1], (float)hi[2]);
+    // the same frame in double for region.cuh, and the domain the regions are clipped to
+    const double AX[3] = {g.ax.x, g.ax.y, g.ax.z}, AY[3] = {g.ay.x, g.ay.y, g.ay.z}, AZ[3] = {g.az.x, g.az.y, g.az.z};
+    if (g.kind == 1) {
+      region::DirFrame &f = lb.df;
+      // gpu/light.cu:70-74: the shadow ray's direction is scale(l.v, -1), exactly
+      f.d[0] = -(double)l.v.x; f.d[1] = -(double)l.v.y; f.d[2] = -(double)l.v.z;
+      for (int k = 0; k < 3; ++k) { f.ax[k] = AX[k]; f.ay[k] = AY[k]; }
+      f.g11 = region::dot3(AX, AX); f.g12 = region::dot3(AX, AY); f.g22 = region::dot3(AY, AY);
+      f.smax = diag; f.Pmax = pmax;
+      lb.dom[0] = lb.dom[2] = 1e300; lb.dom[1] = lb.dom[3] = -1e300;
+      for (int c = 0; c < 8; ++c) {
+        const double X[3] = {(c & 1) ? hi[0] : lo[0], (c & 2) ? hi[1] : lo[1], (c & 4) ? hi[2] : lo[2]};
+        const double x = region::dot3(X, AX), y = region::dot3(X, AY);
+        lb.dom[0] = fmin(lb.dom[0], x); lb.dom[1] = fmax(lb.dom[1], x); lb.dom[2] = fmin(lb.dom[2], y); lb.dom[3] = fmax(lb.dom[3], y);
+      }
+      const double m = 1e-3 * ((lb.dom[1] - lb.dom[0]) + (lb.dom[3] - lb.dom[2])) + 1e-30;
+      lb.dom[0] -= m; lb.dom[1] += m; lb.dom[2] -= m; lb.dom[3] += m;
+    } else {
+      region::PointFrame &f = lb.pf;
+      f.org[0] = l.v.x; f.org[1] = l.v.y; f.org[2] = l.v.z;
+      // dual basis of (ax, ay, az): rows of the inverse of the matrix whose rows are the axes
+      const double M[3][3] = {{AX[0], AX[1], AX[2]}, {AY[0], AY[1], AY[2]}, {AZ[0], AZ[1], AZ[2]}};
+      double c0[3], c1[3], c2[3];
+      region::cross3(M[1], M[2], c0); region::cross3(M[2], M[0], c1); region::cross3(M[0], M[1], c2);
+      const double det = region::dot3(M[0], c0);
+      if (!(fabs(det) > 0.5)) continue;
+      for (int k = 0; k < 3; ++k) { f.hx[k] = c0[k] / det; f.hy[k] = c1[k] / det; f.hz[k] = c2[k] / det; }
+      double far2 = 0;
+      for (int k = 0; k < 3; ++k) { const double m = fmax(fabs(f.org[k] - lo[k]), fabs(f.org[k] - hi[k])); far2 += m * m; }
+      f.smax = diag; f.dmax = sqrt(far2) * (1.0 + 1e-6);
+      const double lim = (double)LG_PERSP_LIMIT * (1.0 + 1e-3);
+      f.ratio = sqrt(1.0 + 2.0 * lim * lim) * 1.001;
+      lb.dom[0] = lb.dom[2] = -lim; lb.dom[1] = lb.dom[3] = lim;
+    }
+    LgScratch tmp;
+    tmp.st = st;
+    float4 *rec = nullptr;
     uint32_t *d_b = nullptr;
-    RTB_CUDA(cudaMallocAsync((void **)&d_b, 32 * 4, st));
+    { int rc = tmp.alloc(&rec, (size_t)n * 4 * sizeof(float4)); if (rc) return rc; }
+    { int rc = tmp.alloc(&d_b, ((size_t)LG_STATE_WORDS + LG_BIG_CAP) * 4); if (rc) return rc; }
+    k_lg_records<<<(n + 127) / 128, 128, 0, st>>>(sc, g, lb, rec);
+    // extent of the grid: the boxes of every 16th triangle from 2^20 on (slots are in spatial order: a regular
+    // sample of the surface); regions that span more than a quarter of the domain are lines, not geometry
     const uint32_t init[4] = {0xffffffffu, 0u, 0xffffffffu, 0u};
     uint32_t hb[4];
     RTB_CUDA(cudaMemcpyAsync(d_b, init, sizeof init, cudaMemcpyHostToDevice, st));
-    // every 16th triangle from 2^20 on (slots are in spatial order: a regular sample of the surface)
     const uint32_t bstride = n >= (1u << 20) ? 16u : 1u;
-    k_lg_bounds<<<(n / bstride + 256) / 256, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, bstride, d_b);
+    const float huge = (float)(0.25 * fmax(lb.dom[1] - lb.dom[0], lb.dom[3] - lb.dom[2]));
+    k_lg_bounds<<<(n / bstride + 256) / 256, 256, 0, st>>>(rec, n, bstride, huge, d_b);
     RTB_CUDA(cudaMemcpyAsync(hb, d_b, sizeof hb, cudaMemcpyDeviceToHost, st));
     RTB_CUDA(cudaStreamSynchronize(st));
     float x0 = ord2f(hb[0]), x1 = ord2f(hb[1]), y0 = ord2f(hb[2]), y1 = ord2f(hb[3]);
@@ -548,57 +631,46 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
       const float mx = 0.01f * (x1 - x0), my = 0.01f * (y1 - y0);
       x0 -= mx; x1 += mx; y0 -= my; y1 += my;
     }
-    if (g.kind == 2) {
-      x0 = fmaxf(x0, -LG_PERSP_LIMIT); y0 = fmaxf(y0, -LG_PERSP_LIMIT);
-      x1 = fminf(x1, LG_PERSP_LIMIT); y1 = fminf(y1, LG_PERSP_LIMIT);
-    }
-    if (!(x1 > x0) || !(y1 > y0) || !(x1 - x0 < 1e30f) || !(y1 - y0 < 1e30f)) { cudaFreeAsync(d_b, st); continue; }
-    // about one cell per triangle: with rectangles from the accept regions a triangle of average
-    // size touches ~6 cells, and a ray scans ~6 entries (C5: 0.5 -> 17.5 ms, 1 -> 17.05, 2 -> 16.8 at twice the memory)
+    x0 = fmaxf(x0, (float)lb.dom[0]); y0 = fmaxf(y0, (float)lb.dom[2]);
+    x1 = fminf(x1, (float)lb.dom[1]); y1 = fminf(y1, (float)lb.dom[3]);
+    if (!(x1 > x0) || !(y1 > y0) || !(x1 - x0 < 1e30f) || !(y1 - y0 < 1e30f)) continue;
+    // about one cell per triangle: a triangle of average size touches ~6 cells, and a ray scans ~6 entries
+    // (C5: 0.5 -> 17.5 ms, 1 -> 17.05, 2 -> 16.8 at twice the memory)
     static const double cells_per_tri = [] { const char *e = getenv("RTB_LG_CELLS"); return e && atof(e) > 0 ? atof(e) : 1.0; }();
     const double target = fmin(fmax(cells_per_tri * (double)n, 1024.0), 64.0e6);
     double cell = sqrt((double)(x1 - x0) * (double)(y1 - y0) / target);
     cell = fmax(cell, fmax((double)(x1 - x0), (double)(y1 - y0)) / 30000.0);
-    g.x0 = x0; g.y0 = y0; g.inv_cell = (float)(1.0 / cell);
+    g.x0 = x0; g.y0 = y0; g.cell = (float)cell; g.inv_cell = 1.0f / g.cell;
     g.nx = (int)ceil((x1 - x0) / cell) + 1; g.ny = (int)ceil((y1 - y0) / cell) + 1;
     const size_t cells = (size_t)g.nx * g.ny;
     uint32_t *counts = nullptr, *cursor = nullptr, *scratch = nullptr;
     uint2 *entries = nullptr;
     const size_t ssw = scan_scratch_words(cells + 1);
-    RTB_CUDA(cudaMallocAsync((void **)&counts, (cells + 1) * 4, st));
-    RTB_CUDA(cudaMallocAsync((void **)&scratch, ssw * 4, st));
+    { int rc = tmp.alloc(&counts, (cells + 1) * 4); if (rc) return rc; }
+    { int rc = tmp.alloc(&scratch, ssw * 4); if (rc) return rc; }
     RTB_CUDA(cudaMemsetAsync(counts, 0, (cells + 1) * 4, st));
-    RTB_CUDA(cudaMemsetAsync(d_b, 0, 32 * 4, st));
-    k_lg_scatter<false><<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, counts, d_b, nullptr, nullptr);
+    RTB_CUDA(cudaMemsetAsync(d_b, 0, LG_STATE_WORDS * 4, st));
+    k_lg_scatter<false><<<blocks, 256, 0, st>>>(sc, g, rec, counts, d_b, nullptr, nullptr);
+    k_lg_big<false><<<S.sm_count * 8, 128, 0, st>>>(sc, g, rec, counts, d_b, nullptr, nullptr);
     int rc = dev_exclusive_scan_u32(counts, cells + 1, scratch, ssw, false, st, nullptr);
+    if (rc) return rc;
     uint32_t total = 0, state[2 + LG_LARGE_MAX];
-    if (!rc) {
-      RTB_CUDA(cudaMemcpyAsync(&total, counts + cells, 4, cudaMemcpyDeviceToHost, st));
-      RTB_CUDA(cudaMemcpyAsync(state, d_b, sizeof state, cudaMemcpyDeviceToHost, st));
-      RTB_CUDA(cudaStreamSynchronize(st));
-    }
-    cudaFreeAsync(scratch, st);
-    const bool ok = !rc && !state[1] && (size_t)total <= 24ull * n + (1u << 20) && total > 0;
-    if (!ok) { cudaFreeAsync(counts, st); cudaFreeAsync(d_b, st); if (rc) return rc; continue; }
-    RTB_CUDA(cudaMallocAsync((void **)&entries, (size_t)total * sizeof(uint2), st));
-    RTB_CUDA(cudaMallocAsync((void **)&cursor, cells * 4, st));
+    RTB_CUDA(cudaMemcpyAsync(&total, counts + cells, 4, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaMemcpyAsync(state, d_b, sizeof state, cudaMemcpyDeviceToHost, st));
+    RTB_CUDA(cudaStreamSynchronize(st));
+    const bool ok = !state[1] && (size_t)total <= 24ull * n + (1u << 20) && total > 0;
+    if (!ok) continue;
+    { int rc2 = tmp.alloc(&entries, (size_t)total * sizeof(uint2)); if (rc2) return rc2; }
+    { int rc2 = tmp.alloc(&cursor, cells * 4); if (rc2) return rc2; }
     RTB_CUDA(cudaMemsetAsync(cursor, 0, cells * 4, st));
-    k_lg_scatter<true><<<blocks, 256, 0, st>>>(sc, g, eps, lg_records ? diag : 0.0f, cursor, d_b, counts, entries);
+    k_lg_scatter<true><<<blocks, 256, 0, st>>>(sc, g, rec, cursor, d_b, counts, entries);
+    k_lg_big<true><<<S.sm_count * 8, 128, 0, st>>>(sc, g, rec, cursor, d_b, counts, entries);
     RTB_CUDA(cudaGetLastError());
-    cudaFreeAsync(cursor, st);
-    cudaFreeAsync(d_b, st);
-    g.cell_start = counts; g.entries = entries;
-    if (lg_records) {
-      float4 *rec = nullptr;
-      RTB_CUDA(cudaMallocAsync((void **)&rec, (size_t)n * 3 * sizeof(float4), st));
-      k_lg_records<<<blocks, 256, 0, st>>>(sc, g, diag, rec);
-      RTB_CUDA(cudaGetLastError());
-      g.rec = rec;
-      S.lgrid_mem[mem++] = rec;
-    }
+    g.cell_start = counts; g.entries = entries; g.rec = rec;
+    tmp.keep(counts); tmp.keep(entries); tmp.keep(rec);
     g.n_large = state[0] < (uint32_t)LG_LARGE_MAX ? state[0] : (uint32_t)LG_LARGE_MAX;
     for (uint32_t k = 0; k < g.n_large; ++k) g.large[k] = state[2 + k];
-    S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
+    S.lgrid_mem[mem++] = rec; S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
     S.lgrid_entries += total; S.lgrid_cells += cells;
     grids[i] = g;
     ++built;

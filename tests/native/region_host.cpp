@@ -88,6 +88,16 @@ void rg_span(const float *rec, const float *dx0, const int32_t *w, const float *
   }
 }
 
+// record_band for n records / bands: out ok, lo, hi
+void rg_band(const float *rec, const float *dy0, const float *dy1, const float *xext, int n, int32_t *ok, float *lohi) {
+  for (int i = 0; i < n; ++i) {
+    const float *r = rec + 12 * i;
+    float lo, hi;
+    ok[i] = record_band(r[0], r[1], r[2], r[3], r[4], r[5], r[6], r[7], r[8], r[11], dy0[i], dy1[i], xext[i], lo, hi) ? 1 : 0;
+    lohi[2 * i] = lo; lohi[2 * i + 1] = hi;
+  }
+}
+
 // row_range / box_touches of the primary region of one triangle (tile emission logic)
 int rg_primary_rows(const double *cam, int W, int H, const float *tri, int tile, int32_t *rows, int max_rows) {
   CamFrame cf;

@@ -43,6 +43,7 @@ def rg():
     L.rg_primary_rows.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, vp, C.c_int]
     L.rg_primary_rows.restype = C.c_int
     L.rg_span.argtypes = [vp, vp, vp, vp, C.c_int, vp]
+    L.rg_band.argtypes = [vp, vp, vp, vp, C.c_int, vp, vp]
     return L
 
 
@@ -324,6 +325,38 @@ def test_row_spans_hold_every_sample_the_record_passes(rg):
                     assert not (ins & ~inspan).any(), (t, j, ab[j], np.where(ins)[0])
                     checked += w; passing += int(ins.sum())
     assert checked > 100000 and passing > 10000, (checked, passing)
+
+
+def test_bands_hold_every_point_the_record_passes(rg):
+    """record_band (the light grids list a region's cells with it) is a superset of record_inside"""
+    rng = np.random.default_rng(23)
+    inside_total = 0
+    for W, H, fov in ((160, 100, 0.7), (96, 64, 60.0)):
+        cam = make_camera(rng, W, H, fov)
+        for gen in (tris_on_screen, tris_grazing, tris_around_camera, tris_needles):
+            tri = gen(rng, cam, 50)
+            out, rec = cull(rg, cam, tri)
+            for t in np.where(out[:, 0] > 0)[0]:
+                kind, x0, y0, x1, y1 = (int(v) for v in out[t])
+                nb = 12
+                edges = np.sort(rng.uniform(-3.0, (y1 - y0) + 3.0, nb + 1)).astype(f32)
+                dy0, dy1 = edges[:-1].copy(), edges[1:].copy()
+                xext = np.full(nb, float(x1 - x0) + 8.0, f32)
+                r = np.broadcast_to(rec[t], (nb, 12)).copy()
+                ok = np.zeros(nb, np.int32); lohi = np.zeros((nb, 2), f32)
+                rg.rg_band(r.ctypes.data, dy0.ctypes.data, dy1.ctypes.data, xext.ctypes.data, nb, ok.ctypes.data, lohi.ctypes.data)
+                # dense points of every band
+                for j in range(nb):
+                    xs = rng.uniform(-4.0, (x1 - x0) + 4.0, 400).astype(f32)
+                    ys = rng.uniform(dy0[j], dy1[j], 400).astype(f32)
+                    ys = np.clip(ys, dy0[j], dy1[j])
+                    ins = record_inside(np.broadcast_to(rec[t], (400, 12)), xs, ys)
+                    if not ok[j]:
+                        assert not ins.any(), (t, j)
+                    else:
+                        assert ((xs[ins] >= lohi[j, 0]) & (xs[ins] <= lohi[j, 1])).all(), (t, j, lohi[j])
+                    inside_total += int(ins.sum())
+    assert inside_total > 20000, inside_total
 
 
 # ---- shadow rays ----
