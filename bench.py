@@ -295,6 +295,31 @@ def run_ours(args):
             hb = (C.c_ubyte * 64)(*handle.cpu().tolist())
             pyrtb._check(L.rtb_ipc_open(hb, C.byref(d_frame)))
 
+    # Sharded projection pass (rtb_scene_exchange_*): every rank projects 1/N of the triangles and stores the
+    # items straight into the owners' inboxes through CUDA-IPC mappings of the peers' exchange blocks (NVLink
+    # stores inside the kernel, device-side epoch barrier) -- the path's one real exchange step, no collective.
+    peer_blocks = []
+    if world > 1 and not args.replicated_setup:
+        import torch
+        blk, blk_bytes = ds.exchange_create(world)
+        hb = (C.c_ubyte * 64)()
+        pyrtb._check(L.rtb_ipc_export(C.c_void_p(blk), hb))
+        mine = torch.tensor(list(hb), dtype=torch.uint8, device="cuda")
+        allh = [torch.zeros(64, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(allh, mine)
+        blocks = []
+        for q in range(world):
+            if q == rank:
+                blocks.append(blk)
+                continue
+            p = C.c_void_p()
+            hq = (C.c_ubyte * 64)(*allh[q].cpu().tolist())
+            pyrtb._check(L.rtb_ipc_open(hq, C.byref(p)))
+            peer_blocks.append(p)
+            blocks.append(p.value)
+        ds.exchange_attach(rank, world, blocks)
+        barrier()
+
     def frame(count=False):
         ds.render_device(d_frame, pitch, rank=rank, nranks=world, count=count)
 
@@ -554,7 +579,10 @@ def run_ours(args):
                        "camera": "fly-through: one new camera per timed frame (0.25 units forward + 0.1 sideways per frame, "
                                  "rtb_scene_set_camera); rays counted per camera in untimed frames",
                        "parallelism": "interleaved 32x32-pixel tiles over %d GPU(s), scene replicated, tiles stored "
-                                      "into rank 0's frame over NVLink" % world,
+                                      "into rank 0's frame over NVLink%s" % (world, "" if world == 1 else (
+                                          "; projection pass replicated on every rank" if args.replicated_setup else
+                                          "; projection pass sharded by triangles, items stored into the owners' inboxes over NVLink "
+                                          "(CUDA IPC), device-side epoch barrier")),
                        "l2": "inputs larger than L2 (triangles 960 MB + nodes %d MB vs 126 MB L2)" % (st0["tree_bytes"] >> 20),
                        "rays_per_frame": {"primary": primary, "shadow": shadow, "bounce": bounce}},
             "e2e": e2e, "gpu_launches": args.steps * launches_per_frame, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
@@ -567,6 +595,11 @@ def run_ours(args):
         print(json.dumps(out), file=_JSON_OUT, flush=True)
     barrier()
     pinned.free()
+    ds.sync()
+    barrier()
+    for p in peer_blocks:
+        L.rtb_ipc_close(p)
+    barrier()
     ds.close()
     if dist is not None:
         dist.destroy_process_group()
@@ -581,6 +614,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--ref-samples", type=int, default=0, help="CPU samples per step (default: one per host thread x4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--replicated-setup", action="store_true",
+                    help="N > 1: every rank projects all triangles (round 1's path) instead of the sharded pass with item exchange")
     ap.add_argument("--no-ref-gpu", action="store_true", help="skip the C1-C4 block (ours and the reference's GPU renderer)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

@@ -209,6 +209,20 @@ typedef struct rtb_stats {
 
 int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out);
 
+/* Sharded projection pass of multi-rank frames (no reference counterpart: the reference is
+ * single-GPU).  By default every rank of a frame projects ALL triangles to find the items of its own tiles.
+ * With an exchange attached, rank r projects only the triangles [r T / N, (r + 1) T / N) and stores each item
+ * straight into the inbox of the rank that owns its tile -- peer-mapped device memory (NVLink stores inside the
+ * projection kernel, no collective), followed by a device-side epoch barrier.  Protocol: every rank calls
+ * rtb_scene_exchange_create (allocates its block: control words + inbox), the blocks' addresses are made
+ * visible to the other ranks (rtb_ipc_export / rtb_ipc_open between processes; the plain pointers inside one
+ * process with peer access), then rtb_scene_exchange_attach(blocks[0..N-1], own entry ignored).  From then on
+ * rtb_scene_render_device with this (rank, nranks) runs sharded; ALL ranks must render the same sequence of
+ * such frames (the barrier counts them), each on its own stream / process.  A rank that does not show up
+ * within ~3 s makes the others fall back to the tree walk for that frame (same pixels, slower). */
+int rtb_scene_exchange_create(rtb_scene_t *h, int nranks, void **d_block, size_t *bytes);
+int rtb_scene_exchange_attach(rtb_scene_t *h, int rank, int nranks, void *const *blocks);
+
 /* Measurement aid (bench.py): with profiling on, every frame records CUDA events between its
  * kernels; rtb_scene_kernel_ms waits for the last frame and returns out[0] clears + k_rast_setup,
  * out[1] k_rast_items, out[2] the frame kernel, out[3] the whole frame, in milliseconds. */

@@ -127,10 +127,12 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   if (S.d_rast_cap < cap) {
     if (S.d_rast_items) cudaFreeAsync(S.d_rast_items, st);
     S.d_rast_items = nullptr; S.d_rast_cap = 0;
-    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, (cap + 3 * (size_t)S.n_tris) * sizeof(uint4), st));   // items, then edge records
+    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, cap * sizeof(RastItem), st));
     S.d_rast_cap = cap;
   }
-  if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, (RAST_STATE_WORDS + (1u << 16)) * 4, st));   // state words, then the big list
+  // state words, the big list, the big list's regions
+  constexpr size_t big_off = ((RAST_STATE_WORDS + (1u << 16)) * 4 + 255) & ~(size_t)255;
+  if (!S.d_rast) RTB_CUDA(cudaMallocAsync((void **)&S.d_rast, big_off + (size_t)(1u << 16) * sizeof(region::PrimaryCull), st));
   // the camera in double precision and the rounding scales of this frame's rays (region::CamFrame)
   {
     region::CamFrame &cf = fa.camf;
@@ -160,11 +162,13 @@ static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st
   fa.rast_area_factor = area_factor;
   S.rast_area_factor = area_factor;
   fa.prim = S.d_prim;
-  fa.rast_items = S.d_rast_items;
-  fa.rast_rec = reinterpret_cast<float4 *>(S.d_rast_items + S.d_rast_cap);
-  fa.rast_cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
+  memset(&fa.x, 0, sizeof fa.x);
+  fa.x.cap = (unsigned)(S.d_rast_cap > 0xfffffff0ull ? 0xfffffff0ull : S.d_rast_cap);
+  fa.x.seg[0] = S.d_rast_items;
+  fa.x.in[0] = S.d_rast_items;
   fa.rast = S.d_rast;
   fa.rast_big = S.d_rast + RAST_STATE_WORDS;
+  fa.rast_big_cull = reinterpret_cast<region::PrimaryCull *>(reinterpret_cast<unsigned char *>(S.d_rast) + big_off);
   return RTB_OK;
 }
 
@@ -194,7 +198,8 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   fa.bounce_scratch = nullptr;
   fa.n_shadow_lights = S.n_shadow_lights;
   memcpy(fa.shadow_light, S.shadow_light, sizeof fa.shadow_light);
-  fa.prim = nullptr; fa.rast_items = nullptr; fa.rast_rec = nullptr; fa.rast = nullptr; fa.rast_big = nullptr; fa.rast_cap = 0; fa.rast_area_factor = 0;
+  fa.prim = nullptr; fa.rast = nullptr; fa.rast_big = nullptr; fa.rast_big_cull = nullptr; fa.rast_area_factor = 0;
+  memset(&fa.x, 0, sizeof fa.x);
   // Primary visibility by projection (raster.cuh): big scenes by default, any scene on request.
   // The frame falls back to the tree by itself when the projection does not pay or is not defined.
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
@@ -210,6 +215,21 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
       if (rc) return rc;
       memcpy(S.rast_key, key, sizeof key);
       S.rast_useless = false;
+      // Sharded projection pass: the ranks of this frame are attached to each other's exchange blocks
+      // (rtb_scene_exchange_attach).  Every rank must take this branch on the same frames: the epoch counts them.
+      if (o.nranks > 1 && S.xchg_block && S.xchg_nranks == o.nranks && S.xchg_rank == o.rank) {
+        const int N = o.nranks;
+        fa.x.sharded = 1;
+        S.rast_key[3] = 1;            // finish_frame: the area the frame left is the whole frame's (k_xchg_sync)
+        fa.x.cap = S.xchg_cap;
+        fa.x.epoch = ++S.xchg_epoch;
+        const size_t p = fa.x.epoch & 1u;
+        for (int q = 0; q < N; ++q) {
+          fa.x.ctl[q] = reinterpret_cast<unsigned *>(S.xchg_peer[q]);
+          fa.x.seg[q] = reinterpret_cast<RastItem *>(S.xchg_peer[q] + XCHG_CTL_WORDS * 4) + (p * N + (size_t)o.rank) * S.xchg_cap;
+          fa.x.in[q] = reinterpret_cast<const RastItem *>(S.xchg_block + XCHG_CTL_WORDS * 4) + (p * N + (size_t)q) * S.xchg_cap;
+        }
+      }
     }
   }
   if (o.frame_kernel == RTB_KERNEL_WAVEFRONT && o.tracer == RTB_TRACER_TREE && o.aliasing <= WAVE_MAX_ALIASING && S.n_shadow_lights <= 32 &&
@@ -296,7 +316,8 @@ static int finish_frame(SceneStore &S, cudaStream_t st) {
   if (S.rast_pending) {
     S.rast_pending = false;
     const unsigned long long area = (unsigned long long)S.h_rast[2] | ((unsigned long long)S.h_rast[3] << 32);
-    const unsigned long long samples = (S.rast_key[1] >> 32) * (S.rast_key[1] & 0xffffffffull) / ((S.rast_key[2] & 0xffffffffull) ? (S.rast_key[2] & 0xffffffffull) : 1ull);
+    const unsigned long long ranks = S.rast_key[3] ? 1ull : ((S.rast_key[2] & 0xffffffffull) ? (S.rast_key[2] & 0xffffffffull) : 1ull);
+    const unsigned long long samples = (S.rast_key[1] >> 32) * (S.rast_key[1] & 0xffffffffull) / ranks;      // as rast_active() counts
     S.rast_useless = S.h_rast[1] != 0 || area > (unsigned long long)S.rast_area_factor * samples + 65536ull;
   }
   float ms = 0;
@@ -691,6 +712,45 @@ int rtb_scene_stats(rtb_scene_t *h, rtb_stats *out) {
   return RTB_OK;
 }
 
+// ---- item exchange of sharded multi-rank frames (raster.cuh) ----
+int rtb_scene_exchange_create(rtb_scene_t *h, int nranks, void **d_block, size_t *bytes) {
+  if (!h || !d_block) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  if (nranks < 2 || nranks > XCHG_MAX_RANKS) { set_error("exchange: %d ranks not in 2..%d", nranks, XCHG_MAX_RANKS); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  RTB_CUDA(cudaSetDevice(S.device));
+  if (S.xchg_block) { cudaFree(S.xchg_block); S.xchg_block = nullptr; S.xchg_nranks = 0; S.xchg_rank = -1; }
+  // a pair (source, destination) sees 1 / N^2 of the frame's items on average (tiles interleave over the
+  // ranks, triangle shares are compact): four times that, but never more than the whole list
+  const size_t all = 2 * (size_t)S.n_tris + (4u << 20);
+  size_t cap = 4 * all / ((size_t)nranks * nranks) + 65536;
+  if (cap > all) cap = all;
+  const size_t total = (size_t)XCHG_CTL_WORDS * 4 + 2 * (size_t)nranks * cap * sizeof(RastItem);
+  RTB_CUDA(cudaMalloc((void **)&S.xchg_block, total));          // cudaMalloc, not the pool: the block is exported over CUDA IPC
+  RTB_CUDA(cudaMemset(S.xchg_block, 0, (size_t)XCHG_CTL_WORDS * 4));
+  RTB_CUDA(cudaDeviceSynchronize());
+  S.xchg_bytes = total;
+  S.xchg_cap = (unsigned)cap;
+  S.xchg_epoch = 0;
+  *d_block = S.xchg_block;
+  if (bytes) *bytes = total;
+  return RTB_OK;
+}
+
+int rtb_scene_exchange_attach(rtb_scene_t *h, int rank, int nranks, void *const *blocks) {
+  if (!h || !blocks) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  SceneStore &S = h->store;
+  if (!S.xchg_block) { set_error("exchange: rtb_scene_exchange_create first"); return RTB_ERR_ARG; }
+  if (nranks < 2 || nranks > XCHG_MAX_RANKS || rank < 0 || rank >= nranks) { set_error("exchange: rank %d of %d", rank, nranks); return RTB_ERR_ARG; }
+  for (int q = 0; q < nranks; ++q) {
+    if (q != rank && !blocks[q]) { set_error("exchange: block of rank %d is NULL", q); return RTB_ERR_ARG; }
+    S.xchg_peer[q] = q == rank ? S.xchg_block : (unsigned char *)blocks[q];
+  }
+  S.xchg_nranks = nranks;
+  S.xchg_rank = rank;
+  S.xchg_epoch = 0;
+  return RTB_OK;
+}
+
 int rtb_scene_profile(rtb_scene_t *h, int on) {
   if (!h) { set_error("NULL argument"); return RTB_ERR_ARG; }
   h->store.profile = on != 0;
@@ -723,8 +783,12 @@ int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]) {
   memcpy(out + 5, grids, sizeof grids);
   if (!S.d_rast) return RTB_OK;
   RTB_CUDA(cudaSetDevice(S.device));
-  RTB_CUDA(cudaMemcpyAsync(out, S.d_rast, 5 * sizeof(unsigned), cudaMemcpyDeviceToHost, S.stream));
+  unsigned st16[16];
+  RTB_CUDA(cudaMemcpyAsync(st16, S.d_rast, sizeof st16, cudaMemcpyDeviceToHost, S.stream));
   RTB_CUDA(cudaStreamSynchronize(S.stream));
+  memcpy(out, st16, 5 * sizeof(unsigned));
+  out[0] = 0;
+  for (int q = 0; q < XCHG_MAX_RANKS; ++q) out[0] += st16[8 + q];      // items this rank wrote (for every destination)
   return RTB_OK;
 }
 

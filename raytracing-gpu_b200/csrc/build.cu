@@ -803,6 +803,7 @@ void SceneStore::release() {
   order = nullptr; up = nullptr; inv_order = nullptr;
   d_prim = nullptr; d_rast_items = nullptr; d_rast = nullptr; d_prim_count = 0; d_rast_cap = 0;
   if (h_rast) { cudaFreeHost(h_rast); h_rast = nullptr; }
+  if (xchg_block) { cudaStreamSynchronize(stream); cudaFree(xchg_block); xchg_block = nullptr; xchg_nranks = 0; xchg_rank = -1; }
   rast_pending = false; rast_useless = false;
   d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);

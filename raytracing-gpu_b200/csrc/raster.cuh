@@ -28,8 +28,9 @@ namespace {
 
 constexpr int RAST_TILE = 32;                 // samples
 constexpr unsigned RAST_TILES_MAX = 1u << 17;  // per triangle (a 4K x 3 frame has 73 000 tiles)
-// rast[] words: 0 item count, 1 fallback flag, 2-3 samples the items cover (u64), 4 triangles with two
-// regions, 5 triangles on the big list
+// rast[] words: 0 -, 1 fallback flag, 2-3 samples the items cover (u64), 4 triangles with two regions,
+// 5 triangles on the big list, 6 exchange timed out, 8..15 items written for destination rank q (8: the
+// only segment when the frame is not sharded)
 constexpr int RAST_WORDS = 8;
 constexpr unsigned RAST_BIG_TILES = 128;       // a rectangle over more tiles goes to k_rast_big (one CTA per triangle)
 constexpr unsigned RAST_BIG_CAP = 1u << 16;    // slots on that list; the rest is emitted by its own thread
@@ -39,7 +40,7 @@ __device__ __forceinline__ bool rast_active(const FrameArgs &fa) {
   const unsigned *r = fa.rast;
   if (r[1]) return false;
   const unsigned long long area = *reinterpret_cast<const unsigned long long *>(r + 2);
-  const unsigned long long samples = (unsigned long long)fa.cam.W * (unsigned long long)fa.cam.H / (unsigned)fa.nranks;
+  const unsigned long long samples = (unsigned long long)fa.cam.W * (unsigned long long)fa.cam.H / (unsigned)(fa.x.sharded ? 1 : fa.nranks);
   return area <= (unsigned long long)fa.rast_area_factor * samples + 65536ull;
 }
 
@@ -51,6 +52,44 @@ __device__ __forceinline__ bool rast_owned(const FrameArgs &fa, int tx, int ty) 
   return (Tx + 3 * Ty) % fa.nranks == fa.rank;
 }
 
+// destination segment of sample tile (tx, ty): the owning rank when the frame is sharded, else segment 0
+// (only owned tiles are emitted then); -1: not emitted by this rank
+__device__ __forceinline__ int rast_dest(const FrameArgs &fa, int tx, int ty) {
+  if (fa.nranks == 1) return 0;
+  const int per = RANK_TILE * fa.aliasing / RAST_TILE;
+  const int owner = (tx / per + 3 * (ty / per)) % fa.nranks;
+  if (fa.x.sharded) return owner;
+  return owner == fa.rank ? 0 : -1;
+}
+
+__device__ __forceinline__ void rast_store(const FrameArgs &fa, int q, unsigned k, uint32_t s, int x0, int y0, int x1, int y1,
+                                           const float *rv) {
+  RastItem *it = fa.x.seg[q] + k;
+  it->hdr = make_uint4(s, (unsigned)x0 | ((unsigned)y0 << 16), (unsigned)x1 | ((unsigned)y1 << 16), 0u);
+  it->r0 = make_float4(rv[0], rv[1], rv[2], rv[3]);
+  it->r1 = make_float4(rv[4], rv[5], rv[6], rv[7]);
+  it->r2 = make_float4(rv[8], rv[9], rv[10], rv[11]);
+}
+
+// prim[] = ~0 ("no candidate") on the tiles this rank owns: a multi-rank frame never touches the rest
+// (one warp per 32 x 32-sample tile row segment; a single rank uses cudaMemsetAsync on the whole array)
+__global__ void __launch_bounds__(256) k_prim_clear(const FrameArgs fa) {
+  const int tiles_x = (fa.cam.W + RAST_TILE - 1) / RAST_TILE, tiles_y = (fa.cam.H + RAST_TILE - 1) / RAST_TILE;
+  const int lane = threadIdx.x & 31;
+  const long long warps = (long long)gridDim.x * 8, w0 = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int per = RANK_TILE * fa.aliasing / RAST_TILE;
+  for (long long t = w0; t < (long long)tiles_x * tiles_y; t += warps) {
+    const int tx = (int)(t % tiles_x), ty = (int)(t / tiles_x);
+    if ((tx / per + 3 * (ty / per)) % fa.nranks != fa.rank) continue;
+    const int x = tx * RAST_TILE + lane;
+    if (x >= fa.cam.W) continue;
+    for (int r = 0; r < RAST_TILE; ++r) {
+      const int y = ty * RAST_TILE + r;
+      if (y < fa.cam.H) fa.prim[(size_t)y * fa.cam.W + x] = ~0ull;
+    }
+  }
+}
+
 // k_rast_setup: one thread per triangle slot.  Region of the screen where the rounded test can
 // accept (region::primary_cull, double precision: ~150 flops per triangle, the kernel is bound by
 // its gathers), the sample rectangle around it, the float edge record k_rast_items tests sample
@@ -58,12 +97,16 @@ __device__ __forceinline__ bool rast_owned(const FrameArgs &fa, int tx, int ty) 
 // tile, else one per 32 x 32-sample tile the region can touch (region::row_range per tile row, so a
 // long thin region costs its length, not its bounding box).
 __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const FrameArgs fa) {
-  const uint32_t s = blockIdx.x * 256 + threadIdx.x;
+  // sharded frames: this rank's share of the triangle slots (slots are in spatial order, so a share is a
+  // compact part of the scene whose items spread over all ranks' interleaved tiles)
+  const uint32_t t0 = fa.x.sharded ? (uint32_t)((uint64_t)sc.n_tris * (unsigned)fa.rank / (unsigned)fa.nranks) : 0u;
+  const uint32_t t1 = fa.x.sharded ? (uint32_t)((uint64_t)sc.n_tris * ((unsigned)fa.rank + 1u) / (unsigned)fa.nranks) : sc.n_tris;
+  const uint32_t s = t0 + blockIdx.x * 256 + threadIdx.x;
   const int lane = threadIdx.x & 31;
   unsigned *rast = fa.rast;
   region::PrimaryCull c;
   c.kind = 0;
-  if (s < sc.n_tris) {
+  if (s < t1) {
     const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
     const float v0[3] = {a4.x, a4.y, a4.z}, e1[3] = {b4.x, b4.y, b4.z}, e2[3] = {c4.x, c4.y, c4.z};
     region::primary_cull(fa.camf, fa.cam.W, fa.cam.H, v0, e1, e2, c);
@@ -71,30 +114,46 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
   const bool any = c.kind != 0;
   const int x0 = c.x0, y0 = c.y0, x1 = c.x1, y1 = c.y1;
   const int ty0 = any ? y0 / RAST_TILE : 0, ty1 = any ? y1 / RAST_TILE : -1;
-  unsigned mine = 0, area = 0, big_k = 0;
+  const int nd = fa.x.sharded ? fa.nranks : 1;                              // destination segments
+  unsigned cnt[XCHG_MAX_RANKS];                                             // items of this triangle per destination
+#pragma unroll
+  for (int q = 0; q < XCHG_MAX_RANKS; ++q) cnt[q] = 0;
+  unsigned mine = 0, touched = 0, area = 0, big_k = 0;
   const int rt = fa.nranks == 1 ? (1 << 30) : RANK_TILE * fa.aliasing;      // rank tile edge in samples
   const bool single = any && x1 - x0 < RAST_TILE && y1 - y0 < RAST_TILE && x0 / rt == x1 / rt && y0 / rt == y1 / rt;
   const bool gave_up = *reinterpret_cast<volatile unsigned *>(rast + 1) != 0;     // the frame has given up: emit nothing more
   if (single) {
-    if (!gave_up && rast_owned(fa, x0 / RAST_TILE, y0 / RAST_TILE)) {
+    const int q = gave_up ? -1 : rast_dest(fa, x0 / RAST_TILE, y0 / RAST_TILE);
+    if (q >= 0) {
+#pragma unroll
+      for (int k = 0; k < XCHG_MAX_RANKS; ++k) cnt[k] = k == q ? 1u : 0u;
       mine = 1;
       area = (unsigned)((x1 - x0 + 1) * (y1 - y0 + 1));
     }
   } else if (any && !gave_up && (unsigned)(ty1 - ty0 + 1) * (unsigned)(x1 / RAST_TILE - x0 / RAST_TILE + 1) > RAST_BIG_TILES &&
              (big_k = atomicAdd(&rast[5], 1u)) < RAST_BIG_CAP) {
     fa.rast_big[big_k] = s;                     // k_rast_big emits its items, tile rows in parallel
+    fa.rast_big_cull[big_k] = c;
   } else if (any && !gave_up) {
     // "area" = the samples k_rast_items will look at: it walks these items row by row over the
     // region's span (region::record_span), so a thin region costs its length, not its rectangle
-    unsigned touched = 0;
     for (int ty = ty0; ty <= ty1 && mine <= RAST_TILES_MAX; ++ty) {
       int ta, tb;
       if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
       touched += (unsigned)(tb - ta + 1);
-      for (int tx = ta; tx <= tb; ++tx)
-        if (rast_owned(fa, tx, ty)) ++mine;
+      for (int tx = ta; tx <= tb; ++tx) {
+        const int q = rast_dest(fa, tx, ty);
+        if (q < 0) continue;
+        ++mine;
+#pragma unroll
+        for (int k = 0; k < XCHG_MAX_RANKS; ++k) cnt[k] += k == q ? 1u : 0u;
+      }
     }
-    if (mine > RAST_TILES_MAX) { rast[1] = 1u; mine = 0; }
+    if (mine > RAST_TILES_MAX) {
+      rast[1] = 1u; mine = 0;
+#pragma unroll
+      for (int k = 0; k < XCHG_MAX_RANKS; ++k) cnt[k] = 0;
+    }
     if (mine) {
       const double rect = (double)(x1 - x0 + 1) * (double)(y1 - y0 + 1);
       const double work = fmin(c.R.work, rect) * (double)mine / (double)touched + 32.0 * (double)mine;
@@ -102,45 +161,52 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
     }
   }
   if (c.kind == 2) atomicAdd(&rast[4], 1u);
-  // one atomic per warp for the item slots and for the area
-  unsigned incl = mine;
+  // item slots: one atomic per warp and destination, and one for the area
+  unsigned pos[XCHG_MAX_RANKS];
+  bool overflow = false;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const unsigned o = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += o;
+  for (int q = 0; q < XCHG_MAX_RANKS; ++q) {
+    pos[q] = 0;
+    if (q < nd) {
+      unsigned incl = cnt[q];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+      }
+      const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
+      unsigned base = 0;
+      if (lane == 31 && total) base = atomicAdd(&rast[8 + q], total);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      pos[q] = base + incl - cnt[q];
+      if (cnt[q] && base + total > fa.x.cap) overflow = true;
+    }
   }
-  const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
   const unsigned wa = __reduce_add_sync(0xffffffffu, min(area, 1u << 26));
-  unsigned base = 0;
-  if (lane == 31) {
-    if (total) base = atomicAdd(&rast[0], total);
-    if (wa) atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)wa);
-  }
-  base = __shfl_sync(0xffffffffu, base, 31);
-  const bool listed = any && !single && !gave_up && !mine && big_k < RAST_BIG_CAP &&
-                      (unsigned)(ty1 - ty0 + 1) * (unsigned)(x1 / RAST_TILE - x0 / RAST_TILE + 1) > RAST_BIG_TILES;
-  if (!mine && !listed) return;
-  if (mine && base + total > fa.rast_cap) { rast[1] = 1u; return; }
-  const float *rv = c.rec.v;
-  fa.rast_rec[3 * (size_t)s] = make_float4(rv[0], rv[1], rv[2], rv[3]);
-  fa.rast_rec[3 * (size_t)s + 1] = make_float4(rv[4], rv[5], rv[6], rv[7]);
-  fa.rast_rec[3 * (size_t)s + 2] = make_float4(rv[8], rv[9], rv[10], rv[11]);
+  if (lane == 31 && wa) atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)wa);
   if (!mine) return;
-  unsigned k = base + incl - mine;
+  if (overflow) { rast[1] = 1u; return; }
+  const float *rv = c.rec.v;
   if (single) {
-    fa.rast_items[k] = make_uint4(s, (unsigned)x0 | ((unsigned)y0 << 16), (unsigned)x1 | ((unsigned)y1 << 16), 0u);
+#pragma unroll
+    for (int q = 0; q < XCHG_MAX_RANKS; ++q)
+      if (cnt[q]) rast_store(fa, q, pos[q], s, x0, y0, x1, y1, rv);
     return;
   }
-  const unsigned end = k + mine;
   for (int ty = ty0; ty <= ty1; ++ty) {
     int ta, tb;
     if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
     const int cy0 = max(y0, ty * RAST_TILE), cy1 = min(y1, ty * RAST_TILE + RAST_TILE - 1);
-    for (int tx = ta; tx <= tb; ++tx)
-      if (rast_owned(fa, tx, ty) && k < end) {
-        const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
-        fa.rast_items[k++] = make_uint4(s, (unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), 0u);
-      }
+    for (int tx = ta; tx <= tb; ++tx) {
+      const int q = rast_dest(fa, tx, ty);
+      if (q < 0) continue;
+      const int cx0 = max(x0, tx * RAST_TILE), cx1 = min(x1, tx * RAST_TILE + RAST_TILE - 1);
+      unsigned k = 0;
+#pragma unroll
+      for (int d = 0; d < XCHG_MAX_RANKS; ++d)
+        if (d == q) k = pos[d]++;
+      rast_store(fa, q, k, s, cx0, cy0, cx1, cy1, rv);
+    }
   }
 }
 
@@ -156,10 +222,7 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
   for (unsigned bi = blockIdx.x; bi < n_big; bi += gridDim.x) {
     if (*reinterpret_cast<volatile unsigned *>(rast + 1)) return;
     const uint32_t s = fa.rast_big[bi];
-    const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
-    const float v0[3] = {a4.x, a4.y, a4.z}, e1[3] = {b4.x, b4.y, b4.z}, e2[3] = {c4.x, c4.y, c4.z};
-    region::PrimaryCull c;
-    region::primary_cull(fa.camf, fa.cam.W, fa.cam.H, v0, e1, e2, c);       // as in k_rast_setup: same bits
+    const region::PrimaryCull &c = fa.rast_big_cull[bi];                    // as k_rast_setup computed it
     if (!c.kind) continue;
     if (threadIdx.x == 0) { s_touched = 0; s_mine = 0; }
     __syncthreads();
@@ -170,7 +233,7 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
       if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
       touched += (unsigned)(tb - ta + 1);
       if (fa.nranks == 1) mine += (unsigned)(tb - ta + 1);
-      else for (int tx = ta; tx <= tb; ++tx) mine += rast_owned(fa, tx, ty) ? 1u : 0u;
+      else for (int tx = ta; tx <= tb; ++tx) mine += rast_dest(fa, tx, ty) >= 0 ? 1u : 0u;
     }
     if (touched) atomicAdd(&s_touched, touched);
     if (mine) atomicAdd(&s_mine, mine);
@@ -184,22 +247,74 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
       const double work = fmin(c.R.work, rect) * (double)all_mine / (double)all_touched + 32.0 * (double)all_mine;
       atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)fmin(work, 1.0e15));
     }
+    const int nd = fa.x.sharded ? fa.nranks : 1;
     for (int ty = ty0 + (int)threadIdx.x; ty <= ty1; ty += RAST_BIG_THREADS) {
       int ta, tb;
       if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
-      unsigned cnt = 0;
-      if (fa.nranks == 1) cnt = (unsigned)(tb - ta + 1);
-      else for (int tx = ta; tx <= tb; ++tx) cnt += rast_owned(fa, tx, ty) ? 1u : 0u;
-      if (!cnt) continue;
-      unsigned k = atomicAdd(&rast[0], cnt);
-      if (k + cnt > fa.rast_cap) { rast[1] = 1u; continue; }
       const int cy0 = max(c.y0, ty * RAST_TILE), cy1 = min(c.y1, ty * RAST_TILE + RAST_TILE - 1);
-      for (int tx = ta; tx <= tb; ++tx)
-        if (rast_owned(fa, tx, ty)) {
-          const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
-          fa.rast_items[k++] = make_uint4(s, (unsigned)cx0 | ((unsigned)cy0 << 16), (unsigned)cx1 | ((unsigned)cy1 << 16), 0u);
-        }
+      // the row's tiles per destination: slots with one atomic per destination, then the items
+      for (int q = 0; q < nd; ++q) {
+        unsigned n = 0;
+        for (int tx = ta; tx <= tb; ++tx) n += rast_dest(fa, tx, ty) == q ? 1u : 0u;
+        if (!n) continue;
+        unsigned k = atomicAdd(&rast[8 + q], n);
+        if (k + n > fa.x.cap) { rast[1] = 1u; continue; }
+        for (int tx = ta; tx <= tb; ++tx)
+          if (rast_dest(fa, tx, ty) == q) {
+            const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
+            rast_store(fa, q, k++, s, cx0, cy0, cx1, cy1, c.rec.v);
+          }
+      }
     }
+  }
+}
+
+// k_xchg_sync (sharded frames, one warp): publish to every rank how many items this rank wrote into its
+// inbox, whether this rank gave up and its work estimate; then the epoch (release); then wait until every
+// rank has published this epoch (acquire) and fold their verdicts into the local state, so that
+// rast_active() decides alike on every rank.  The items themselves were written by k_rast_setup /
+// k_rast_big before this kernel on the same stream.
+__global__ void __launch_bounds__(32) k_xchg_sync(const FrameArgs fa) {
+  unsigned *rast = fa.rast;
+  const int lane = threadIdx.x, N = fa.nranks, p = (int)(fa.x.epoch & 1u);
+  if (lane < N) {
+    volatile unsigned *ctl = fa.x.ctl[lane];
+    const unsigned n = rast[8 + lane];
+    ctl[XCHG_COUNT + p * XCHG_MAX_RANKS + fa.rank] = min(n, fa.x.cap);
+    ctl[XCHG_GAVE + p * XCHG_MAX_RANKS + fa.rank] = (rast[1] || n > fa.x.cap) ? 1u : 0u;
+    ctl[XCHG_AREA + 2 * (p * XCHG_MAX_RANKS + fa.rank)] = rast[2];
+    ctl[XCHG_AREA + 2 * (p * XCHG_MAX_RANKS + fa.rank) + 1] = rast[3];
+    __threadfence_system();
+    ctl[XCHG_READY + fa.rank] = fa.x.epoch;
+  }
+  __syncwarp();
+  bool timed_out = false;
+  if (lane < N) {
+    volatile unsigned *mine = fa.x.ctl[fa.rank];
+    const long long t0 = clock64();
+    // epochs only grow; a rank that is a whole frame ahead has published a larger one
+    while ((int)(mine[XCHG_READY + lane] - fa.x.epoch) < 0) {
+      if (clock64() - t0 > 6000000000ll) { timed_out = true; break; }      // ~3 s: a rank died; this frame walks the tree
+      __nanosleep(200);
+    }
+    __threadfence_system();
+  }
+  const unsigned late = __ballot_sync(0xffffffffu, timed_out);
+  unsigned gave = 0;
+  unsigned long long area = 0;
+  if (lane < N) {
+    volatile unsigned *mine = fa.x.ctl[fa.rank];
+    gave = mine[XCHG_GAVE + p * XCHG_MAX_RANKS + lane];
+    area = (unsigned long long)mine[XCHG_AREA + 2 * (p * XCHG_MAX_RANKS + lane)] |
+           ((unsigned long long)mine[XCHG_AREA + 2 * (p * XCHG_MAX_RANKS + lane) + 1] << 32);
+  }
+  gave = __reduce_or_sync(0xffffffffu, gave);
+#pragma unroll
+  for (int d = 16; d; d >>= 1) area += __shfl_xor_sync(0xffffffffu, area, d);
+  if (lane == 0) {
+    if (gave || late) rast[1] = 1u;
+    if (late) rast[6] = 1u;
+    *reinterpret_cast<unsigned long long *>(rast + 2) = area;       // the whole frame's work: rast_active compares with the whole frame
   }
 }
 
@@ -232,19 +347,34 @@ __device__ __forceinline__ void rast_test(const DevScene &sc, const FrameArgs &f
 __global__ void __launch_bounds__(32 * RAST_WARPS) k_rast_items(const DevScene sc, const FrameArgs fa) {
   __shared__ uint2 queue[RAST_WARPS][64];
   if (!rast_active(fa)) return;
-  const unsigned n = min(fa.rast[0], fa.rast_cap);
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const unsigned lt = (1u << lane) - 1u;
   const unsigned warps = gridDim.x * RAST_WARPS;
   uint2 *Q = queue[wid];
   int qn = 0;                                   // warp-uniform
+  // the items of this rank: one local segment, or (sharded) one segment per source rank in this rank's inbox
+  const int n_src = fa.x.sharded ? fa.nranks : 1;
+  unsigned first[XCHG_MAX_RANKS + 1];
+  first[0] = 0;
+#pragma unroll
+  for (int q = 0; q < XCHG_MAX_RANKS; ++q) {
+    unsigned cnt = 0;
+    if (q < n_src)
+      cnt = fa.x.sharded ? fa.x.ctl[fa.rank][XCHG_COUNT + (fa.x.epoch & 1u) * XCHG_MAX_RANKS + q] : min(fa.rast[8], fa.x.cap);
+    first[q + 1] = first[q] + cnt;
+  }
+  const unsigned n = first[XCHG_MAX_RANKS];
   for (unsigned i = blockIdx.x * RAST_WARPS + wid; i < n; i += warps) {
-    const uint4 it = __ldg(fa.rast_items + i);
+    const RastItem *src = fa.x.in[0];
+    unsigned j = i;
+#pragma unroll
+    for (int q = 1; q < XCHG_MAX_RANKS; ++q)
+      if (q < n_src && i >= first[q]) { src = fa.x.in[q]; j = i - first[q]; }
+    const uint4 it = src[j].hdr;              // plain loads: a sharded frame's items were written by peers
     const int x0 = (int)(it.y & 0xffffu), y0 = (int)(it.y >> 16), x1 = (int)(it.z & 0xffffu), y1 = (int)(it.z >> 16);
     const int w = x1 - x0 + 1, cnt = w * (y1 - y0 + 1);
     const unsigned rw = c_rast_rw[w];
-    const float4 r0 = __ldg(fa.rast_rec + 3 * (size_t)it.x), r1 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 1),
-                 r2 = __ldg(fa.rast_rec + 3 * (size_t)it.x + 2);
+    const float4 r0 = src[j].r0, r1 = src[j].r1, r2 = src[j].r2;
     const float ox = (float)x0 - r2.y, oy = (float)y0 - r2.z;     // item corner relative to the record's origin
     if (cnt <= RAST_SCAN_MAX) {
       // small rectangle: its samples 32 at a time

@@ -86,6 +86,25 @@ struct DevCamera {
   float L;                  // distance of the image plane (raster.cuh)
 };
 
+// Item exchange of the projection pass between the ranks of a frame (raster.cuh).  Non-sharded (one
+// rank, or every rank projecting all triangles): one local segment.  Sharded: rank r projects the
+// triangles [r T / N, (r + 1) T / N) and writes each item straight into the inbox of the rank that
+// owns its tile -- peer-mapped memory, NVLink stores, no collective -- then publishes its counts and
+// its epoch to every peer and waits for theirs (k_xchg_sync).
+constexpr int XCHG_MAX_RANKS = 8;
+// control block of a rank, 32-bit words: READY[src] epoch that source has published; per parity p (epoch & 1):
+// COUNT[p][src] items in segment src, GAVE[p][src] that source gave up, AREA[p][src] (2 words) its work estimate
+constexpr int XCHG_READY = 0, XCHG_COUNT = 8, XCHG_GAVE = 24, XCHG_AREA = 40, XCHG_CTL_WORDS = 128;
+struct RastItem { uint4 hdr; float4 r0, r1, r2; };      // (slot, x0 | y0 << 16, x1 | y1 << 16, -) + the triangle's edge record
+struct XchgView {
+  int sharded;                          // 0: items stay on this rank (segment 0 only)
+  unsigned cap;                         // items per segment
+  unsigned epoch;                       // frame number of the exchange (all ranks count alike), parity = double buffer
+  RastItem *seg[XCHG_MAX_RANKS];        // seg[q]: this rank's segment in rank q's inbox (remote unless q == rank)
+  unsigned *ctl[XCHG_MAX_RANKS];        // ctl[q]: rank q's control block
+  const RastItem *in[XCHG_MAX_RANKS];   // this rank's inbox: the segment of source s (local memory)
+};
+
 struct FrameArgs {
   DevCamera cam;
   int aliasing;
@@ -101,11 +120,10 @@ struct FrameArgs {
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
   // primary visibility by projection (raster.cuh); prim == nullptr: every ray walks the tree
   unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
-  uint4 *rast_items;              // (slot, x0 | y0 << 16, x1 | y1 << 16, -) rectangles clipped to 32x32-sample tiles
-  unsigned rast_cap;              // capacity of rast_items
-  float4 *rast_rec;               // 3 per triangle slot: edge record of the projected triangle (raster.cuh)
+  XchgView x;                     // where the items go and come from
   unsigned *rast;                 // counters and flags (raster.cuh RAST_WORDS)
   unsigned *rast_big;             // [RAST_BIG_CAP] slots of triangles whose items k_rast_big emits
+  region::PrimaryCull *rast_big_cull;   // [RAST_BIG_CAP] their regions as k_rast_setup computed them
   region::CamFrame camf;          // the camera in double precision + the rounding scales of this frame (region.cuh)
   unsigned rast_area_factor;      // give up when the rectangles cover more than this many times the frame
   // wavefront kernel only

@@ -45,8 +45,16 @@ struct SceneStore {
   // primary visibility by projection (raster.cuh), grown on demand by api.cu
   unsigned long long *d_prim = nullptr;
   size_t d_prim_count = 0;
-  uint4 *d_rast_items = nullptr;
+  RastItem *d_rast_items = nullptr;     // the local item segment of frames that are not sharded
   size_t d_rast_cap = 0;
+  // item exchange of sharded multi-rank frames (raster.cuh, rtb_scene_exchange_*): this rank's block =
+  // control words + inbox (2 parities x nranks segments), and the peers' blocks as mapped here
+  unsigned char *xchg_block = nullptr;
+  size_t xchg_bytes = 0;
+  unsigned xchg_cap = 0;                // items per segment
+  int xchg_nranks = 0, xchg_rank = -1;  // attached: the frame layout the peers' pointers are for
+  unsigned char *xchg_peer[XCHG_MAX_RANKS] = {nullptr};
+  unsigned xchg_epoch = 0;
   unsigned *d_rast = nullptr;
   unsigned *h_rast = nullptr;           // pinned: state the last projection pass left (read back with the frame)
   bool one_frame = false;               // built with RTB_BUILD_ONE_FRAME

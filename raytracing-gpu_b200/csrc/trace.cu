@@ -731,16 +731,21 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
   if (launches) *launches = 1;
   if (fa.prim && tracer == RTB_TRACER_TREE && !count) {
     // projection pass: records of the nearest primary candidate per sample (raster.cuh)
-    RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
+    // rank tiles are whole sample tiles when 32 a is a multiple of 32 (always): a rank clears what it owns
+    if (fa.nranks > 1) k_prim_clear<<<sm_count * 8, 256, 0, st>>>(fa);
+    else RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
     RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
     if (sc.n_tris) {
-      k_rast_setup<<<(sc.n_tris + 255) / 256, 256, 0, st>>>(sc, fa);
-      k_rast_big<<<sm_count * 4, RAST_BIG_THREADS, 0, st>>>(sc, fa);
+      const unsigned share = fa.x.sharded ? sc.n_tris / (unsigned)fa.nranks + 1u : sc.n_tris;
+      k_rast_setup<<<(share + 255) / 256, 256, 0, st>>>(sc, fa);
+      k_rast_big<<<sm_count * 8, RAST_BIG_THREADS, 0, st>>>(sc, fa);
     }
+    // sharded frames: counts and epoch to every rank, wait for theirs (the items went over NVLink already)
+    if (fa.x.sharded) k_xchg_sync<<<1, 32, 0, st>>>(fa);
     if (marks) RTB_CUDA(cudaEventRecord(marks[1], st));
     if (sc.n_tris) k_rast_items<<<sm_count * 8, 256, 0, st>>>(sc, fa);
     RTB_CUDA(cudaGetLastError());
-    if (launches) *launches = 4;
+    if (launches) *launches = fa.x.sharded ? 5 : 4;
   } else if (marks) RTB_CUDA(cudaEventRecord(marks[1], st));
   if (marks) RTB_CUDA(cudaEventRecord(marks[2], st));
   const int rc = launch_frame_kernel(sc, fa, tracer, count, sm_count, st);
@@ -808,7 +813,7 @@ int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int
   RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
   if (sc.n_tris) {
     k_rast_setup<<<(sc.n_tris + 255) / 256, 256, 0, st>>>(sc, fa);
-    k_rast_big<<<sm_count * 4, RAST_BIG_THREADS, 0, st>>>(sc, fa);
+    k_rast_big<<<sm_count * 8, RAST_BIG_THREADS, 0, st>>>(sc, fa);
     k_rast_items<<<sm_count * 8, 256, 0, st>>>(sc, fa);
   }
   const size_t n = (size_t)fa.cam.W * fa.cam.H;

@@ -69,7 +69,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_render", "rtb_render_multi", "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_set_camera",
     "rtb_scene_render", "rtb_scene_render_device", "rtb_scene_sync", "rtb_scene_hit_ids", "rtb_scene_trace_rays",
     "rtb_scene_stats", "rtb_radix_sort_pairs_u32", "rtb_radix_sort_pairs_u64", "rtb_inclusive_scan_u32",
-    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_dev_inclusive_scan_u32_static", "rtb_scene_dump_tree", "rtb_scene_raster_state", "rtb_scene_profile", "rtb_scene_kernel_ms",
+    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_dev_inclusive_scan_u32_static", "rtb_scene_dump_tree", "rtb_scene_raster_state", "rtb_scene_profile", "rtb_scene_kernel_ms", "rtb_scene_exchange_create", "rtb_scene_exchange_attach",
     "rtb_device_count", "rtb_version", "rtb_scene_root", "rtb_set_margin_k", "rtb_set_schedule", "rtb_warmup", "rtb_scene_timer_start",
     "rtb_scene_timer_stop", "rtb_host_alloc", "rtb_host_free", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_memset",
     "rtb_dev_download", "rtb_scene_mem_alloc", "rtb_scene_mem_free", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close",
@@ -405,6 +405,20 @@ class DeviceScene:
         _check(fn(self.h, out))
         return dict(items=out[0], gave_up=out[1], area=out[2] | (out[3] << 32), two_part_regions=out[4], light_grids=out[5],
                     grid_entries_k=out[6], grid_cells_k=out[7])
+
+    def exchange_create(self, nranks):
+        """rtb_scene_exchange_create: this rank's exchange block (device pointer, bytes)"""
+        ptr, n = C.c_void_p(), C.c_size_t()
+        fn = lib().rtb_scene_exchange_create
+        fn.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]
+        _check(fn(self.h, nranks, C.byref(ptr), C.byref(n)))
+        return ptr.value, n.value
+
+    def exchange_attach(self, rank, nranks, blocks):
+        arr = (C.c_void_p * nranks)(*[C.c_void_p(b) for b in blocks])
+        fn = lib().rtb_scene_exchange_attach
+        fn.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        _check(fn(self.h, rank, nranks, arr))
 
     def profile(self, on=True):
         fn = lib().rtb_scene_profile

@@ -314,3 +314,22 @@ def test_frames_wider_than_the_item_corners_walk_the_tree(gpu):
         assert ds.stats()["kernel_launches"] == 1
     finally:
         ds.close()
+
+
+@pytest.mark.parametrize("nranks", [2, 4, 8])
+def test_sharded_projection_pass_with_item_exchange(gpu, nranks):
+    """rtb_scene_exchange_*: every rank projects 1/N of the triangles and stores the items into the owners'
+    inboxes (peer stores between GPUs; here N handles on ONE device, each on its own stream, so the
+    device-side epoch barrier really waits for the other ranks' kernels).  Runs in a process of its own
+    with CUDA_DEVICE_MAX_CONNECTIONS=32: with the default 8 hardware queues the streams of 8 "ranks" on one
+    device alias, and a spinning barrier kernel can sit in front of the kernel it waits for (real ranks
+    have a device each).  tests/native/exchange_probe.py has the body."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, CUDA_DEVICE_MAX_CONNECTIONS="32")
+    r = subprocess.run([sys.executable, os.path.join(here, "native", "exchange_probe.py"), str(nranks)], env=env,
+                       capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "exchange ok" in r.stdout
