@@ -263,7 +263,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     if (S.sched_items < cap) {
       if (S.d_sched) cudaFreeAsync(S.d_sched, st);
       S.d_sched = nullptr; S.d_item_order = nullptr; S.sched_items = 0;
-      const size_t bytes = cap * (2 + 8 + 8 + 4 + 4) + radix_sort_scratch_words(cap) * 4 + 1024;
+      const size_t bytes = cap * (4 + 8 + 8 + 4 + 4) + radix_sort_scratch_words(cap) * 4 + 1024;
       RTB_CUDA(cudaMallocAsync((void **)&S.d_sched, bytes, st));
       S.sched_items = cap;
     }
@@ -276,15 +276,34 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     sv = (uint32_t *)(sk2 + c); sv2 = sv + c;
     ss = sv2 + c;
     ssw = radix_sort_scratch_words(c);
-    unsigned short *cost = (unsigned short *)(ss + ssw + 64);
+    unsigned int *cost = (unsigned int *)(ss + ssw + 64);
     record = !S.d_item_order || S.order_camera_gen != S.camera_gen;
     fa.item_order = S.d_item_order;
     if (record) {
       // the current order (if any) lives in sv or sv2 and is read by this frame: the new one is
       // sorted after the frame on the same stream, so overwriting either is safe
-      RTB_CUDA(cudaMemsetAsync(cost, 0, (size_t)n_items * 2, st));
+      RTB_CUDA(cudaMemsetAsync(cost, 0, (size_t)n_items * 4, st));
       fa.item_cost = cost;
     }
+  }
+  // fine work items (one round of a tile each) for multi-rank frames of the per-sample kernel
+  fa.fine_acc = nullptr; fa.fine_done = nullptr;
+  static const int fine_min_ranks = [] { const char *e = getenv("RTB_FINE_ITEMS_FROM"); return e ? atoi(e) : 2; }();
+  if (o.nranks >= fine_min_ranks && fine_min_ranks > 0 && o.tracer == RTB_TRACER_TREE && !o.count_rays && !fa.bounce_scratch && o.aliasing > 1) {
+    const size_t pixels = (size_t)out_w * out_h, items = frame_item_count(out_w, out_h, o.nranks);
+    if (S.fine_pixels < pixels) {
+      if (S.d_fine_acc) cudaFreeAsync(S.d_fine_acc, st);
+      S.d_fine_acc = nullptr; S.fine_pixels = 0;
+      RTB_CUDA(cudaMallocAsync((void **)&S.d_fine_acc, pixels * sizeof(uint2), st));
+      S.fine_pixels = pixels;
+    }
+    if (S.fine_items < items) {
+      if (S.d_fine_done) cudaFreeAsync(S.d_fine_done, st);
+      S.d_fine_done = nullptr; S.fine_items = 0;
+      RTB_CUDA(cudaMallocAsync((void **)&S.d_fine_done, items * 4, st));
+      S.fine_items = items;
+    }
+    fa.fine_acc = S.d_fine_acc; fa.fine_done = S.d_fine_done;
   }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   if (S.profile && !S.kev[0])

@@ -223,6 +223,22 @@ __global__ void __launch_bounds__(128) k_lg_big(const DevScene sc, const LightGr
   }
 }
 
+// statistics of a grid (RTB_BUILD_TRACE): out[0] longest cell list, out[1] cells with more than 64 entries,
+// out[2] sum of squares of the list lengths (a random entry's list length is that / the entry count)
+__global__ void __launch_bounds__(256) k_lg_stats(const uint32_t *cell_start, size_t cells, unsigned long long *out) {
+  unsigned mx = 0, big = 0;
+  unsigned long long sq = 0;
+  for (size_t c = (size_t)blockIdx.x * 256 + threadIdx.x; c < cells; c += (size_t)gridDim.x * 256) {
+    const unsigned n = cell_start[c + 1] - cell_start[c];
+    mx = max(mx, n); big += n > 64u; sq += (unsigned long long)n * n;
+  }
+  mx = __reduce_max_sync(0xffffffffu, mx);
+  big = __reduce_add_sync(0xffffffffu, big);
+#pragma unroll
+  for (int d = 16; d; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
+  if ((threadIdx.x & 31) == 0) { atomicMax(out, (unsigned long long)mx); atomicAdd(out + 1, (unsigned long long)big); atomicAdd(out + 2, sq); }
+}
+
 // ---- the lookup ----
 // 1: some candidate on the ray, 0: none, -1: this ray has to walk the tree (its point is off the grid, or its
 // origin outside the box the regions were bounded for).

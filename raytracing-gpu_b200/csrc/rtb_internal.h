@@ -116,7 +116,11 @@ struct FrameArgs {
   // work-item scheduling (trace.cu frame_item): order to take the items in (nullptr = 0,1,2,..)
   // and where to leave each item's cost, in 256-cycle units (nullptr = not recorded)
   const unsigned int *item_order;
-  unsigned short *item_cost;
+  unsigned int *item_cost;        // per item, 256-cycle units (fine items: summed over the item's rounds)
+  // fine work items of multi-rank frames (k_frame<.., FINE>): per output pixel the channel sums of its samples,
+  // per item the number of finished rounds; nullptr: one warp does all rounds of an item (sums in shared memory)
+  uint2 *fine_acc;
+  unsigned int *fine_done;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
   // primary visibility by projection (raster.cuh); prim == nullptr: every ray walks the tree
   unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
@@ -151,7 +155,7 @@ size_t scan_scratch_words(size_t n);
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches, cudaEvent_t *marks = nullptr);
 unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
-int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
+int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
                       cudaStream_t st, int *result_in_alt);
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,

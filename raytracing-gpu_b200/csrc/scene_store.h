@@ -62,6 +62,9 @@ struct SceneStore {
   unsigned long long rast_key[4] = {0, 0, 0, 0};   // camera generation, samples, ranks, factor of the frame h_rast is for
   unsigned rast_area_factor = 20;
   bool rast_useless = false;            // that frame walked the tree although it ran the pass: do not try again
+  uint2 *d_fine_acc = nullptr;          // fine work items of multi-rank frames (trace.cu k_frame<.., FINE>)
+  unsigned int *d_fine_done = nullptr;
+  size_t fine_pixels = 0, fine_items = 0;
   float *d_bounce = nullptr;            // wavefront kernel: reflected-ray scratch
   size_t d_bounce_floats = 0;
   int n_shadow_lights = 0;              // DIRECTIONAL + POINT lights

@@ -394,17 +394,21 @@ __device__ __forceinline__ bool frame_item(const FrameArgs &fa, unsigned item, i
 #ifndef RTB_FRAME_MINBLOCKS
 #define RTB_FRAME_MINBLOCKS 8
 #endif
-template <int TRACER, bool COUNT>
+// FINE (multi-rank frames): a work item is ONE round of 32 samples of a warp tile, the sums go to a global
+// accumulator with atomics and the warp that finishes a tile's last round resolves it.  With 1/N of the
+// tiles per rank the slowest tile sets the frame's tail (a tile over a cell of a light grid that hundreds of
+// line regions cross takes milliseconds); cut into a x a rounds taken by different warps it no longer does.
+template <int TRACER, bool COUNT, bool FINE>
 __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
   // Per output pixel of the warp tile: the channel sums of its a x a samples (x: r | g << 16,
   // y: b).  The reference sums the u8 channels as floats (gpu/raytracer.cu:62-70); sums of at
   // most 256 values below 256 are exact in either arithmetic, so integers give the same bits.
   // 1 KB per CTA whatever the aliasing, which leaves the unified L1 its largest share.
-  __shared__ uint2 s_acc[FRAME_WARPS][32];
+  __shared__ uint2 s_acc[FINE ? 1 : FRAME_WARPS][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int a = fa.aliasing;
-  uint2 *acc = s_acc[warp];
-  const unsigned total = frame_items(fa);
+  const int a = fa.aliasing, aa = a * a;
+  uint2 *acc = s_acc[FINE ? 0 : warp];
+  const unsigned total = frame_items(fa) * (FINE ? (unsigned)aa : 1u);
   const bool use_prim = TRACER == RTB_TRACER_TREE && !COUNT && rast_active(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
@@ -412,29 +416,51 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
     if (lane == 0) t = atomicAdd(fa.tile_counter, 1u);
     t = __shfl_sync(0xffffffffu, t, 0);
     if (t >= total) break;
-    // items are taken in the order of the previous frame's cost, longest first (api.cu)
-    const unsigned item = fa.item_order ? __ldg(fa.item_order + t) : t;
+    // items are taken in the order of the previous frame's cost, longest first (api.cu); the rounds of a
+    // fine item are consecutive, so different warps take them at about the same time
+    const unsigned ti = FINE ? t / (unsigned)aa : t;
+    const int q0 = FINE ? (int)(t - ti * (unsigned)aa) : 0, q1 = FINE ? q0 + 1 : aa;
+    const unsigned item = fa.item_order ? __ldg(fa.item_order + ti) : ti;
     int lx0, ly0;
-    if (!frame_item(fa, item, lx0, ly0)) continue;
-    // start time parked in the cost slot itself (256-cycle units, 16 bits): no register, no shared memory
-    if (fa.item_cost && lane == 0) fa.item_cost[item] = (unsigned short)(clock64() >> 8);
-    acc[lane] = make_uint2(0u, 0u);
-    __syncwarp();
-    for (int q = 0; q < a * a; ++q) {
-      const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
-      const int px = a * lx0 + sx, py = a * ly0 + sy;
-      if (px < fa.cam.W && py < fa.cam.H) {
-        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
-        uint2 *dst = acc + (sy / a) * 8 + sx / a;
-        atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
-        atomicAdd(&dst->y, ch_b(col));
-      }
+    const bool inside = frame_item(fa, item, lx0, ly0);
+    if (!inside && !FINE) continue;
+    long long t_start = 0;
+    if (fa.item_cost && lane == 0) t_start = clock64();
+    if (!FINE) {
+      acc[lane] = make_uint2(0u, 0u);
+      __syncwarp();
     }
-    __syncwarp();
+    if (inside)
+      for (int q = q0; q < q1; ++q) {
+        const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
+        const int px = a * lx0 + sx, py = a * ly0 + sy;
+        if (px < fa.cam.W && py < fa.cam.H) {
+          const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
+          uint2 *dst = FINE ? fa.fine_acc + (size_t)(ly0 + sy / a) * fa.out_w + (lx0 + sx / a) : acc + (sy / a) * 8 + sx / a;
+          atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
+          atomicAdd(&dst->y, ch_b(col));
+        }
+      }
+    bool resolve = !FINE;
+    if (FINE) {
+      // the last round of the item to finish resolves it: sums first (atomics at L2), then the count
+      __threadfence();
+      __syncwarp();
+      unsigned before = 0;
+      if (lane == 0) before = atomicAdd(fa.fine_done + item, 1u);
+      before = __shfl_sync(0xffffffffu, before, 0);
+      resolve = inside && before == (unsigned)aa - 1u;
+      if (resolve) __threadfence();
+    } else __syncwarp();
+    if (fa.item_cost && lane == 0) {
+      const unsigned dt = (unsigned)((clock64() - t_start) >> 8);
+      if (FINE) atomicAdd(fa.item_cost + item, dt); else fa.item_cost[item] = dt;
+    }
+    if (!resolve) continue;
     // downscale kernel body (gpu/raytracer.cu:49-85) for this lane's output pixel
     const int lx = lx0 + (lane & 7), ly = ly0 + (lane >> 3);
     if (lx < fa.out_w && ly < fa.out_h) {
-      const uint2 sum = acc[lane];
+      const uint2 sum = FINE ? __ldcg(fa.fine_acc + (size_t)ly * fa.out_w + lx) : acc[lane];
       float r = (float)(sum.x & 0xffffu), g = (float)(sum.x >> 16), b = (float)sum.y;
       const float ali2 = 255.0f * (float)a * (float)a;
       r /= ali2;
@@ -444,9 +470,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       unsigned char *dst = fa.out + (long long)(fa.out_h - ly - 1) * fa.pitch + 4ll * (fa.out_w - lx - 1);
       *reinterpret_cast<uint32_t *>(dst) = e;
     }
-    __syncwarp();
-    if (fa.item_cost && lane == 0)
-      fa.item_cost[item] = (unsigned short)((unsigned short)(clock64() >> 8) - fa.item_cost[item]);   // modulo 2^16
+    if (!FINE) __syncwarp();
   }
   if (COUNT) {
     unsigned v[5] = {c.primary, c.shadow, c.bounce, c.nodes, c.tris};
@@ -509,7 +533,7 @@ constexpr int LG_MAX_GRIDS = 8;
 // device scratch of one light's grid build, freed on every way out (kept blocks excepted)
 struct LgScratch {
   cudaStream_t st;
-  void *p[8] = {nullptr};
+  void *p[16] = {nullptr};
   int n = 0;
   template <typename T> int alloc(T **out, size_t bytes) {
     *out = nullptr;
@@ -668,6 +692,22 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     RTB_CUDA(cudaGetLastError());
     g.cell_start = counts; g.entries = entries; g.rec = rec;
     tmp.keep(counts); tmp.keep(entries); tmp.keep(rec);
+    static const bool lg_trace = [] { const char *e = getenv("RTB_BUILD_TRACE"); return e && atoi(e) != 0; }();
+    if (lg_trace) {
+      unsigned long long *d_st = nullptr, h_st[3] = {0, 0, 0};
+      unsigned h_big = 0;
+      if (tmp.alloc(&d_st, 32) == RTB_OK) {
+        cudaMemsetAsync(d_st, 0, 32, st);
+        k_lg_stats<<<S.sm_count * 4, 256, 0, st>>>(counts, cells, d_st);
+        cudaMemcpyAsync(h_st, d_st, 24, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(&h_big, d_b + 24, 4, cudaMemcpyDeviceToHost, st);
+        cudaStreamSynchronize(st);
+        fprintf(stderr, "rtb light grid %zu (%s): %d x %d cells, %u entries (%.2f per cell), %u triangles over more than %d rows, "
+                "%u tested by every ray, longest list %llu, %llu cells with > 64 entries, a random entry's list has %.1f entries\n",
+                i, g.kind == 1 ? "directional" : "point", g.nx, g.ny, total, (double)total / (double)cells, h_big, LG_BIG_ROWS,
+                state[0], h_st[0], h_st[1], (double)h_st[2] / (double)(total ? total : 1));
+      }
+    }
     g.n_large = state[0] < (uint32_t)LG_LARGE_MAX ? state[0] : (uint32_t)LG_LARGE_MAX;
     for (uint32_t k = 0; k < g.n_large; ++k) g.large[k] = state[2 + k];
     S.lgrid_mem[mem++] = rec; S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
@@ -684,10 +724,10 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
   return RTB_OK;
 }
 
-template <int TRACER, bool COUNT>
+template <int TRACER, bool COUNT, bool FINE = false>
 static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
   const size_t smem = 0;
-  auto kern = k_frame<TRACER, COUNT>;
+  auto kern = k_frame<TRACER, COUNT, FINE>;
 #ifdef RTB_CARVEOUT   /* A/B only: shared-memory share of the unified L1, percent */
   RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, RTB_CARVEOUT));
 #endif
@@ -761,8 +801,13 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
   if (tracer == RTB_TRACER_BRUTE)
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);
-  return count ? launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st)
-               : launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
+  if (count) return launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st);
+  if (fa.fine_acc) {
+    RTB_CUDA(cudaMemsetAsync(fa.fine_acc, 0, (size_t)fa.out_w * fa.out_h * sizeof(uint2), st));
+    RTB_CUDA(cudaMemsetAsync(fa.fine_done, 0, (size_t)frame_item_count(fa.out_w, fa.out_h, fa.nranks) * 4, st));
+    return launch_frame_t<RTB_TRACER_TREE, false, true>(sc, fa, sm_count, st);
+  }
+  return launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
 }
 
 // ---- longest-first item order from the costs the previous frame left (api.cu) ----
@@ -772,11 +817,11 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
 #ifndef RTB_COST_CLASSES_PER_OCTAVE
 #define RTB_COST_CLASSES_PER_OCTAVE 2
 #endif
-__global__ void __launch_bounds__(256) k_item_keys(const unsigned short *cost, unsigned n, uint64_t *keys,
+__global__ void __launch_bounds__(256) k_item_keys(const unsigned int *cost, unsigned n, uint64_t *keys,
                                                    uint32_t *vals) {
   const unsigned i = blockIdx.x * 256 + threadIdx.x;
   if (i >= n) return;
-  const int cls = (int)((float)RTB_COST_CLASSES_PER_OCTAVE * log2f((float)cost[i] + 1.0f));   // 0 .. 16 * classes
+  const int cls = (int)((float)RTB_COST_CLASSES_PER_OCTAVE * log2f((float)min(cost[i], 0xffffffu) + 1.0f));   // 0 .. 16 * classes
   keys[i] = (uint64_t)(255 - min(cls, 255));   // ascending sort = heaviest class first; empty items (cost 0) last
   vals[i] = i;
 }
@@ -786,7 +831,7 @@ unsigned frame_item_count(int out_w, int out_h, int nranks) {
   return (unsigned)((nTx + nranks - 1) / nranks) * (unsigned)nTy * (unsigned)RT_ITEMS;
 }
 
-int launch_item_order(const unsigned short *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
+int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
                       cudaStream_t st, int *result_in_alt) {
   k_item_keys<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_keys, d_vals);
