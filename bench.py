@@ -503,9 +503,9 @@ def run_ours(args):
         alg_ops = primary * OPS_PRIMARY + shadow * OPS_SHADOW + bounce * OPS_PRIMARY
         alg_bytes = primary * BYTES_PRIMARY + shadow * BYTES_SHADOW + bounce * BYTES_PRIMARY
         achieved_tflops = alg_ops / world / kern_s / 1e12        # per GPU: each rank's kernel does 1/world of the rays
-        kernels_live = {"clears+k_rast_setup+k_rast_big": float(parts[0]), "k_rast_items": float(parts[1]),
-                        "k_frame": float(parts[2]), "frame": float(parts[3])}
-        dominant = max(("clears+k_rast_setup+k_rast_big", "k_rast_items", "k_frame"), key=lambda k: kernels_live[k])
+        kernels_live = {"clears+k_rast_setup": float(parts[4]), "k_rast_big": float(parts[5]), "k_xchg_sync": float(parts[6]),
+                        "k_rast_items": float(parts[1]), "k_frame": float(parts[2]), "frame": float(parts[3])}
+        dominant = max(("clears+k_rast_setup", "k_rast_big", "k_rast_items", "k_frame"), key=lambda k: kernels_live[k])
         roofline = {
             "bound": "fp32_issue",
             "kernel": "k_frame<tree>" if launches_per_frame == 1 else "the frame's kernels: k_rast_setup + k_rast_big + k_rast_items + k_frame<tree>",

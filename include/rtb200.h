@@ -224,10 +224,12 @@ int rtb_scene_exchange_create(rtb_scene_t *h, int nranks, void **d_block, size_t
 int rtb_scene_exchange_attach(rtb_scene_t *h, int rank, int nranks, void *const *blocks);
 
 /* Measurement aid (bench.py): with profiling on, every frame records CUDA events between its
- * kernels; rtb_scene_kernel_ms waits for the last frame and returns out[0] clears + k_rast_setup,
- * out[1] k_rast_items, out[2] the frame kernel, out[3] the whole frame, in milliseconds. */
+ * kernels; rtb_scene_kernel_ms waits for the last frame and returns, in milliseconds, out[0] clears +
+ * k_rast_setup + k_rast_big + k_xchg_sync, out[1] k_rast_items, out[2] the frame kernel, out[3] the whole
+ * frame, and the parts of out[0]: out[4] clears + k_rast_setup, out[5] k_rast_big, out[6] k_xchg_sync (the
+ * wait for the other ranks' items, sharded frames only); out[7] is 0. */
 int rtb_scene_profile(rtb_scene_t *h, int on);
-int rtb_scene_kernel_ms(rtb_scene_t *h, double out[4]);
+int rtb_scene_kernel_ms(rtb_scene_t *h, double out[8]);
 
 /* State the projection pass of the last frame (or hit-id query) left: out[0] items,
  * out[1] != 0: it gave up (too many items, a triangle over too many tiles), out[2] | out[3] << 32

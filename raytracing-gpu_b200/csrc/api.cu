@@ -287,23 +287,31 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     }
   }
   // fine work items (one round of a tile each) for multi-rank frames of the per-sample kernel
-  fa.fine_acc = nullptr; fa.fine_done = nullptr;
-  static const int fine_min_ranks = [] { const char *e = getenv("RTB_FINE_ITEMS_FROM"); return e ? atoi(e) : 2; }();
-  if (o.nranks >= fine_min_ranks && fine_min_ranks > 0 && o.tracer == RTB_TRACER_TREE && !o.count_rays && !fa.bounce_scratch && o.aliasing > 1) {
+  fa.fine_acc = nullptr; fa.fine_done = nullptr; fa.fine_hot = nullptr;
+  static const int fine_min_ranks = [] { const char *e = getenv("RTB_FINE_ITEMS_FROM"); return e ? atoi(e) : 1; }();
+  static const float hot_div = [] { const char *e = getenv("RTB_HOT_DIV"); return e ? (float)atof(e) : 4.0f; }();
+  unsigned *d_hot = nullptr;
+  const bool fine = schedule && o.nranks >= fine_min_ranks && fine_min_ranks > 0 && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
+                    !fa.bounce_scratch && o.aliasing > 1;
+  if (schedule)      // 4 words behind the costs, aligned for the 64-bit sum
+    d_hot = (unsigned *)(((uintptr_t)((unsigned *)(ss + ssw + 64) + S.sched_items) + 15u) & ~(uintptr_t)15u);
+  if (fine) {
     const size_t pixels = (size_t)out_w * out_h, items = frame_item_count(out_w, out_h, o.nranks);
     if (S.fine_pixels < pixels) {
       if (S.d_fine_acc) cudaFreeAsync(S.d_fine_acc, st);
       S.d_fine_acc = nullptr; S.fine_pixels = 0;
       RTB_CUDA(cudaMallocAsync((void **)&S.d_fine_acc, pixels * sizeof(uint2), st));
+      RTB_CUDA(cudaMemsetAsync(S.d_fine_acc, 0, pixels * sizeof(uint2), st));      // once: k_frame leaves it zero
       S.fine_pixels = pixels;
     }
     if (S.fine_items < items) {
       if (S.d_fine_done) cudaFreeAsync(S.d_fine_done, st);
       S.d_fine_done = nullptr; S.fine_items = 0;
       RTB_CUDA(cudaMallocAsync((void **)&S.d_fine_done, items * 4, st));
+      RTB_CUDA(cudaMemsetAsync(S.d_fine_done, 0, items * 4, st));
       S.fine_items = items;
     }
-    fa.fine_acc = S.d_fine_acc; fa.fine_done = S.d_fine_done;
+    fa.fine_acc = S.d_fine_acc; fa.fine_done = S.d_fine_done; fa.fine_hot = d_hot + 2;
   }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   if (S.profile && !S.kev[0])
@@ -313,7 +321,9 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   RTB_CUDA(cudaEventRecord(S.ev1, st));
   if (record) {
     int in_alt = 0;
-    rc = launch_item_order(fa.item_cost, n_items, sk, sv, sk2, sv2, ss, ssw, st, &in_alt);
+    // a warp's fair share of the frame: the costs are what the warps of the persistent grid spent, stalls included
+    const float per_share = fine ? 1.0f / ((float)S.sm_count * 32.0f /* 8 CTAs of 4 warps per SM, trace.cu k_frame */ * hot_div) : 0.0f;
+    rc = launch_item_order(fa.item_cost, n_items, sk, sv, sk2, sv2, ss, ssw, st, &in_alt, d_hot, per_share);
     if (rc) return rc;
     S.d_item_order = in_alt ? sv2 : sv;
     S.order_camera_gen = S.camera_gen;
@@ -591,15 +601,23 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
   std::vector<int> rcs((size_t)n_devices, RTB_OK);
   std::vector<std::string> errs((size_t)n_devices);
   std::vector<std::thread> workers;
+  const char *tr = getenv("RTB_TRACE");
+  const bool trace = tr && *tr == '1';
+  using clk = std::chrono::steady_clock;
+  const auto t_start = clk::now();
   for (int dev = 0; dev < n_devices; ++dev)
     workers.emplace_back([&, dev] {
+      auto ms = [&](clk::time_point b) { return std::chrono::duration<double, std::milli>(b - t_start).count(); };
+      const auto t0 = clk::now();
       rtb_scene_t *h = nullptr;
       int r = rtb_scene_create(scene, dev, RTB_BUILD_ONE_FRAME, &h);
+      const auto t1 = clk::now();
       if (!r && dev != 0) {
         const cudaError_t e = cudaDeviceEnablePeerAccess(0, 0);
         if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) r = cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
         cudaGetLastError();
       }
+      const auto t2 = clk::now();
       if (!r) {
         rtb_frame_opts o;
         memset(&o, 0, sizeof o);
@@ -609,8 +627,16 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
         r = rtb_scene_render_device(h, &o, d_frame, (ptrdiff_t)row, out_h, out_w, nullptr);
         if (!r) r = rtb_scene_sync(h);
       }
+      const auto t3 = clk::now();
       if (r) errs[(size_t)dev] = g_err;
+      rtb_stats st;
+      memset(&st, 0, sizeof st);
+      if (trace && h) rtb_scene_stats(h, &st);
       if (h) rtb_scene_destroy(h);
+      if (trace)
+        fprintf(stderr, "rtb_render_multi dev %d: thread start +%.2f, create until +%.2f (device: upload %.2f + build %.2f), peer access +%.2f, "
+                "frame until +%.2f (kernels %.2f), destroy until +%.2f ms\n", dev, ms(t0), ms(t1), st.upload_ms, st.build_ms, ms(t2), ms(t3),
+                st.frame_ms, ms(clk::now()));
       rcs[(size_t)dev] = r;
     });
   for (std::thread &t : workers) t.join();
@@ -776,22 +802,27 @@ int rtb_scene_profile(rtb_scene_t *h, int on) {
   return RTB_OK;
 }
 
-int rtb_scene_kernel_ms(rtb_scene_t *h, double out[4]) {
+int rtb_scene_kernel_ms(rtb_scene_t *h, double out[8]) {
   if (!h || !out) { set_error("NULL argument"); return RTB_ERR_ARG; }
   SceneStore &S = h->store;
-  for (int k = 0; k < 4; ++k) out[k] = 0.0;
+  for (int k = 0; k < 8; ++k) out[k] = 0.0;
   if (!S.kev[0]) { set_error("rtb_scene_profile was not switched on before the frame"); return RTB_ERR_ARG; }
   RTB_CUDA(cudaSetDevice(S.device));
-  RTB_CUDA(cudaEventSynchronize(S.kev[3]));
-  for (int k = 0; k < 3; ++k) {
+  RTB_CUDA(cudaEventSynchronize(S.kev[5]));
+  auto span = [&](int a, int b, double &ms_out) -> int {
     float ms = 0;
-    RTB_CUDA(cudaEventElapsedTime(&ms, S.kev[k], S.kev[k + 1]));
-    out[k] = ms;
-  }
-  float ms = 0;
-  RTB_CUDA(cudaEventElapsedTime(&ms, S.kev[0], S.kev[3]));
-  out[3] = ms;
-  return RTB_OK;
+    RTB_CUDA(cudaEventElapsedTime(&ms, S.kev[a], S.kev[b]));
+    ms_out = ms;
+    return RTB_OK;
+  };
+  int rc = span(0, 3, out[0]);                 // clears + k_rast_setup + k_rast_big + k_xchg_sync
+  if (!rc) rc = span(3, 4, out[1]);            // k_rast_items
+  if (!rc) rc = span(4, 5, out[2]);            // the frame kernel
+  if (!rc) rc = span(0, 5, out[3]);
+  if (!rc) rc = span(0, 1, out[4]);            // clears + k_rast_setup
+  if (!rc) rc = span(1, 2, out[5]);            // k_rast_big
+  if (!rc) rc = span(2, 3, out[6]);            // k_xchg_sync: the wait for the slowest rank's items
+  return rc;
 }
 
 int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]) {
@@ -806,6 +837,8 @@ int rtb_scene_raster_state(rtb_scene_t *h, unsigned out[8]) {
   RTB_CUDA(cudaMemcpyAsync(st16, S.d_rast, sizeof st16, cudaMemcpyDeviceToHost, S.stream));
   RTB_CUDA(cudaStreamSynchronize(S.stream));
   memcpy(out, st16, 5 * sizeof(unsigned));
+  if (getenv("RTB_BUILD_TRACE"))
+    fprintf(stderr, "[rtb200] projection pass: %u triangles on the big list, %u with two-part regions, exchange timeouts %u\n", st16[5], st16[4], st16[6]);
   out[0] = 0;
   for (int q = 0; q < XCHG_MAX_RANKS; ++q) out[0] += st16[8 + q];      // items this rank wrote (for every destination)
   return RTB_OK;

@@ -97,11 +97,11 @@ __global__ void __launch_bounds__(256) k_prim_clear(const FrameArgs fa) {
 // tile, else one per 32 x 32-sample tile the region can touch (region::row_range per tile row, so a
 // long thin region costs its length, not its bounding box).
 __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const FrameArgs fa) {
-  // sharded frames: this rank's share of the triangle slots (slots are in spatial order, so a share is a
-  // compact part of the scene whose items spread over all ranks' interleaved tiles)
-  const uint32_t t0 = fa.x.sharded ? (uint32_t)((uint64_t)sc.n_tris * (unsigned)fa.rank / (unsigned)fa.nranks) : 0u;
-  const uint32_t t1 = fa.x.sharded ? (uint32_t)((uint64_t)sc.n_tris * ((unsigned)fa.rank + 1u) / (unsigned)fa.nranks) : sc.n_tris;
-  const uint32_t s = t0 + blockIdx.x * 256 + threadIdx.x;
+  // sharded frames: this rank's share of the triangle slots, blocks of 256 dealt round robin (slots are in
+  // spatial order and the triangles next to the camera make most of the items: a compact share would leave
+  // one rank with most of the writing)
+  const uint32_t t1 = sc.n_tris;
+  const uint32_t s = fa.x.sharded ? (blockIdx.x * (unsigned)fa.nranks + (unsigned)fa.rank) * 256u + threadIdx.x : blockIdx.x * 256u + threadIdx.x;
   const int lane = threadIdx.x & 31;
   unsigned *rast = fa.rast;
   region::PrimaryCull c;
@@ -160,13 +160,14 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
       area = (unsigned)fmin(work, 67108864.0);
     }
   }
-  if (c.kind == 2) atomicAdd(&rast[4], 1u);
-  // item slots: one atomic per warp and destination, and one for the area
-  unsigned pos[XCHG_MAX_RANKS];
-  bool overflow = false;
+  // item slots: one atomic per CTA and destination, one for the area, one for the two-part count (all of
+  // rast[] is one line of one L2 slice: an atomic per warp made the slice's ALU the kernel's bottleneck)
+  __shared__ unsigned s_w[8][XCHG_MAX_RANKS + 2], s_base[XCHG_MAX_RANKS], s_tot[XCHG_MAX_RANKS];
+  const int warp = threadIdx.x >> 5;
+  unsigned incl_q[XCHG_MAX_RANKS];
 #pragma unroll
   for (int q = 0; q < XCHG_MAX_RANKS; ++q) {
-    pos[q] = 0;
+    incl_q[q] = 0;
     if (q < nd) {
       unsigned incl = cnt[q];
 #pragma unroll
@@ -174,16 +175,40 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
         const unsigned o = __shfl_up_sync(0xffffffffu, incl, d);
         if (lane >= d) incl += o;
       }
-      const unsigned total = __shfl_sync(0xffffffffu, incl, 31);
-      unsigned base = 0;
-      if (lane == 31 && total) base = atomicAdd(&rast[8 + q], total);
-      base = __shfl_sync(0xffffffffu, base, 31);
-      pos[q] = base + incl - cnt[q];
-      if (cnt[q] && base + total > fa.x.cap) overflow = true;
+      incl_q[q] = incl;
+      if (lane == 31) s_w[warp][q] = incl;
     }
   }
   const unsigned wa = __reduce_add_sync(0xffffffffu, min(area, 1u << 26));
-  if (lane == 31 && wa) atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)wa);
+  const unsigned w2 = (unsigned)__popc(__ballot_sync(0xffffffffu, c.kind == 2));
+  if (lane == 31) { s_w[warp][XCHG_MAX_RANKS] = wa; s_w[warp][XCHG_MAX_RANKS + 1] = w2; }
+  __syncthreads();
+  if ((int)threadIdx.x < nd) {
+    const int q = (int)threadIdx.x;
+    unsigned run = 0;
+    for (int w = 0; w < 8; ++w) { const unsigned t = s_w[w][q]; s_w[w][q] = run; run += t; }
+    s_tot[q] = run;
+    s_base[q] = run ? atomicAdd(&rast[8 + q], run) : 0u;
+  } else if (threadIdx.x == XCHG_MAX_RANKS) {
+    unsigned long long sum = 0;
+    for (int w = 0; w < 8; ++w) sum += s_w[w][XCHG_MAX_RANKS];
+    if (sum) atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), sum);
+  } else if (threadIdx.x == XCHG_MAX_RANKS + 1) {
+    unsigned sum = 0;
+    for (int w = 0; w < 8; ++w) sum += s_w[w][XCHG_MAX_RANKS + 1];
+    if (sum) atomicAdd(&rast[4], sum);
+  }
+  __syncthreads();
+  unsigned pos[XCHG_MAX_RANKS];
+  bool overflow = false;
+#pragma unroll
+  for (int q = 0; q < XCHG_MAX_RANKS; ++q) {
+    pos[q] = 0;
+    if (q < nd) {
+      pos[q] = s_base[q] + s_w[warp][q] + incl_q[q] - cnt[q];
+      if (cnt[q] && s_base[q] + s_tot[q] > fa.x.cap) overflow = true;
+    }
+  }
   if (!mine) return;
   if (overflow) { rast[1] = 1u; return; }
   const float *rv = c.rec.v;
@@ -212,19 +237,26 @@ __global__ void __launch_bounds__(256) k_rast_setup(const DevScene sc, const Fra
 
 // k_rast_big: the triangles k_rast_setup listed because their rectangles span many tiles (a road
 // across the frame, a triangle seen edge-on whose region is a line across the screen).  One CTA
-// per triangle, one thread per tile row: region::primary_row_tiles gives the tiles of the row the
-// region can touch, every row takes its slots with one atomic.
+// per triangle: region::primary_row_tiles gives the tiles of each tile row the region can touch (one
+// thread per row), a prefix sum over the rows numbers the tiles, and the CTA's threads take the tiles
+// in that order -- a diagonal line (200 rows of 2 tiles) and a horizontal one (2 rows of 360) keep
+// all lanes busy alike.  Every 32 tiles take their slots with one atomic per destination.
 constexpr int RAST_BIG_THREADS = 128;
+constexpr int RAST_BIG_ROWS = 512;              // tile rows per pass (a 4K x 3 frame has 203)
 __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc, const FrameArgs fa) {
-  __shared__ unsigned s_touched, s_mine;
+  __shared__ unsigned s_touched, s_mine, s_total, s_over, s_cnt[XCHG_MAX_RANKS], s_pos[XCHG_MAX_RANKS];
+  __shared__ int s_ta[RAST_BIG_ROWS];
+  __shared__ unsigned s_off[RAST_BIG_ROWS];
   unsigned *rast = fa.rast;
   const unsigned n_big = min(rast[5], RAST_BIG_CAP);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nd = fa.x.sharded ? fa.nranks : 1;
   for (unsigned bi = blockIdx.x; bi < n_big; bi += gridDim.x) {
     if (*reinterpret_cast<volatile unsigned *>(rast + 1)) return;
     const uint32_t s = fa.rast_big[bi];
     const region::PrimaryCull &c = fa.rast_big_cull[bi];                    // as k_rast_setup computed it
     if (!c.kind) continue;
-    if (threadIdx.x == 0) { s_touched = 0; s_mine = 0; }
+    if (threadIdx.x == 0) { s_touched = 0; s_mine = 0; s_over = 0; }
     __syncthreads();
     const int ty0 = c.y0 / RAST_TILE, ty1 = c.y1 / RAST_TILE;
     unsigned touched = 0, mine = 0;
@@ -232,7 +264,7 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
       int ta, tb;
       if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
       touched += (unsigned)(tb - ta + 1);
-      if (fa.nranks == 1) mine += (unsigned)(tb - ta + 1);
+      if (fa.nranks == 1 || fa.x.sharded) mine += (unsigned)(tb - ta + 1);
       else for (int tx = ta; tx <= tb; ++tx) mine += rast_dest(fa, tx, ty) >= 0 ? 1u : 0u;
     }
     if (touched) atomicAdd(&s_touched, touched);
@@ -247,24 +279,90 @@ __global__ void __launch_bounds__(RAST_BIG_THREADS) k_rast_big(const DevScene sc
       const double work = fmin(c.R.work, rect) * (double)all_mine / (double)all_touched + 32.0 * (double)all_mine;
       atomicAdd(reinterpret_cast<unsigned long long *>(rast + 2), (unsigned long long)fmin(work, 1.0e15));
     }
-    const int nd = fa.x.sharded ? fa.nranks : 1;
-    for (int ty = ty0 + (int)threadIdx.x; ty <= ty1; ty += RAST_BIG_THREADS) {
-      int ta, tb;
-      if (!region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, ty, ta, tb)) continue;
-      const int cy0 = max(c.y0, ty * RAST_TILE), cy1 = min(c.y1, ty * RAST_TILE + RAST_TILE - 1);
-      // the row's tiles per destination: slots with one atomic per destination, then the items
-      for (int q = 0; q < nd; ++q) {
-        unsigned n = 0;
-        for (int tx = ta; tx <= tb; ++tx) n += rast_dest(fa, tx, ty) == q ? 1u : 0u;
-        if (!n) continue;
-        unsigned k = atomicAdd(&rast[8 + q], n);
-        if (k + n > fa.x.cap) { rast[1] = 1u; continue; }
-        for (int tx = ta; tx <= tb; ++tx)
-          if (rast_dest(fa, tx, ty) == q) {
-            const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
-            rast_store(fa, q, k++, s, cx0, cy0, cx1, cy1, c.rec.v);
-          }
+    for (int r0 = ty0; r0 <= ty1; r0 += RAST_BIG_ROWS) {
+      const int nrows = min(RAST_BIG_ROWS, ty1 - r0 + 1);
+      for (int i = (int)threadIdx.x; i < nrows; i += RAST_BIG_THREADS) {
+        int ta = 0, tb = -1;
+        const bool ok = region::primary_row_tiles(c, fa.cam.W, fa.cam.H, RAST_TILE, r0 + i, ta, tb);
+        s_ta[i] = ta;
+        s_off[i] = ok ? (unsigned)(tb - ta + 1) : 0u;
       }
+      __syncthreads();
+      if (warp == 0) {                          // exclusive prefix sum over the rows: 16 consecutive rows per lane
+        constexpr int PER = RAST_BIG_ROWS / 32;
+        unsigned v[PER], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) { const int i = lane * PER + k; v[k] = i < nrows ? s_off[i] : 0u; sum += v[k]; }
+        unsigned incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const unsigned o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+        unsigned base = incl - sum;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) { const int i = lane * PER + k; if (i < nrows) s_off[i] = base; base += v[k]; }
+        if (lane == 31) s_total = incl;
+      }
+      __syncthreads();
+      const unsigned total = s_total;
+      // one rank: every tile is emitted, so the pass takes its slots with a single atomic
+      if (fa.nranks == 1) {
+        if (threadIdx.x == 0) s_touched = atomicAdd(&rast[8], total);
+        __syncthreads();
+        const unsigned base = s_touched;
+        if (base + total > fa.x.cap) { if (threadIdx.x == 0) rast[1] = 1u; return; }
+        for (unsigned i = threadIdx.x; i < total; i += RAST_BIG_THREADS) {
+          int lo = 0, hi = nrows - 1;
+          while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_off[mid] <= i) lo = mid; else hi = mid - 1; }
+          const int tx = s_ta[lo] + (int)(i - s_off[lo]), ty = r0 + lo;
+          const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
+          const int cy0 = max(c.y0, ty * RAST_TILE), cy1 = min(c.y1, ty * RAST_TILE + RAST_TILE - 1);
+          rast_store(fa, 0, base + i, s, cx0, cy0, cx1, cy1, c.rec.v);
+        }
+        __syncthreads();
+        continue;
+      }
+      // several destinations (or only the owned tiles): count per destination, take the slots with one atomic
+      // per destination, then hand them out through shared counters
+      if (threadIdx.x < XCHG_MAX_RANKS) s_cnt[threadIdx.x] = 0u;
+      __syncthreads();
+      for (int pass = 0; pass < 2; ++pass) {
+        for (unsigned i0 = 0; i0 < total; i0 += RAST_BIG_THREADS) {
+          const unsigned i = i0 + threadIdx.x;
+          int q = -1, tx = 0, ty = 0;
+          if (i < total) {
+            int lo = 0, hi = nrows - 1;            // the last row whose offset is <= i (rows without tiles share offsets)
+            while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if (s_off[mid] <= i) lo = mid; else hi = mid - 1; }
+            tx = s_ta[lo] + (int)(i - s_off[lo]); ty = r0 + lo;
+            q = rast_dest(fa, tx, ty);
+          }
+          for (int d = 0; d < nd; ++d) {
+            const unsigned m = __ballot_sync(0xffffffffu, q == d);
+            if (!m) continue;
+            const int leader = __ffs(m) - 1;
+            unsigned k = 0;
+            if (lane == leader) k = atomicAdd(&s_cnt[d], (unsigned)__popc(m));
+            if (pass == 0) continue;
+            k = __shfl_sync(0xffffffffu, k, leader);
+            if (q == d) {
+              const int cx0 = max(c.x0, tx * RAST_TILE), cx1 = min(c.x1, tx * RAST_TILE + RAST_TILE - 1);
+              const int cy0 = max(c.y0, ty * RAST_TILE), cy1 = min(c.y1, ty * RAST_TILE + RAST_TILE - 1);
+              rast_store(fa, d, s_pos[d] + k + (unsigned)__popc(m & ((1u << lane) - 1u)), s, cx0, cy0, cx1, cy1, c.rec.v);
+            }
+          }
+        }
+        __syncthreads();
+        if (pass == 0) {
+          if ((int)threadIdx.x < nd) {
+            const unsigned n = s_cnt[threadIdx.x];
+            unsigned base = n ? atomicAdd(&rast[8 + threadIdx.x], n) : 0u;
+            if (base + n > fa.x.cap) { rast[1] = 1u; s_over = 1u; }
+            s_pos[threadIdx.x] = base;
+            s_cnt[threadIdx.x] = 0u;
+          }
+          __syncthreads();
+          if (s_over) return;
+        }
+      }
+      __syncthreads();
     }
   }
 }

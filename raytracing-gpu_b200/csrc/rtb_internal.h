@@ -117,10 +117,12 @@ struct FrameArgs {
   // and where to leave each item's cost, in 256-cycle units (nullptr = not recorded)
   const unsigned int *item_order;
   unsigned int *item_cost;        // per item, 256-cycle units (fine items: summed over the item's rounds)
-  // fine work items of multi-rank frames (k_frame<.., FINE>): per output pixel the channel sums of its samples,
-  // per item the number of finished rounds; nullptr: one warp does all rounds of an item (sums in shared memory)
+  // hot tiles as fine work items (k_frame<.., FINE>): per output pixel the channel sums of its samples, per
+  // item the number of finished rounds (both zero between frames: the resolving warp clears them), and how
+  // many leading entries of item_order are hot; nullptr: one warp does all rounds of every item
   uint2 *fine_acc;
   unsigned int *fine_done;
+  const unsigned int *fine_hot;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
   // primary visibility by projection (raster.cuh); prim == nullptr: every ray walks the tree
   unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
@@ -150,14 +152,14 @@ int dev_inclusive_scan_u64(uint64_t *d_data, size_t n, uint64_t *d_scratch, size
 size_t scan_scratch_words(size_t n);
 
 // ---- frame kernels (trace.cu) ----
-// marks: nullptr, or 4 events recorded before the frame's first operation, after k_rast_setup, after
-// k_rast_items and after the frame kernel (rtb_scene_profile)
+// marks: nullptr, or 6 events recorded before the frame's first operation, after k_rast_setup, after k_rast_big,
+// after k_xchg_sync, after k_rast_items and after the frame kernel (rtb_scene_profile)
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches, cudaEvent_t *marks = nullptr);
 unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
 int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
-                      cudaStream_t st, int *result_in_alt);
+                      cudaStream_t st, int *result_in_alt, unsigned *d_hot, float per_share);
 int launch_hit_ids(const DevScene &sc, const DevCamera &cam, int tracer, int32_t *d_tri, int32_t *d_obj,
                    cudaStream_t st);
 int launch_prim_ids(const DevScene &sc, const FrameArgs &fa, int32_t *d_tri, int32_t *d_obj, int sm_count, cudaStream_t st);

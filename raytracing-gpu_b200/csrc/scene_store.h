@@ -11,7 +11,7 @@ struct SceneStore {
   cudaEvent_t tev0 = nullptr, tev1 = nullptr;   // bracket timer (rtb_scene_timer_*)
   int sm_count = 148;
   bool profile = false;                         // rtb_scene_profile: events between the frame's kernels
-  cudaEvent_t kev[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t kev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 
   float4 *v0 = nullptr, *e1 = nullptr, *e2 = nullptr, *n0 = nullptr, *n1 = nullptr, *n2 = nullptr;
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;

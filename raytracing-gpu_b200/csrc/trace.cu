@@ -394,21 +394,26 @@ __device__ __forceinline__ bool frame_item(const FrameArgs &fa, unsigned item, i
 #ifndef RTB_FRAME_MINBLOCKS
 #define RTB_FRAME_MINBLOCKS 8
 #endif
-// FINE (multi-rank frames): a work item is ONE round of 32 samples of a warp tile, the sums go to a global
-// accumulator with atomics and the warp that finishes a tile's last round resolves it.  With 1/N of the
-// tiles per rank the slowest tile sets the frame's tail (a tile over a cell of a light grid that hundreds of
-// line regions cross takes milliseconds); cut into a x a rounds taken by different warps it no longer does.
+// FINE: the leading *fa.fine_hot entries of the item order (the tiles whose cost in the previous frame was
+// above a quarter of a warp's fair share of the frame, launch_item_order) are cut into their a x a rounds of
+// 32 samples, one work item each: the sums go to a global accumulator with atomics and the warp that finishes
+// a tile's last round resolves it and leaves accumulator and counter zero for the next frame.  With 1/N of
+// the tiles per rank the slowest tile sets the frame's tail (a tile over a cell of a light grid that hundreds
+// of line regions cross takes milliseconds); cut into rounds taken by different warps it no longer does.
+// Every other tile stays whole: its rounds share one SM's L1 (all tiles as rounds cost 19 % at any N).
 template <int TRACER, bool COUNT, bool FINE>
 __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
   // Per output pixel of the warp tile: the channel sums of its a x a samples (x: r | g << 16,
   // y: b).  The reference sums the u8 channels as floats (gpu/raytracer.cu:62-70); sums of at
   // most 256 values below 256 are exact in either arithmetic, so integers give the same bits.
   // 1 KB per CTA whatever the aliasing, which leaves the unified L1 its largest share.
-  __shared__ uint2 s_acc[FINE ? 1 : FRAME_WARPS][32];
+  __shared__ uint2 s_acc[FRAME_WARPS][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = fa.aliasing, aa = a * a;
-  uint2 *acc = s_acc[FINE ? 0 : warp];
-  const unsigned total = frame_items(fa) * (FINE ? (unsigned)aa : 1u);
+  uint2 *acc = s_acc[warp];
+  const unsigned n_items = frame_items(fa);
+  const unsigned hot = FINE && fa.item_order ? min(__ldg(fa.fine_hot), n_items) : 0u;
+  const unsigned n_fine = hot * (unsigned)aa, total = n_items + hot * (unsigned)(aa - 1);
   const bool use_prim = TRACER == RTB_TRACER_TREE && !COUNT && rast_active(fa);
   Counters c = {0, 0, 0, 0, 0};
   for (;;) {
@@ -417,50 +422,54 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
     t = __shfl_sync(0xffffffffu, t, 0);
     if (t >= total) break;
     // items are taken in the order of the previous frame's cost, longest first (api.cu); the rounds of a
-    // fine item are consecutive, so different warps take them at about the same time
-    const unsigned ti = FINE ? t / (unsigned)aa : t;
-    const int q0 = FINE ? (int)(t - ti * (unsigned)aa) : 0, q1 = FINE ? q0 + 1 : aa;
+    // hot tile are consecutive, so different warps take them at about the same time
+    const bool fine = FINE && t < n_fine;
+    const unsigned ti = fine ? t / (unsigned)aa : t - (n_fine - hot);
+    const int q0 = fine ? (int)(t - ti * (unsigned)aa) : 0, q1 = fine ? q0 + 1 : aa;
     const unsigned item = fa.item_order ? __ldg(fa.item_order + ti) : ti;
     int lx0, ly0;
-    const bool inside = frame_item(fa, item, lx0, ly0);
-    if (!inside && !FINE) continue;
+    if (!frame_item(fa, item, lx0, ly0)) continue;
     long long t_start = 0;
     if (fa.item_cost && lane == 0) t_start = clock64();
-    if (!FINE) {
+    if (!fine) {
       acc[lane] = make_uint2(0u, 0u);
       __syncwarp();
     }
-    if (inside)
-      for (int q = q0; q < q1; ++q) {
-        const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
-        const int px = a * lx0 + sx, py = a * ly0 + sy;
-        if (px < fa.cam.W && py < fa.cam.H) {
-          const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
-          uint2 *dst = FINE ? fa.fine_acc + (size_t)(ly0 + sy / a) * fa.out_w + (lx0 + sx / a) : acc + (sy / a) * 8 + sx / a;
-          atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
-          atomicAdd(&dst->y, ch_b(col));
-        }
+    for (int q = q0; q < q1; ++q) {
+      const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
+      const int px = a * lx0 + sx, py = a * ly0 + sy;
+      if (px < fa.cam.W && py < fa.cam.H) {
+        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
+        uint2 *dst = fine ? fa.fine_acc + (size_t)(ly0 + sy / a) * fa.out_w + (lx0 + sx / a) : acc + (sy / a) * 8 + sx / a;
+        atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
+        atomicAdd(&dst->y, ch_b(col));
       }
-    bool resolve = !FINE;
-    if (FINE) {
-      // the last round of the item to finish resolves it: sums first (atomics at L2), then the count
+    }
+    bool resolve = true;
+    if (fine) {
+      // the last round of the tile to finish resolves it: sums first (atomics at L2), then the count
       __threadfence();
       __syncwarp();
       unsigned before = 0;
       if (lane == 0) before = atomicAdd(fa.fine_done + item, 1u);
       before = __shfl_sync(0xffffffffu, before, 0);
-      resolve = inside && before == (unsigned)aa - 1u;
+      resolve = before == (unsigned)aa - 1u;
       if (resolve) __threadfence();
     } else __syncwarp();
     if (fa.item_cost && lane == 0) {
       const unsigned dt = (unsigned)((clock64() - t_start) >> 8);
-      if (FINE) atomicAdd(fa.item_cost + item, dt); else fa.item_cost[item] = dt;
+      if (fine) atomicAdd(fa.item_cost + item, dt); else fa.item_cost[item] = dt;
     }
     if (!resolve) continue;
     // downscale kernel body (gpu/raytracer.cu:49-85) for this lane's output pixel
     const int lx = lx0 + (lane & 7), ly = ly0 + (lane >> 3);
     if (lx < fa.out_w && ly < fa.out_h) {
-      const uint2 sum = FINE ? __ldcg(fa.fine_acc + (size_t)ly * fa.out_w + lx) : acc[lane];
+      uint2 sum = acc[lane];
+      if (fine) {
+        uint2 *g = fa.fine_acc + (size_t)ly * fa.out_w + lx;
+        sum = __ldcg(g);
+        __stcg(g, make_uint2(0u, 0u));
+      }
       float r = (float)(sum.x & 0xffffu), g = (float)(sum.x >> 16), b = (float)sum.y;
       const float ali2 = 255.0f * (float)a * (float)a;
       r /= ali2;
@@ -470,7 +479,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       unsigned char *dst = fa.out + (long long)(fa.out_h - ly - 1) * fa.pitch + 4ll * (fa.out_w - lx - 1);
       *reinterpret_cast<uint32_t *>(dst) = e;
     }
-    if (!FINE) __syncwarp();
+    if (fine && lane == 0) fa.fine_done[item] = 0u;
+    __syncwarp();
   }
   if (COUNT) {
     unsigned v[5] = {c.primary, c.shadow, c.bounce, c.nodes, c.tris};
@@ -776,20 +786,23 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
     else RTB_CUDA(cudaMemsetAsync(fa.prim, 0xff, (size_t)fa.cam.W * fa.cam.H * 8, st));
     RTB_CUDA(cudaMemsetAsync(fa.rast, 0, RAST_STATE_WORDS * 4, st));
     if (sc.n_tris) {
-      const unsigned share = fa.x.sharded ? sc.n_tris / (unsigned)fa.nranks + 1u : sc.n_tris;
-      k_rast_setup<<<(share + 255) / 256, 256, 0, st>>>(sc, fa);
+      const unsigned blocks = (sc.n_tris + 255) / 256;
+      k_rast_setup<<<fa.x.sharded ? (blocks + fa.nranks - 1) / fa.nranks : blocks, 256, 0, st>>>(sc, fa);
+      if (marks) RTB_CUDA(cudaEventRecord(marks[1], st));
       k_rast_big<<<sm_count * 8, RAST_BIG_THREADS, 0, st>>>(sc, fa);
-    }
+      if (marks) RTB_CUDA(cudaEventRecord(marks[2], st));
+    } else if (marks) { RTB_CUDA(cudaEventRecord(marks[1], st)); RTB_CUDA(cudaEventRecord(marks[2], st)); }
     // sharded frames: counts and epoch to every rank, wait for theirs (the items went over NVLink already)
     if (fa.x.sharded) k_xchg_sync<<<1, 32, 0, st>>>(fa);
-    if (marks) RTB_CUDA(cudaEventRecord(marks[1], st));
+    if (marks) RTB_CUDA(cudaEventRecord(marks[3], st));
     if (sc.n_tris) k_rast_items<<<sm_count * 8, 256, 0, st>>>(sc, fa);
     RTB_CUDA(cudaGetLastError());
     if (launches) *launches = fa.x.sharded ? 5 : 4;
-  } else if (marks) RTB_CUDA(cudaEventRecord(marks[1], st));
-  if (marks) RTB_CUDA(cudaEventRecord(marks[2], st));
+  } else if (marks)
+    for (int k = 1; k <= 3; ++k) RTB_CUDA(cudaEventRecord(marks[k], st));
+  if (marks) RTB_CUDA(cudaEventRecord(marks[4], st));
   const int rc = launch_frame_kernel(sc, fa, tracer, count, sm_count, st);
-  if (!rc && marks) RTB_CUDA(cudaEventRecord(marks[3], st));
+  if (!rc && marks) RTB_CUDA(cudaEventRecord(marks[5], st));
   return rc;
 }
 
@@ -802,11 +815,7 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);
   if (count) return launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st);
-  if (fa.fine_acc) {
-    RTB_CUDA(cudaMemsetAsync(fa.fine_acc, 0, (size_t)fa.out_w * fa.out_h * sizeof(uint2), st));
-    RTB_CUDA(cudaMemsetAsync(fa.fine_done, 0, (size_t)frame_item_count(fa.out_w, fa.out_h, fa.nranks) * 4, st));
-    return launch_frame_t<RTB_TRACER_TREE, false, true>(sc, fa, sm_count, st);
-  }
+  if (fa.fine_acc) return launch_frame_t<RTB_TRACER_TREE, false, true>(sc, fa, sm_count, st);
   return launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
 }
 
@@ -817,13 +826,41 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
 #ifndef RTB_COST_CLASSES_PER_OCTAVE
 #define RTB_COST_CLASSES_PER_OCTAVE 2
 #endif
+__device__ __forceinline__ int cost_class(unsigned cost) {      // 0 .. 24 * classes per octave
+  return (int)((float)RTB_COST_CLASSES_PER_OCTAVE * log2f((float)min(cost, 0xffffffu) + 1.0f));
+}
+
+// hot[0..1]: sum of the costs (u64); hot[2]: items in a class above that of the threshold (k_item_hot)
 __global__ void __launch_bounds__(256) k_item_keys(const unsigned int *cost, unsigned n, uint64_t *keys,
-                                                   uint32_t *vals) {
+                                                   uint32_t *vals, unsigned *hot) {
+  __shared__ unsigned long long s_sum;
+  if (threadIdx.x == 0) s_sum = 0ull;
+  __syncthreads();
   const unsigned i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= n) return;
-  const int cls = (int)((float)RTB_COST_CLASSES_PER_OCTAVE * log2f((float)min(cost[i], 0xffffffu) + 1.0f));   // 0 .. 16 * classes
-  keys[i] = (uint64_t)(255 - min(cls, 255));   // ascending sort = heaviest class first; empty items (cost 0) last
-  vals[i] = i;
+  unsigned long long mine = 0;
+  if (i < n) {
+    const unsigned c = cost[i];
+    mine = c;
+    keys[i] = (uint64_t)(255 - min(cost_class(c), 255));   // ascending sort = heaviest class first; empty items (cost 0) last
+    vals[i] = i;
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&s_sum, mine);
+  __syncthreads();
+  if (threadIdx.x == 0 && s_sum) atomicAdd(reinterpret_cast<unsigned long long *>(hot), s_sum);
+}
+
+// hot tiles: cost class above the class of (sum of costs / resident warps) / hot_div -- a tile that keeps one
+// warp for more than 1 / hot_div of the time the frame takes when every warp gets the same share.  They are
+// a prefix of the sorted order (whole classes).
+__global__ void __launch_bounds__(256) k_item_hot(const unsigned int *cost, unsigned n, unsigned *hot, float per_share) {
+  const unsigned i = blockIdx.x * 256 + threadIdx.x;
+  const float sum = (float)*reinterpret_cast<const unsigned long long *>(hot);
+  const int cls_t = cost_class((unsigned)fminf(sum * per_share, 16777215.0f));
+  const bool is_hot = i < n && cost[i] > 0u && cost_class(cost[i]) > cls_t;
+  const unsigned m = __ballot_sync(0xffffffffu, is_hot);
+  if ((threadIdx.x & 31) == 0 && m) atomicAdd(hot + 2, (unsigned)__popc(m));
 }
 
 unsigned frame_item_count(int out_w, int out_h, int nranks) {
@@ -833,8 +870,10 @@ unsigned frame_item_count(int out_w, int out_h, int nranks) {
 
 int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
-                      cudaStream_t st, int *result_in_alt) {
-  k_item_keys<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_keys, d_vals);
+                      cudaStream_t st, int *result_in_alt, unsigned *d_hot, float per_share) {
+  RTB_CUDA(cudaMemsetAsync(d_hot, 0, 4 * sizeof(unsigned), st));
+  k_item_keys<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_keys, d_vals, d_hot);
+  if (per_share > 0.0f) k_item_hot<<<(n + 255) / 256, 256, 0, st>>>(d_cost, n, d_hot, per_share);
   RTB_CUDA(cudaGetLastError());
   return dev_radix_sort_pairs_u64(d_keys, d_vals, d_keys_alt, d_vals_alt, n, 8, d_scratch, scratch_words, st,
                                   result_in_alt, nullptr);

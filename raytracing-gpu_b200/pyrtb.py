@@ -426,8 +426,9 @@ class DeviceScene:
         _check(fn(self.h, int(on)))
 
     def kernel_ms(self):
-        """(clears + k_rast_setup, k_rast_items, frame kernel, whole frame) of the last profiled frame"""
-        out = (C.c_double * 4)()
+        """(setup phase, k_rast_items, frame kernel, whole frame, then the parts of the setup phase: clears +
+        k_rast_setup, k_rast_big, k_xchg_sync, 0) of the last profiled frame, ms"""
+        out = (C.c_double * 8)()
         fn = lib().rtb_scene_kernel_ms
         fn.argtypes = [C.c_void_p, C.c_void_p]
         _check(fn(self.h, out))
