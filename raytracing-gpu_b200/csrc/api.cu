@@ -313,6 +313,45 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     }
     fa.fine_acc = S.d_fine_acc; fa.fine_done = S.d_fine_done; fa.fine_hot = d_hot + 2;
   }
+  // Experiment: RTB_L2_PERSIST=<array>:<MB> pins part of one array in L2 for the frame's stream
+  // (cudaAccessPolicyWindow, persisting hits / streaming misses).  Arrays: prim, nodes, tris, rec<g>, cells<g>, entries<g>.
+  static const char *l2p = getenv("RTB_L2_PERSIST");
+  if (l2p && *l2p) {
+    const char *colon = strchr(l2p, ':');
+    const size_t mb = colon ? (size_t)atoi(colon + 1) : 32;
+    const void *ptr = nullptr; size_t bytes = 0;
+    auto grid = [&](int which, const char *digit) {
+      const int g = (*digit >= '0' && *digit <= '7') ? *digit - '0' : 0;
+      ptr = S.lgrid_mem[3 * g + which]; bytes = S.lgrid_mem_bytes[3 * g + which];
+    };
+    if (!strncmp(l2p, "prim", 4)) { ptr = fa.prim; bytes = (size_t)fa.cam.W * fa.cam.H * 8; }
+    else if (!strncmp(l2p, "nodes", 5)) { ptr = S.nodes; bytes = (size_t)S.n_nodes * NODE_QUADS * 16; }
+    else if (!strncmp(l2p, "tris", 4)) { ptr = S.v0; bytes = (size_t)S.n_tris * 16; }
+    else if (!strncmp(l2p, "rec", 3)) grid(0, l2p + 3);
+    else if (!strncmp(l2p, "cells", 5)) grid(1, l2p + 5);
+    else if (!strncmp(l2p, "entries", 7)) grid(2, l2p + 7);
+    if (ptr && bytes) {
+      cudaDeviceProp prop;
+      RTB_CUDA(cudaGetDeviceProperties(&prop, S.device));
+      const size_t want = mb << 20, cap = (size_t)prop.persistingL2CacheMaxSize;
+      RTB_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want < cap ? want : cap));
+      cudaStreamAttrValue v;
+      memset(&v, 0, sizeof v);
+      v.accessPolicyWindow.base_ptr = const_cast<void *>(ptr);
+      v.accessPolicyWindow.num_bytes = bytes < (size_t)prop.accessPolicyMaxWindowSize ? bytes : (size_t)prop.accessPolicyMaxWindowSize;
+      v.accessPolicyWindow.hitRatio = (float)fmin(1.0, (double)(want < cap ? want : cap) / (double)v.accessPolicyWindow.num_bytes);
+      v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+      v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+      RTB_CUDA(cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v));
+      static bool said = false;
+      if (!said) {
+        said = true;
+        fprintf(stderr, "[rtb200] L2 window on %s: %zu of %zu bytes, hit ratio %.3f, persisting L2 %zu MB (device max %d MB, max window %d MB)\n", l2p,
+                (size_t)v.accessPolicyWindow.num_bytes, bytes, v.accessPolicyWindow.hitRatio, (want < cap ? want : cap) >> 20,
+                prop.persistingL2CacheMaxSize >> 20, prop.accessPolicyMaxWindowSize >> 20);
+      }
+    }
+  }
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   if (S.profile && !S.kev[0])
     for (cudaEvent_t &e : S.kev) RTB_CUDA(cudaEventCreate(&e));
@@ -444,7 +483,13 @@ int rtb_device_count(void) {
   return n;
 }
 
+static int scene_create_impl(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out, UploadGroup *grp, int member);
+
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out) {
+  return scene_create_impl(scene, device, flags, out, nullptr, 0);
+}
+
+static int scene_create_impl(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out, UploadGroup *grp, int member) {
   if (!out) { set_error("out is NULL"); return RTB_ERR_ARG; }
   *out = nullptr;
   const char *tr = getenv("RTB_TRACE");
@@ -460,7 +505,7 @@ int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_
   rc = acquire_frame_ctx(device, S);
   if (rc) { delete h; return rc; }
   const auto t2 = clk::now();
-  rc = build_scene(scene, flags, &S);
+  rc = build_scene(scene, flags, &S, grp, member);
   if (rc) { delete h; return rc; }
   if (trace) {
     auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
@@ -605,18 +650,49 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
   const bool trace = tr && *tr == '1';
   using clk = std::chrono::steady_clock;
   const auto t_start = clk::now();
+  // shared upload (UploadGroup, scene_store.h): device 0 reads the host, the others read device 0; RTB_SHARED_UPLOAD=0: A/B
+  UploadGroup grp;
+  grp.n = n_devices;
+  const char *su = getenv("RTB_SHARED_UPLOAD");
+  bool share_upload = n_devices <= 8 && !(su && *su == '0');
+  for (int b = 1; b < n_devices && share_upload; ++b) {
+    int can = 0;
+    if (cudaDeviceCanAccessPeer(&can, b, 0) != cudaSuccess || !can) share_upload = false;
+  }
+  cudaGetLastError();
+  for (int dev = 0; dev < n_devices && dev < 8; ++dev) grp.device[dev] = dev;
+  struct GroupGuard {
+    UploadGroup &g;
+    ~GroupGuard() {
+      cudaSetDevice(0);
+      if (g.ready_v) cudaEventDestroy(g.ready_v);
+      if (g.ready_n) cudaEventDestroy(g.ready_n);
+      if (g.src_v) cudaFree(g.src_v);
+      if (g.src_n) cudaFree(g.src_n);
+    }
+  } group_guard{grp};
+  if (share_upload) {
+    const size_t raw = 36ull * (scene->triangle_count ? scene->triangle_count : 1);
+    RTB_CUDA(cudaMalloc((void **)&grp.src_v, raw));
+    RTB_CUDA(cudaMalloc((void **)&grp.src_n, raw));
+    RTB_CUDA(cudaEventCreateWithFlags(&grp.ready_v, cudaEventDisableTiming));
+    RTB_CUDA(cudaEventCreateWithFlags(&grp.ready_n, cudaEventDisableTiming));
+  }
   for (int dev = 0; dev < n_devices; ++dev)
     workers.emplace_back([&, dev] {
       auto ms = [&](clk::time_point b) { return std::chrono::duration<double, std::milli>(b - t_start).count(); };
       const auto t0 = clk::now();
       rtb_scene_t *h = nullptr;
-      int r = rtb_scene_create(scene, dev, RTB_BUILD_ONE_FRAME, &h);
-      const auto t1 = clk::now();
+      // every device reads the scene from device 0 (UploadGroup) and stores its pixels into device 0's frame
+      int r = pick_device(dev);
       if (!r && dev != 0) {
         const cudaError_t e = cudaDeviceEnablePeerAccess(0, 0);
         if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) r = cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
         cudaGetLastError();
       }
+      if (!r) r = scene_create_impl(scene, dev, RTB_BUILD_ONE_FRAME, &h, share_upload ? &grp : nullptr, dev);
+      if (r) grp.fail();
+      const auto t1 = clk::now();
       const auto t2 = clk::now();
       if (!r) {
         rtb_frame_opts o;

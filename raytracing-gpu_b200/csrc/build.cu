@@ -842,7 +842,7 @@ float camera_origin_radius(const struct camera &cm) {
   return (float)(pm + fabs(L) + 0.5 * (abs(cm.width) + abs(cm.height)));
 }
 
-int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
+int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGroup *grp, int member) {
   if (!hs) { set_error("scene is NULL"); return RTB_ERR_ARG; }
   const size_t n_obj = hs->object_count, n_light = hs->light_count;
   if (n_obj && !hs->objects) { set_error("object_count > 0 but objects is NULL"); return RTB_ERR_ARG; }
@@ -898,10 +898,15 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
   RTB_CUDA(cudaEventRecord(e_up0, st));
   float *raw_v = nullptr, *raw_n = nullptr;
   uint32_t *d_first = nullptr;
-  CK(tmp.alloc(&raw_v, 9ull * n));
-  CK(tmp.alloc(&raw_n, 9ull * n));
+  if (grp && member == 0) { raw_v = grp->src_v; raw_n = grp->src_n; }      // shared upload (UploadGroup, scene_store.h)
+  else {
+    CK(tmp.alloc(&raw_v, 9ull * n));
+    CK(tmp.alloc(&raw_n, 9ull * n));
+  }
   CK(tmp.alloc(&d_first, n_obj + 1));
   // objects whose arrays are adjacent in host memory (the SoA scene) go up in one copy
+  struct Run { const vector3 *pv, *pn; size_t first, tri; };
+  std::vector<Run> runs;
   for (size_t o = 0; o < n_obj;) {
     size_t e = o;
     const vector3 *pv = hs->objects[o].triangles.vertex, *pn = hs->objects[o].triangles.normal;
@@ -911,19 +916,41 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S) {
       ++e;
       tri += hs->objects[e].triangle_count;
     }
-    if (tri) {
-      RTB_CUDA(cudaMemcpyAsync(raw_v + 9ull * first[o], pv, 36ull * tri, cudaMemcpyHostToDevice, st));
-      if (overlap) normal_spans.push_back({pn, first[o], tri});
-      else RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * first[o], pn, 36ull * tri, cudaMemcpyHostToDevice, st));
-    }
+    if (tri) runs.push_back({pv, pn, first[o], tri});
     o = e + 1;
+  }
+  const bool fetch = grp && member != 0;      // the arrays come from member 0's device, not from the host
+  if (!fetch)
+    for (const Run &r : runs) {
+      RTB_CUDA(cudaMemcpyAsync(raw_v + 9ull * r.first, r.pv, 36ull * r.tri, cudaMemcpyHostToDevice, st));
+      if (overlap) normal_spans.push_back({r.pn, r.first, r.tri});
+      else RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * r.first, r.pn, 36ull * r.tri, cudaMemcpyHostToDevice, st));
+    }
+  else {
+    if (!grp->barrier()) { set_error("device %d of the call failed during the upload", grp->device[0]); return RTB_ERR_CUDA; }
+    RTB_CUDA(cudaStreamWaitEvent(st, grp->ready_v, 0));
+    RTB_CUDA(cudaMemcpyPeerAsync(raw_v, grp->device[member], grp->src_v, grp->device[0], 36ull * n, st));
+    if (!overlap) {
+      RTB_CUDA(cudaStreamWaitEvent(st, grp->ready_n, 0));
+      RTB_CUDA(cudaMemcpyPeerAsync(raw_n, grp->device[member], grp->src_n, grp->device[0], 36ull * n, st));
+    }
   }
   if (overlap) {
     RTB_CUDA(cudaEventRecord(side.verts, st));               // also orders raw_n's allocation before its use
     RTB_CUDA(cudaStreamWaitEvent(side.st, side.verts, 0));   // vertices first: they gate the build
     for (const Span &sp : normal_spans)
       RTB_CUDA(cudaMemcpyAsync(raw_n + 9ull * sp.first, sp.src, 36ull * sp.tri, cudaMemcpyHostToDevice, side.st));
+    if (fetch) {
+      RTB_CUDA(cudaStreamWaitEvent(side.st, grp->ready_n, 0));
+      RTB_CUDA(cudaMemcpyPeerAsync(raw_n, grp->device[member], grp->src_n, grp->device[0], 36ull * n, side.st));
+    }
     RTB_CUDA(cudaEventRecord(side.normals, side.st));
+  }
+  if (grp && member == 0) {
+    // the peers may start: vertices are behind ready_v on the build stream, normals behind ready_n
+    RTB_CUDA(cudaEventRecord(grp->ready_v, st));
+    RTB_CUDA(cudaEventRecord(grp->ready_n, overlap ? side.st : st));
+    if (!grp->barrier()) { set_error("a device of the call failed during the upload"); return RTB_ERR_CUDA; }
   }
   RTB_CUDA(cudaMemcpyAsync(d_first, first.data(), (n_obj + 1) * 4, cudaMemcpyHostToDevice, st));
   std::vector<float> mat(8 * (n_obj ? n_obj : 1), 0.0f);

@@ -270,6 +270,34 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
   const float qx = (fx - fi) * LG_Q, qy = (fy - fj) * LG_Q;
   auto byte = [](float v) { return (uint32_t)fminf(fmaxf(v, 0.0f), LG_Q); };
   const uint32_t P = (byte(floorf(qx)) | ((127u - byte(ceilf(qx))) << 8) | (byte(floorf(qy)) << 16) | ((127u - byte(ceilf(qy))) << 24)) | 0x80808080u;
+#ifdef RTB_LG_WHILE_WHILE      /* A/B only: measured 16.6 ms against 13.3 ms for k_frame on C5 */
+  // "while-while": every lane runs through its list (rectangle words of 32 entries at a time, records of the
+  // survivors) until it holds ONE candidate, then the lanes that hold one run the exact test together
+  uint32_t base = e0, cur = e0, m = 0;
+  for (;;) {
+    int cand = -1;
+    for (;;) {
+      if (!m) {
+        if (base >= e1) break;
+        const uint32_t cnt = min(32u, e1 - base);
+#pragma unroll 4
+        for (uint32_t k = 0; k < cnt; ++k) {
+          const uint32_t r = __ldg(&g.entries[base + k].y);
+          if (((P - r) & 0x80808080u) == 0x80808080u) m |= 1u << k;
+        }
+        cur = base; base += 32;
+        continue;
+      }
+      const uint32_t k = (uint32_t)__ffs((int)m) - 1u;
+      m &= m - 1u;
+      const uint32_t s = __ldg(&g.entries[cur + k].x);
+      const float4 r0 = __ldg(g.rec + 4 * (size_t)s), r1 = __ldg(g.rec + 4 * (size_t)s + 1), r2 = __ldg(g.rec + 4 * (size_t)s + 2);
+      if (region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, x - r2.y, y - r2.z)) { cand = (int)s; break; }
+    }
+    if (cand < 0) break;
+    if (consider<true>(sc, o, d, cand, b)) return 1;
+  }
+#else
   for (uint32_t base = e0; base < e1; base += 32) {
     const uint32_t cnt = min(32u, e1 - base);
     uint32_t mask = 0;
@@ -292,6 +320,7 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
       if (consider<true>(sc, o, d, (int)__ldg(&g.entries[base + k].x), b)) return 1;
     }
   }
+#endif
   return 0;
 }
 

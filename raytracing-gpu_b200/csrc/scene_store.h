@@ -1,5 +1,7 @@
 // The resident scene behind rtb_scene_t: every device allocation the library owns.
 #pragma once
+#include <condition_variable>
+#include <mutex>
 #include "rtb_internal.h"
 
 namespace rtb {
@@ -17,7 +19,8 @@ struct SceneStore {
   float4 *nodes = nullptr, *materials = nullptr, *lights = nullptr;
   uint32_t *order = nullptr;            // slot -> global triangle id
   LightGrid *lgrids = nullptr;          // device array [n_lights] (lightgrid.cuh)
-  void *lgrid_mem[24] = {nullptr};      // cell_start / entries / edge records of up to 8 grids
+  void *lgrid_mem[24] = {nullptr};      // edge records / cell_start / entries of up to 8 grids
+  size_t lgrid_mem_bytes[24] = {0};
   int n_lgrids = 0;
   unsigned long long lgrid_entries = 0, lgrid_cells = 0;
   float lgrid_margin_k = 0;             // ray-time margin the grids were built for
@@ -94,7 +97,39 @@ struct SceneStore {
   }
 };
 
-int build_scene(const struct scene *hs, unsigned flags, SceneStore *S);
+// rtb_render_multi: the devices of one call share the scene upload.  Member 0 copies the vertex and normal
+// arrays from the host into src_v / src_n (plain cudaMalloc memory on its device, which every peer has mapped
+// for the frame anyway) and builds from them; the other members fetch them from there over NVLink, vertices
+// first, normals on their side stream while the hierarchy is being built.  The host is read once whatever the
+// number of devices: N devices each pulling the whole scene over PCIe queue up on the host's memory and made
+// an 8-device render() three times slower than a 1-device one.
+struct UploadGroup {
+  int n = 0;
+  int device[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float *src_v = nullptr, *src_n = nullptr;           // 9 floats per triangle each, on device[0]
+  cudaEvent_t ready_v = nullptr, ready_n = nullptr;   // recorded by member 0 behind its host copies
+  std::mutex mu;
+  std::condition_variable cv;
+  int arrived = 0;
+  unsigned phase = 0;
+  bool failed = false;
+  // all members arrive (true), or one of them has failed (false, for everybody, from then on)
+  bool barrier() {
+    std::unique_lock<std::mutex> lk(mu);
+    if (failed) return false;
+    const unsigned my = phase;
+    if (++arrived == n) { arrived = 0; ++phase; cv.notify_all(); return true; }
+    cv.wait(lk, [&] { return phase != my || failed; });
+    return !failed;
+  }
+  void fail() {
+    std::lock_guard<std::mutex> lk(mu);
+    failed = true;
+    cv.notify_all();
+  }
+};
+
+int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGroup *grp = nullptr, int member = 0);
 // per-device cache of stream, events and frame buffers (api.cu)
 int acquire_frame_ctx(int device, SceneStore &S);
 void recycle_frame_ctx(SceneStore &S);

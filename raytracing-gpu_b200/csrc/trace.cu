@@ -720,7 +720,9 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
     }
     g.n_large = state[0] < (uint32_t)LG_LARGE_MAX ? state[0] : (uint32_t)LG_LARGE_MAX;
     for (uint32_t k = 0; k < g.n_large; ++k) g.large[k] = state[2 + k];
-    S.lgrid_mem[mem++] = rec; S.lgrid_mem[mem++] = counts; S.lgrid_mem[mem++] = entries;
+    S.lgrid_mem_bytes[mem] = (size_t)sc.n_tris * 64; S.lgrid_mem[mem++] = rec;
+    S.lgrid_mem_bytes[mem] = ((size_t)cells + 1) * 4; S.lgrid_mem[mem++] = counts;
+    S.lgrid_mem_bytes[mem] = (size_t)total * 4; S.lgrid_mem[mem++] = entries;
     S.lgrid_entries += total; S.lgrid_cells += cells;
     grids[i] = g;
     ++built;
