@@ -251,7 +251,7 @@ __global__ void __launch_bounds__(256) k_lg_stats(const uint32_t *cell_start, si
 // instruction 27 instead of 23, but 11.9 G instead of 8.3 G warp-instructions and 18.6 instead of 11.9 ms
 // on C5 -- a record test is ~35 instructions, the queue traffic around it costs more than the idle lanes
 // (profiles/r2_ncu_kframe_coop.txt).
-__device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, const V3 o, const V3 d) {
+__device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, const V3 o, const V3 d, int &hit) {
   if (!(o.x >= g.bmin.x && o.x <= g.bmax.x && o.y >= g.bmin.y && o.y <= g.bmax.y && o.z >= g.bmin.z && o.z <= g.bmax.z)) return -1;
   float x, y, den;
   lg_project(g, o, x, y, den);
@@ -263,7 +263,7 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
   Best b;
   b.dist = INF; b.id = 0x7fffffff; b.slot = -1;
   for (uint32_t k = 0; k < g.n_large; ++k)
-    if (consider<true>(sc, o, d, (int)g.large[k], b)) return 1;
+    if (consider<true>(sc, o, d, (int)g.large[k], b)) { hit = (int)g.large[k]; return 1; }
   const size_t c = (size_t)(int)fj * g.nx + (int)fi;
   const uint32_t e0 = __ldg(g.cell_start + c), e1 = __ldg(g.cell_start + c + 1);
   // the ray's point inside its cell as the four bytes the entries compare with (lg_pack)
@@ -295,7 +295,7 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
       if (region::record_inside(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.w, x - r2.y, y - r2.z)) { cand = (int)s; break; }
     }
     if (cand < 0) break;
-    if (consider<true>(sc, o, d, cand, b)) return 1;
+    if (consider<true>(sc, o, d, cand, b)) { hit = cand; return 1; }
   }
 #else
   for (uint32_t base = e0; base < e1; base += 32) {
@@ -317,7 +317,8 @@ __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, co
     while (mask) {
       const uint32_t k = (uint32_t)__ffs((int)mask) - 1u;
       mask &= mask - 1u;
-      if (consider<true>(sc, o, d, (int)__ldg(&g.entries[base + k].x), b)) return 1;
+      const int cand = (int)__ldg(&g.entries[base + k].x);
+      if (consider<true>(sc, o, d, cand, b)) { hit = cand; return 1; }
     }
   }
 #endif
