@@ -169,7 +169,9 @@ int rtb_scene_render(rtb_scene_t *h, const rtb_frame_opts *opts,
 /* Render into a DEVICE buffer (cudaMalloc'ed or peer-mapped memory, e.g. rank 0's
  * framebuffer opened over CUDA IPC): only pixels of tiles owned by opts->rank are
  * written.  `stream` is a cudaStream_t (0 = the library's own stream).  Asynchronous:
- * call rtb_scene_sync() or synchronise the stream. */
+ * call rtb_scene_sync() or synchronise the stream.  A caller's stream is ordered behind the
+ * handle's earlier work, and the handle's own stream waits for the frame: rtb_scene_sync(),
+ * rtb_scene_stats() and the next frame see it finished whichever stream it ran on. */
 int rtb_scene_render_device(rtb_scene_t *h, const rtb_frame_opts *opts,
                             void *d_rgba, ptrdiff_t pitch, int out_h, int out_w,
                             void *stream);

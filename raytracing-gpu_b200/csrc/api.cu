@@ -182,6 +182,21 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
                         int out_w, cudaStream_t st) {
   int rc = ensure_frame_resources(S);
   if (rc) return rc;
+  // a caller's stream (rtb_scene_render_device): the frame runs behind everything the handle's own stream
+  // holds (the scratch it reuses), and the handle's stream waits for the frame, so that rtb_scene_sync, the
+  // frame time and the state words cover it whichever stream it ran on
+  struct Rejoin {
+    SceneStore &S; cudaStream_t st;
+    ~Rejoin() {
+      if (st == S.stream || !S.xev) return;
+      if (cudaEventRecord(S.xev, st) == cudaSuccess) cudaStreamWaitEvent(S.stream, S.xev, 0);
+    }
+  } rejoin_streams{S, st};
+  if (st != S.stream) {
+    if (!S.xev) RTB_CUDA(cudaEventCreateWithFlags(&S.xev, cudaEventDisableTiming));
+    RTB_CUDA(cudaEventRecord(S.xev, S.stream));
+    RTB_CUDA(cudaStreamWaitEvent(st, S.xev, 0));
+  }
   FrameArgs fa;
   fa.cam = camera_frame(S.camera);
   fa.aliasing = o.aliasing;

@@ -810,6 +810,7 @@ void SceneStore::release() {
   d_sched = nullptr; d_item_order = nullptr; sched_items = 0;
   if (stream) cudaStreamSynchronize(stream);
   for (cudaEvent_t &e : kev) { if (e) cudaEventDestroy(e); e = nullptr; }
+  if (xev) { cudaEventDestroy(xev); xev = nullptr; }
   recycle_frame_ctx(*this);
 }
 

@@ -10,6 +10,7 @@ struct SceneStore {
   int device = -1;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;     // around the last frame kernel / upload
+  cudaEvent_t xev = nullptr;                    // orders a caller's stream (rtb_scene_render_device) with the handle's own
   cudaEvent_t tev0 = nullptr, tev1 = nullptr;   // bracket timer (rtb_scene_timer_*)
   int sm_count = 148;
   bool profile = false;                         // rtb_scene_profile: events between the frame's kernels

@@ -359,9 +359,11 @@ class DeviceScene:
         _check(lib().rtb_scene_render(self.h, C.byref(o), out.ctypes.data, out.strides[0], self.out_h, self.out_w))
         return out
 
-    def render_device(self, d_ptr, pitch, tracer=TRACER_TREE, rank=0, nranks=1, count=False):
+    def render_device(self, d_ptr, pitch, tracer=TRACER_TREE, rank=0, nranks=1, count=False, stream=None):
+        """stream: a cudaStream_t as an integer (None: the handle's own stream)"""
         o = self._opts(tracer, rank, nranks, count)
-        _check(lib().rtb_scene_render_device(self.h, C.byref(o), d_ptr, pitch, self.out_h, self.out_w, None))
+        _check(lib().rtb_scene_render_device(self.h, C.byref(o), d_ptr, pitch, self.out_h, self.out_w,
+                                             C.c_void_p(stream) if stream else None))
 
     def sync(self):
         _check(lib().rtb_scene_sync(self.h))

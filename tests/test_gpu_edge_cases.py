@@ -157,3 +157,28 @@ def test_unit_box_known_answer_of_the_reference(gpu):
         assert np.array_equal(at >= 0, ab >= 0)
     finally:
         ds.close()
+
+
+def test_frames_on_a_callers_stream_are_ordered_with_the_handles_own(gpu):
+    """rtb_scene_render_device with a cudaStream_t of the caller: rtb_scene_sync() covers the frame, the frame
+    time and the projection pass's state words are the frame's, and frames that alternate between the
+    caller's stream and the handle's reuse the same scratch without stepping on each other"""
+    import torch
+    torch.cuda.set_device(0)
+    hs = pyrtb.HostScene.terrain(132, 320, 180)            # >= 2^15 triangles: projection pass + light grids
+    ds = pyrtb.DeviceScene(hs, 3)
+    try:
+        want = ds.render()
+        side = torch.cuda.Stream()
+        frame = torch.zeros((180, 320, 4), dtype=torch.uint8, device="cuda:0")
+        torch.cuda.synchronize()
+        for k in range(6):
+            frame.zero_()
+            torch.cuda.synchronize()
+            ds.render_device(frame.data_ptr(), 320 * 4, stream=side.cuda_stream if k % 2 == 0 else None)
+            ds.sync()                                       # the handle's sync alone, whichever stream ran the frame
+            st = ds.raster_state()
+            assert not st["gave_up"] and st["items"] > 0 and ds.stats()["frame_ms"] > 0
+            assert np.array_equal(frame.cpu().numpy(), want), k
+    finally:
+        ds.close()
