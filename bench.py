@@ -421,14 +421,19 @@ def run_ours(args):
     e2e = None
     if world == 1:
         e2e_steps = max(2, min(args.steps, args.e2e_steps))
-        pyrtb.render_oneshot(hs, ALIASING, out=host_img)          # warm-up (allocator, pinned staging)
+        for _ in range(2):                                        # warm-up: allocator pools grow over two calls, pinned staging
+            pyrtb.render_oneshot(hs, ALIASING, out=host_img)
+        per_call = []
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
+            t1 = time.perf_counter()
             pyrtb.render_oneshot(hs, ALIASING, out=host_img)
+            per_call.append(1e3 * (time.perf_counter() - t1))
         e2e_s = (time.perf_counter() - t0) / e2e_steps
         h2d = hs.triangle_count * 72 + 72 * hs.s.object_count + 28 * hs.s.light_count + 48
         e2e = {"value": rays / e2e_s / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * e2e_s,
+               "ms_per_call": [round(x, 2) for x in per_call],      # value is their mean: a stalled call shows here
                "call": "rtb_render (= render(), gpu/headers/raytracer.h:6): scene upload + hierarchy build + frame + download"}
         # resident-scene variant (rtb_scene_render): camera in, frame out
         ds.render(out=host_img)
@@ -446,7 +451,8 @@ def run_ours(args):
         barrier()
         e2e_s = 0.0
         if rank == 0:
-            pyrtb.render_multi(hs, world, ALIASING, out=host_img)     # warm-up: contexts, peer access, pools
+            for _ in range(2):                                        # warm-up: contexts, peer access, pools
+                pyrtb.render_multi(hs, world, ALIASING, out=host_img)
             t0 = time.perf_counter()
             for _ in range(e2e_steps):
                 pyrtb.render_multi(hs, world, ALIASING, out=host_img)
@@ -611,7 +617,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--ref-samples", type=int, default=0, help="CPU samples per step (default: one per host thread x4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--replicated-setup", action="store_true",

@@ -17,12 +17,6 @@ constexpr float SLIVER_K = RTB_SLIVER_K;
                                sharpest corner at every corner, 5 (product): third-edge slop + corner spikes */
 #endif
 
-// Constants of the "where can the rounded test accept" regions that the projection passes cull
-// with (raster.cuh k_rast_setup has the derivation, lightgrid.cuh k_lg_records uses the same).
-constexpr float RAST_HULL_MIN_COS = 1.0f / 256;  // flatter than this: the box only
-constexpr float RAST_RAY_C = 8.0f;               // distance between the rounded ray and the line through pos and the sample, in 2^-24 |s|
-constexpr float RAST_HULL_C = 14.0f;             // rounding of u and v in units of 2^-24 |s| |e| / |a|: twice the first-order bound
-
 // 1 / sin(theta / 2) for the corner between unit-length-normalised edges (cosine given)
 __device__ __forceinline__ float corner_kappa(float cosine) {
   const float c = fminf(cosine, 1.0f);

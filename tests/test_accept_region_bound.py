@@ -1,19 +1,21 @@
-"""The error bound behind the accept regions of the projection passes (CPU, numpy).
+"""The rounding model behind the accept regions of the projection passes (CPU, numpy).
 
-csrc/raster.cuh (k_rast_setup) and csrc/lightgrid.cuh (lg_region) cull with the region of a
-triangle's plane where the ROUNDED Moeller-Trumbore test of the reference (gpu/hit.cu:8-60,
-un-fused float32) can accept a ray:  u >= -du, v >= -dv, u + v <= 1 + du + dv + 4 eps  with
-du = C eps |s| |e2| |d| / |a|,  dv = C eps |s| |e1| |d| / |a|,  C = RAST_HULL_C = 14 (pad.cuh),
-eps = 2^-24, s = origin - vertex0, a = e1 . (d x e2).  This test replays the test in numpy float32,
-operation by operation, on rays aimed at the edges of triangles seen from far away (the geometry
-of the C5 frame: |s| of thousands of triangle sizes) and at every incidence the code accepts,
-and checks the exact (float64) u, v of every ACCEPTED ray against that bound."""
+csrc/region.cuh bounds where the ROUNDED Moeller-Trumbore test of the reference (gpu/hit.cu:8-60,
+un-fused float32) can accept a ray from the error of the computed numerators:
+|fl(s . h) - s . h| < 7 eps |s| |d| |e2| (and the same with e1 for v), eps = 2^-24, s = origin -
+vertex0, h = d x e2, times SAFETY = 1.25 for the second order.  In barycentric terms an accepted
+ray therefore has  u >= -du, v >= -dv, u + v <= 1 + du + dv + 4 eps  with du = C eps |s||e2||d| / |a|,
+dv = C eps |s||e1||d| / |a|, C = 7 x 1.25, a = e1 . h.  This test replays the test in numpy float32,
+operation by operation, on rays aimed at the edges of triangles seen from far away (the geometry of
+the C5 frame: |s| of thousands of triangle sizes) down to grazing incidence, and checks the exact
+(float64) u, v of every ACCEPTED ray against that bound.  The regions themselves (edge functions,
+clipping, records, spans) are tested on the shipped code in tests/test_region_cpu.py."""
 import numpy as np
 
 f32 = np.float32
 EPS24 = 2.0 ** -24
-C = 14.0                      # RAST_HULL_C
-MIN_COS = 1.0 / 256           # RAST_HULL_MIN_COS
+C = 7.0 * 1.25                # region.cuh: 7 eps per numerator, SAFETY
+MIN_COS = 1.0 / 256           # flatter than this the sample below would need |s| beyond any frame
 
 
 def _cross(a, b):
@@ -95,7 +97,7 @@ def _check(o, d, v0, e1, e2):
     keep = ok & (cos >= MIN_COS)
     du = C * EPS24 * ls * l2 * ld / np.abs(a)
     dv = C * EPS24 * ls * l1 * ld / np.abs(a)
-    keep &= (du < 2) & (dv < 2)                          # beyond that the code culls with the box only
+    keep &= (du < 2) & (dv < 2)                          # (beyond that the allowance is wider than the triangle)
     # how much of the allowance the worst accepted ray uses (1 = at the bound)
     used_u = np.where(keep, np.maximum(-u, 0) / du, 0)
     used_v = np.where(keep, np.maximum(-v, 0) / dv, 0)
@@ -115,8 +117,7 @@ def test_accepted_rays_cross_the_plane_inside_the_grown_triangle():
         worst = max(worst, uu, vv, ww)
         assert n > 50_000, "the sample must contain accepted rays near the edges"
         assert max(uu, vv, ww) <= 1.0, (dist, size, uu, vv, ww)
-    # the constant is meant to have room: the first-order worst case is half of it, and random rays
-    # stay far below that (0.11 of the allowance on these two million, i.e. 1.5 eps |s||e||d| / |a|)
+    # a bound, so it has room: random rays use about 0.18 of it (1.5 eps |s||e||d| / |a|) on these two million
     assert worst <= 0.5, worst
     assert accepted > 500_000
 
