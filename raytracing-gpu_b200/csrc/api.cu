@@ -10,6 +10,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 #include "rtb_internal.h"
 #include "scene_store.h"
@@ -118,16 +119,16 @@ constexpr uint32_t RASTER_AUTO_MIN_TRIS = 1u;
 static int ensure_raster_resources(SceneStore &S, FrameArgs &fa, cudaStream_t st) {
   const size_t samples = (size_t)fa.cam.W * fa.cam.H;
   if (S.d_prim_count < samples) {
-    if (S.d_prim) cudaFreeAsync(S.d_prim, st);
+    if (S.d_prim) block_free(S.d_prim, st);
     S.d_prim = nullptr; S.d_prim_count = 0;
-    RTB_CUDA(cudaMallocAsync((void **)&S.d_prim, samples * 8, st));
+    { const int rc = block_alloc((void **)&S.d_prim, samples * 8, st); if (rc) return rc; }
     S.d_prim_count = samples;
   }
   const size_t cap = 2 * (size_t)S.n_tris + (4u << 20);
   if (S.d_rast_cap < cap) {
-    if (S.d_rast_items) cudaFreeAsync(S.d_rast_items, st);
+    if (S.d_rast_items) block_free(S.d_rast_items, st);
     S.d_rast_items = nullptr; S.d_rast_cap = 0;
-    RTB_CUDA(cudaMallocAsync((void **)&S.d_rast_items, cap * sizeof(RastItem), st));
+    { const int rc = block_alloc((void **)&S.d_rast_items, cap * sizeof(RastItem), st); if (rc) return rc; }
     S.d_rast_cap = cap;
   }
   // state words, the big list, the big list's regions
@@ -180,8 +181,12 @@ static int ensure_frame_resources(SceneStore &S) {
 
 static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d_out, ptrdiff_t pitch, int out_h,
                         int out_w, cudaStream_t st) {
+  static const bool tr_ = [] { const char *e = getenv("RTB_TRACE"); return e && *e == '2'; }();
+  const auto tr0_ = std::chrono::steady_clock::now();
+  auto TR = [&](const char *what) { if (tr_) fprintf(stderr, "  render_async %s +%.3f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tr0_).count()); };
   int rc = ensure_frame_resources(S);
   if (rc) return rc;
+  TR("frame resources");
   // a caller's stream (rtb_scene_render_device): the frame runs behind everything the handle's own stream
   // holds (the scratch it reuses), and the handle's stream waits for the frame, so that rtb_scene_sync, the
   // frame time and the state words cover it whichever stream it ran on
@@ -227,6 +232,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     const bool same = memcmp(key, S.rast_key, sizeof key) == 0;
     if (!(o.primary == RTB_PRIMARY_AUTO && same && S.rast_useless)) {
       rc = ensure_raster_resources(S, fa, st);
+      TR("raster resources");
       if (rc) return rc;
       memcpy(S.rast_key, key, sizeof key);
       S.rast_useless = false;
@@ -271,6 +277,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   uint32_t *sv = nullptr, *sv2 = nullptr, *ss = nullptr;
   size_t ssw = 0;
   unsigned n_items = 0;
+  TR("before schedule");
   if (schedule) {
     n_items = frame_item_count(out_w, out_h, o.nranks);
     const int key[5] = {o.rank, o.nranks, out_w, out_h, o.aliasing};
@@ -310,12 +317,13 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
                     !fa.bounce_scratch && o.aliasing > 1;
   if (schedule)      // 4 words behind the costs, aligned for the 64-bit sum
     d_hot = (unsigned *)(((uintptr_t)((unsigned *)(ss + ssw + 64) + S.sched_items) + 15u) & ~(uintptr_t)15u);
+  TR("before fine");
   if (fine) {
     const size_t pixels = (size_t)out_w * out_h, items = frame_item_count(out_w, out_h, o.nranks);
     if (S.fine_pixels < pixels) {
-      if (S.d_fine_acc) cudaFreeAsync(S.d_fine_acc, st);
+      if (S.d_fine_acc) block_free(S.d_fine_acc, st);
       S.d_fine_acc = nullptr; S.fine_pixels = 0;
-      RTB_CUDA(cudaMallocAsync((void **)&S.d_fine_acc, pixels * sizeof(uint2), st));
+      { const int rc2 = block_alloc((void **)&S.d_fine_acc, pixels * sizeof(uint2), st); if (rc2) return rc2; }
       RTB_CUDA(cudaMemsetAsync(S.d_fine_acc, 0, pixels * sizeof(uint2), st));      // once: k_frame leaves it zero
       S.fine_pixels = pixels;
     }
@@ -370,7 +378,9 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   if (S.profile && !S.kev[0])
     for (cudaEvent_t &e : S.kev) RTB_CUDA(cudaEventCreate(&e));
+  TR("before launches");
   rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches, S.profile ? S.kev : nullptr);
+  TR("after launches");
   if (rc) return rc;
   RTB_CUDA(cudaEventRecord(S.ev1, st));
   if (record) {
@@ -420,10 +430,107 @@ struct FrameCtx {
   unsigned long long *d_counters;
   float *d_bounce;
   size_t d_bounce_floats;
+  // the projection pass's scratch (samples x 8 B, items, state): GB-sized blocks cost the stream-ordered pool
+  // milliseconds each to map even when it holds the memory (6 ms of a one-shot render() of C5)
+  unsigned long long *d_prim;
+  size_t d_prim_count;
+  RastItem *d_rast_items;
+  size_t d_rast_cap;
+  unsigned *d_rast;
 };
 static std::mutex g_ctx_mu;
 static std::vector<FrameCtx> g_ctx_pool;
 static std::vector<int> g_pool_tuned;   // devices whose memory pool keeps freed blocks
+
+// ---- block cache (rtb_internal.h) ----
+namespace {
+struct ParkedBlock { void *p; size_t bytes; cudaStream_t st; cudaEvent_t ev; };
+struct BlockCache {
+  std::vector<ParkedBlock> parked;                    // oldest first
+  std::unordered_map<void *, size_t> live;            // big blocks handed out: their sizes
+  size_t parked_bytes = 0;
+};
+std::mutex g_block_mu;
+std::unordered_map<int, BlockCache> g_block_cache;    // per device
+constexpr size_t BLOCK_CACHE_MIN = 8u << 20;
+size_t block_cache_cap() {
+  static const size_t cap = [] { const char *e = getenv("RTB_BLOCK_CACHE_MB"); return (size_t)(e ? atoll(e) : 24576) << 20; }();
+  return cap;
+}
+}  // namespace
+
+int block_alloc(void **p, size_t bytes, cudaStream_t st) {
+  *p = nullptr;
+  if (bytes >= BLOCK_CACHE_MIN && block_cache_cap()) {
+    int dev = 0;
+    RTB_CUDA(cudaGetDevice(&dev));
+    ParkedBlock hit = {nullptr, 0, nullptr, nullptr};
+    {
+      std::lock_guard<std::mutex> lk(g_block_mu);
+      BlockCache &c = g_block_cache[dev];
+      for (size_t i = c.parked.size(); i-- > 0;)
+        if (c.parked[i].bytes == bytes) {
+          hit = c.parked[i];
+          c.parked.erase(c.parked.begin() + (long)i);
+          c.parked_bytes -= bytes;
+          c.live[hit.p] = bytes;
+          break;
+        }
+    }
+    if (hit.p) {
+      // whatever the freeing stream still had queued on the block comes first
+      if (hit.st != st) RTB_CUDA(cudaStreamWaitEvent(st, hit.ev, 0));
+      cudaEventDestroy(hit.ev);
+      *p = hit.p;
+      return RTB_OK;
+    }
+  }
+  RTB_CUDA(cudaMallocAsync(p, bytes ? bytes : 1, st));
+  if (bytes >= BLOCK_CACHE_MIN && block_cache_cap()) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(g_block_mu);
+    g_block_cache[dev].live[*p] = bytes;
+  }
+  return RTB_OK;
+}
+
+void block_free(void *p, cudaStream_t st) {
+  if (!p) return;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  size_t bytes = 0;
+  std::vector<ParkedBlock> evict;
+  {
+    std::lock_guard<std::mutex> lk(g_block_mu);
+    BlockCache &c = g_block_cache[dev];
+    auto it = c.live.find(p);
+    if (it != c.live.end()) { bytes = it->second; c.live.erase(it); }
+    if (bytes) {
+      cudaEvent_t ev = nullptr;
+      if (bytes <= block_cache_cap() && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess &&
+          cudaEventRecord(ev, st) == cudaSuccess) {
+        c.parked.push_back({p, bytes, st, ev});
+        c.parked_bytes += bytes;
+        while (c.parked_bytes > block_cache_cap() && !c.parked.empty()) {
+          evict.push_back(c.parked.front());
+          c.parked_bytes -= c.parked.front().bytes;
+          c.parked.erase(c.parked.begin());
+        }
+      } else {
+        if (ev) cudaEventDestroy(ev);
+        cudaGetLastError();
+        bytes = 0;
+      }
+    }
+  }
+  if (!bytes) cudaFreeAsync(p, st);
+  for (ParkedBlock &b : evict) {
+    cudaStreamWaitEvent(st, b.ev, 0);
+    cudaEventDestroy(b.ev);
+    cudaFreeAsync(b.p, st);
+  }
+}
 
 // cudaMallocAsync's default pool hands freed blocks back to the driver at every
 // synchronisation unless told to keep them; keeping them makes scratch allocation ~1 us.
@@ -450,6 +557,8 @@ int acquire_frame_ctx(int device, SceneStore &S) {
         S.d_frame = c.d_frame; S.h_frame = c.h_frame; S.d_frame_bytes = c.d_frame_bytes; S.h_frame_bytes = c.h_frame_bytes;
         S.d_tile_counter = c.d_tile_counter; S.d_counters = c.d_counters; S.d_bounce = c.d_bounce;
         S.d_bounce_floats = c.d_bounce_floats;
+        S.d_prim = c.d_prim; S.d_prim_count = c.d_prim_count; S.d_rast_items = c.d_rast_items; S.d_rast_cap = c.d_rast_cap;
+        S.d_rast = c.d_rast;
         return RTB_OK;
       }
   }
@@ -469,6 +578,8 @@ void recycle_frame_ctx(SceneStore &S) {
   c.tev1 = S.tev1; c.d_frame = S.d_frame; c.h_frame = S.h_frame; c.d_frame_bytes = S.d_frame_bytes;
   c.h_frame_bytes = S.h_frame_bytes; c.d_tile_counter = S.d_tile_counter; c.d_counters = S.d_counters;
   c.d_bounce = S.d_bounce; c.d_bounce_floats = S.d_bounce_floats;
+  c.d_prim = S.d_prim; c.d_prim_count = S.d_prim_count; c.d_rast_items = S.d_rast_items; c.d_rast_cap = S.d_rast_cap; c.d_rast = S.d_rast;
+  S.d_prim = nullptr; S.d_prim_count = 0; S.d_rast_items = nullptr; S.d_rast_cap = 0; S.d_rast = nullptr;
   S.stream = nullptr; S.ev0 = S.ev1 = S.tev0 = S.tev1 = nullptr; S.d_frame = S.h_frame = nullptr;
   S.d_frame_bytes = S.h_frame_bytes = 0; S.d_tile_counter = nullptr; S.d_counters = nullptr; S.d_bounce = nullptr;
   S.d_bounce_floats = 0;
@@ -479,6 +590,10 @@ void recycle_frame_ctx(SceneStore &S) {
   if (c.d_tile_counter) cudaFree(c.d_tile_counter);
   if (c.d_counters) cudaFree(c.d_counters);
   if (c.d_bounce) cudaFree(c.d_bounce);
+  if (c.d_prim) block_free(c.d_prim, c.stream);
+  if (c.d_rast_items) block_free(c.d_rast_items, c.stream);
+  if (c.d_rast) cudaFreeAsync(c.d_rast, c.stream);
+  cudaStreamSynchronize(c.stream);
   cudaEventDestroy(c.ev0); cudaEventDestroy(c.ev1); cudaEventDestroy(c.tev0); cudaEventDestroy(c.tev1);
   cudaStreamDestroy(c.stream);
 }
@@ -580,17 +695,27 @@ int rtb_scene_render(rtb_scene_t *h, const rtb_frame_opts *opts, unsigned char *
     RTB_CUDA(cudaMalloc((void **)&S.d_frame, bytes));
     S.d_frame_bytes = bytes;
   }
+  static const bool trace = [] { const char *tr = getenv("RTB_TRACE"); return tr && *tr == '1'; }();
+  const auto t0 = std::chrono::steady_clock::now();
   if (o.nranks > 1) RTB_CUDA(cudaMemsetAsync(S.d_frame, 0, bytes, S.stream));
   rc = render_async(S, o, S.d_frame, (ptrdiff_t)row, out_h, out_w, S.stream);
   if (rc) return rc;
+  const auto t1 = std::chrono::steady_clock::now();
   // D2H: straight into the caller's buffer when it is page-locked, else through our pinned staging
   cudaPointerAttributes attr;
   bool pinned = cudaPointerGetAttributes(&attr, rgba_out) == cudaSuccess &&
                 (attr.type == cudaMemoryTypeHost);
   cudaGetLastError();
   if (pinned) {
-    RTB_CUDA(cudaMemcpy2DAsync(rgba_out, (size_t)stride, S.d_frame, row, row, out_h, cudaMemcpyDeviceToHost, S.stream));
-    return finish_frame(S, S.stream);
+    if ((size_t)stride == row) RTB_CUDA(cudaMemcpyAsync(rgba_out, S.d_frame, bytes, cudaMemcpyDeviceToHost, S.stream));
+    else RTB_CUDA(cudaMemcpy2DAsync(rgba_out, (size_t)stride, S.d_frame, row, row, out_h, cudaMemcpyDeviceToHost, S.stream));
+    rc = finish_frame(S, S.stream);
+    if (trace) {
+      auto ms = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+      fprintf(stderr, "rtb_scene_render: launches enqueued after %.2f ms, frame + download done after %.2f ms (kernels %.2f)\n", ms(t0, t1),
+              ms(t0, std::chrono::steady_clock::now()), S.frame_ms);
+    }
+    return rc;
   }
   if (S.h_frame_bytes < bytes) {
     if (S.h_frame) cudaFreeHost(S.h_frame);

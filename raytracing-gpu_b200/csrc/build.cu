@@ -795,14 +795,13 @@ SceneStore::~SceneStore() { release(); }
 // Stream, events and frame buffers go back to a per-device cache (recycle_frame_ctx).
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, d_prim, d_rast_items, d_rast, lgrids,
-                  d_fine_acc, d_fine_done};
-  for (void *p : ptrs) if (p) cudaFreeAsync(p, stream);
-  for (void *&p : lgrid_mem) { if (p) cudaFreeAsync(p, stream); p = nullptr; }
+  // (d_prim, d_rast_items, d_rast go back to the per-device cache with the stream: recycle_frame_ctx)
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, lgrids, d_fine_acc, d_fine_done};
+  for (void *p : ptrs) if (p) block_free(p, stream);
+  for (void *&p : lgrid_mem) { if (p) block_free(p, stream); p = nullptr; }
   lgrids = nullptr; n_lgrids = 0; lgrid_entries = lgrid_cells = 0;
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
   order = nullptr; up = nullptr; inv_order = nullptr;
-  d_prim = nullptr; d_rast_items = nullptr; d_rast = nullptr; d_prim_count = 0; d_rast_cap = 0;
   d_fine_acc = nullptr; d_fine_done = nullptr; fine_pixels = fine_items = 0;
   if (h_rast) { cudaFreeHost(h_rast); h_rast = nullptr; }
   if (xchg_block) { cudaStreamSynchronize(stream); cudaFree(xchg_block); xchg_block = nullptr; xchg_nranks = 0; xchg_rank = -1; }
@@ -821,13 +820,12 @@ static thread_local cudaStream_t tl_alloc_stream = nullptr;   // set by build_sc
 template <typename T>
 static int dev_alloc(T **p, size_t count) {
   *p = nullptr;
-  RTB_CUDA(cudaMallocAsync((void **)p, (count ? count : 1) * sizeof(T), tl_alloc_stream));
-  return RTB_OK;
+  return block_alloc((void **)p, (count ? count : 1) * sizeof(T), tl_alloc_stream);
 }
 
 struct Temp {   // build-time scratch, freed (stream-ordered) when build_scene returns
   std::vector<void *> ptrs;
-  ~Temp() { for (void *p : ptrs) cudaFreeAsync(p, tl_alloc_stream); }
+  ~Temp() { for (void *p : ptrs) block_free(p, tl_alloc_stream); }
   template <typename T> int alloc(T **p, size_t count) {
     int rc = dev_alloc(p, count);
     if (!rc) ptrs.push_back(*p);

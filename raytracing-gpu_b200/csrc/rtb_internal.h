@@ -151,6 +151,15 @@ int dev_exclusive_scan_u32(uint32_t *d_data, size_t n, uint32_t *d_scratch, size
 int dev_inclusive_scan_u64(uint64_t *d_data, size_t n, uint64_t *d_scratch, size_t scratch_words, cudaStream_t st);
 size_t scan_scratch_words(size_t n);
 
+// ---- device blocks (api.cu) ----
+// cudaMallocAsync / cudaFreeAsync with a per-device cache of big blocks in front.  The stream-ordered pool keeps
+// freed memory (api.cu raises its release threshold), but mapping a block of hundreds of MB out of it costs the
+// host 1-3 ms every time; a render() of a 10 M-triangle scene allocates 30 such blocks.  Freed blocks of >= 8 MB
+// are parked with an event on the freeing stream and handed to the next request of exactly that size (the next
+// render() of the same scene); RTB_BLOCK_CACHE_MB bounds what is parked per device (default 24 576, 0: off).
+int block_alloc(void **p, size_t bytes, cudaStream_t st);
+void block_free(void *p, cudaStream_t st);
+
 // ---- frame kernels (trace.cu) ----
 // marks: nullptr, or 6 events recorded before the frame's first operation, after k_rast_setup, after k_rast_big,
 // after k_xchg_sync, after k_rast_items and after the frame kernel (rtb_scene_profile)

@@ -580,12 +580,12 @@ struct LgScratch {
   int n = 0;
   template <typename T> int alloc(T **out, size_t bytes) {
     *out = nullptr;
-    RTB_CUDA(cudaMallocAsync((void **)out, bytes, st));
+    { const int rc = block_alloc((void **)out, bytes, st); if (rc) return rc; }
     p[n++] = *out;
     return RTB_OK;
   }
   void keep(void *q) { for (int k = 0; k < n; ++k) if (p[k] == q) p[k] = nullptr; }
-  ~LgScratch() { for (int k = 0; k < n; ++k) if (p[k]) cudaFreeAsync(p[k], st); }
+  ~LgScratch() { for (int k = 0; k < n; ++k) if (p[k]) block_free(p[k], st); }
 };
 
 int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights, const float bmin[3],
