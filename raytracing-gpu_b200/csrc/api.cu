@@ -981,7 +981,7 @@ int rtb_scene_exchange_create(rtb_scene_t *h, int nranks, void **d_block, size_t
   RTB_CUDA(cudaSetDevice(S.device));
   if (S.xchg_block) { cudaFree(S.xchg_block); S.xchg_block = nullptr; S.xchg_nranks = 0; S.xchg_rank = -1; }
   // a pair (source, destination) sees 1 / N^2 of the frame's items on average (tiles interleave over the
-  // ranks, triangle shares are compact): four times that, but never more than the whole list
+  // ranks, triangle blocks are dealt round robin): four times that, but never more than the whole list
   const size_t all = 2 * (size_t)S.n_tris + (4u << 20);
   size_t cap = 4 * all / ((size_t)nranks * nranks) + 65536;
   if (cap > all) cap = all;
