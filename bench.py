@@ -391,6 +391,7 @@ def run_ours(args):
     barrier()
     ms_static = max_over_ranks(ms_static)
     clocks = sampler.stop() if rank == 0 else None
+    barrier()       # (stopping the sampler takes rank 0 a moment: the others would wait for its items inside their first frame)
     # per-kernel durations of a frame (events between the launches, same stream), moving camera again
     ds.profile(True)
     kernel_ms, parts = [], []
