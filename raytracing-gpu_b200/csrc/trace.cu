@@ -25,7 +25,7 @@
 //     <= 3 samples per random needle soup, tests/test_gpu_random_scenes.py).
 // Deviation kept on purpose: the reference treats a hit record whose interpolated normal is exactly
 // (0,0,0) as a miss (gpu/hit.cu:100, gpu/raytracer.cu:36); this tracer does not (unit vertex normals
-// produce it only where they cancel exactly, e.g. n0 = -n1 at u = 0.5), the oracle does.
+// produce it only where they cancel exactly, e.g. n0 = -n1 at u = 0.5); DESIGN.md section 4.2.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
