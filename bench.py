@@ -278,22 +278,28 @@ def run_ours(args):
 
     # rank 0 owns the framebuffer; the other ranks store their tiles straight into it
     # through a CUDA-IPC mapping (NVLink peer stores) — no gather collective.
-    d_frame = C.c_void_p()
-    if rank == 0:
-        pyrtb._check(L.rtb_dev_alloc(local_rank, frame_bytes, C.byref(d_frame)))
-        pyrtb._check(L.rtb_dev_memset(d_frame, 0, frame_bytes))
-    if world > 1:
-        import torch
-        handle = torch.zeros(64, dtype=torch.uint8)
+    # (two frames, for the double-buffered resident loop: frame k + 1 renders while frame k is downloaded)
+    def shared_frame():
+        d = C.c_void_p()
         if rank == 0:
-            hb = (C.c_ubyte * 64)()
-            pyrtb._check(L.rtb_ipc_export(d_frame, hb))
-            handle = torch.tensor(list(hb), dtype=torch.uint8)
-        handle = handle.cuda()
-        dist.broadcast(handle, 0)
-        if rank != 0:
-            hb = (C.c_ubyte * 64)(*handle.cpu().tolist())
-            pyrtb._check(L.rtb_ipc_open(hb, C.byref(d_frame)))
+            pyrtb._check(L.rtb_dev_alloc(local_rank, frame_bytes, C.byref(d)))
+            pyrtb._check(L.rtb_dev_memset(d, 0, frame_bytes))
+        if world > 1:
+            import torch
+            handle = torch.zeros(64, dtype=torch.uint8)
+            if rank == 0:
+                hb = (C.c_ubyte * 64)()
+                pyrtb._check(L.rtb_ipc_export(d, hb))
+                handle = torch.tensor(list(hb), dtype=torch.uint8)
+            handle = handle.cuda()
+            dist.broadcast(handle, 0)
+            if rank != 0:
+                hb = (C.c_ubyte * 64)(*handle.cpu().tolist())
+                pyrtb._check(L.rtb_ipc_open(hb, C.byref(d)))
+        return d
+
+    d_frame = shared_frame()
+    d_frame_b = shared_frame()
 
     # Sharded projection pass (rtb_scene_exchange_*): every rank projects 1/N of the triangles and stores the
     # items straight into the owners' inboxes through CUDA-IPC mappings of the peers' exchange blocks (NVLink
@@ -320,8 +326,8 @@ def run_ours(args):
         ds.exchange_attach(rank, world, blocks)
         barrier()
 
-    def frame(count=False):
-        ds.render_device(d_frame, pitch, rank=rank, nranks=world, count=count)
+    def frame(count=False, into=None):
+        ds.render_device(into or d_frame, pitch, rank=rank, nranks=world, count=count)
 
     # Camera path: the headline times a fly-through, one new camera per frame (a dolly along the view
     # direction with a little side-slip), so that nothing a frame learns about its camera (the
@@ -440,14 +446,13 @@ def run_ours(args):
                "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * e2e_s, "statistic": "median of %d calls" % e2e_steps,
                "ms_per_step_mean": 1e3 * mean_s, "ms_per_call": [round(x, 2) for x in per_call],
                "call": "rtb_render (= render(), gpu/headers/raytracer.h:6): scene upload + hierarchy build + frame + download"}
-        # resident-scene variant (rtb_scene_render): camera in, frame out
+        # resident-scene variants: camera in, frame out.  (a) rtb_scene_render, one synchronous call per frame;
+        # (b) double-buffered (below, the same loop at every N)
         ds.render(out=host_img)
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             ds.render(out=host_img)
-        res_s = (time.perf_counter() - t0) / e2e_steps
-        e2e["resident"] = {"value": rays / res_s / 1e6, "ms_per_step": 1e3 * res_s, "h2d_bytes_per_step": 48,
-                           "d2h_bytes_per_step": frame_bytes, "call": "rtb_scene_render"}
+        res_sync_s = (time.perf_counter() - t0) / e2e_steps
     else:
         # the SAME call as at N = 1: the one-shot render(), here on N devices of rank 0's process
         # (rtb_render_multi: every device uploads the scene and builds its hierarchy, renders its tiles
@@ -473,20 +478,47 @@ def run_ours(args):
                "ms_per_step_mean": 1e3 * mean_s, "ms_per_call": [round(x, 2) for x in per_call],
                "call": "rtb_render_multi (= render() with RT_GPUS = N): scene upload + hierarchy build on every device, "
                        "tiles stored into device 0's frame over NVLink, download"}
-        # resident-scene variant: all ranks render their tiles into rank 0's device frame; rank 0 downloads it
+        res_sync_s = None
+    # resident scene, double-buffered, the same loop at every N: every rank renders its tiles of frame k into one
+    # of two frames in rank 0's memory (NVLink peer stores); when all ranks are done rank 0 starts the download of
+    # that frame on a copy stream (rtb_dev_download_async) and everybody goes on with frame k + 1 in the other
+    # buffer.  Every frame is downloaded (33 MB into pinned memory); the last download is waited for inside the
+    # timed region.
+    pinned_b = pyrtb.PinnedBuffer(frame_bytes)
+    host_b = pinned_b.array((HEIGHT, WIDTH, 4))
+    bufs = ((d_frame, host_img), (d_frame_b, host_b))
+    res_steps = max(4, min(args.steps, 2 * args.e2e_steps))
+    for k in range(2):                              # warm-up: both buffers, the copy stream
+        frame(into=bufs[k][0])
+        ds.sync()
         barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            frame()
-            ds.sync()
-            barrier()
-            if rank == 0:
-                pyrtb._check(L.rtb_dev_download(host_img.ctypes.data, d_frame, frame_bytes))
+        if rank == 0:
+            pyrtb._check(L.rtb_dev_download_async(bufs[k][1].ctypes.data, bufs[k][0], frame_bytes))
+    if rank == 0:
+        pyrtb._check(L.rtb_dev_download_wait(d_frame))
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(res_steps):
+        ds.set_camera(path[k % len(path)])
+        dev_buf, host_buf = bufs[k % 2]
+        if rank == 0 and k >= 2:
+            pyrtb._check(L.rtb_dev_download_wait(dev_buf))          # (the copy two frames back: long finished)
+        frame(into=dev_buf)
+        ds.sync()
         barrier()
-        res_s = max_over_ranks((time.perf_counter() - t0) / e2e_steps)
-        e2e["resident"] = {"value": rays / res_s / 1e6, "ms_per_step": 1e3 * res_s, "h2d_bytes_per_step": 48,
-                           "d2h_bytes_per_step": frame_bytes,
-                           "call": "rtb_scene_render_device on every rank (tiles stored into rank 0's frame over NVLink) + download"}
+        if rank == 0:
+            pyrtb._check(L.rtb_dev_download_async(host_buf.ctypes.data, dev_buf, frame_bytes))
+    if rank == 0:
+        pyrtb._check(L.rtb_dev_download_wait(d_frame))
+    barrier()
+    res_s = max_over_ranks((time.perf_counter() - t0) / res_steps)
+    ds.set_camera(cam0)
+    e2e["resident"] = {"value": rays_path / len(path) / res_s / 1e6, "ms_per_step": 1e3 * res_s, "h2d_bytes_per_step": 48,
+                       "d2h_bytes_per_step": frame_bytes, "steps": res_steps,
+                       "call": "rtb_scene_set_camera + rtb_scene_render_device on every rank (tiles stored into rank 0's frame "
+                               "over NVLink) + rtb_dev_download_async, double-buffered: frame k is downloaded while frame k + 1 renders"}
+    if res_sync_s is not None:
+        e2e["resident"]["synchronous_ms_per_step"] = 1e3 * res_sync_s      # rtb_scene_render: frame, then download, one call
 
     # frame check: the composed frame equals a single-GPU frame of the same scene (camera 0)
     ds.set_camera(cam0)

@@ -1159,6 +1159,39 @@ int rtb_dev_download(void *dst_host, const void *src_dev, size_t bytes) {
   RTB_CUDA(cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost));
   return RTB_OK;
 }
+// Double-buffered frames: the download of frame k on a copy stream of its own while frame k + 1 renders.
+// One copy stream per device, created on first use; the caller has made sure the frame is complete
+// (rtb_scene_sync, a barrier between ranks) before it asks for the copy.
+static std::mutex g_copy_mu;
+static cudaStream_t g_copy_stream[64] = {nullptr};
+static int copy_stream_of(const void *dev_ptr, cudaStream_t *out, int *device) {
+  cudaPointerAttributes attr;
+  RTB_CUDA(cudaPointerGetAttributes(&attr, dev_ptr));
+  const int dev = attr.device;
+  if (attr.type != cudaMemoryTypeDevice || dev < 0 || dev >= 64) { set_error("not a device pointer"); return RTB_ERR_ARG; }
+  RTB_CUDA(cudaSetDevice(dev));
+  std::lock_guard<std::mutex> lk(g_copy_mu);
+  if (!g_copy_stream[dev]) RTB_CUDA(cudaStreamCreateWithFlags(&g_copy_stream[dev], cudaStreamNonBlocking));
+  *out = g_copy_stream[dev];
+  if (device) *device = dev;
+  return RTB_OK;
+}
+int rtb_dev_download_async(void *dst_host, const void *src_dev, size_t bytes) {
+  if (!dst_host || !src_dev) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  cudaStream_t st = nullptr;
+  const int rc = copy_stream_of(src_dev, &st, nullptr);
+  if (rc) return rc;
+  RTB_CUDA(cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, st));
+  return RTB_OK;
+}
+int rtb_dev_download_wait(const void *src_dev) {
+  if (!src_dev) { set_error("NULL argument"); return RTB_ERR_ARG; }
+  cudaStream_t st = nullptr;
+  const int rc = copy_stream_of(src_dev, &st, nullptr);
+  if (rc) return rc;
+  RTB_CUDA(cudaStreamSynchronize(st));
+  return RTB_OK;
+}
 int rtb_ipc_export(void *d_ptr, unsigned char handle_out[64]) {
   cudaIpcMemHandle_t hnd;
   RTB_CUDA(cudaIpcGetMemHandle(&hnd, d_ptr));

@@ -69,7 +69,7 @@ ABI_SYMBOLS = [
     "rtb_last_error", "rtb_render", "rtb_render_multi", "rtb_scene_create", "rtb_scene_destroy", "rtb_scene_set_camera",
     "rtb_scene_render", "rtb_scene_render_device", "rtb_scene_sync", "rtb_scene_hit_ids", "rtb_scene_trace_rays",
     "rtb_scene_stats", "rtb_radix_sort_pairs_u32", "rtb_radix_sort_pairs_u64", "rtb_inclusive_scan_u32",
-    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_dev_inclusive_scan_u32_static", "rtb_scene_dump_tree", "rtb_scene_raster_state", "rtb_scene_profile", "rtb_scene_kernel_ms", "rtb_scene_exchange_create", "rtb_scene_exchange_attach",
+    "rtb_inclusive_scan_u64", "rtb_dev_radix_sort_pairs_u64", "rtb_dev_inclusive_scan_u32", "rtb_dev_inclusive_scan_u32_static", "rtb_scene_dump_tree", "rtb_scene_raster_state", "rtb_scene_profile", "rtb_scene_kernel_ms", "rtb_scene_exchange_create", "rtb_scene_exchange_attach", "rtb_dev_download_async", "rtb_dev_download_wait",
     "rtb_device_count", "rtb_version", "rtb_scene_root", "rtb_set_margin_k", "rtb_set_schedule", "rtb_warmup", "rtb_scene_timer_start",
     "rtb_scene_timer_stop", "rtb_host_alloc", "rtb_host_free", "rtb_dev_alloc", "rtb_dev_free", "rtb_dev_memset",
     "rtb_dev_download", "rtb_scene_mem_alloc", "rtb_scene_mem_free", "rtb_ipc_export", "rtb_ipc_open", "rtb_ipc_close",
@@ -128,6 +128,8 @@ def lib():
         L.rtb_dev_free.argtypes = [C.c_void_p]
         L.rtb_dev_memset.argtypes = [C.c_void_p, C.c_int, C.c_size_t]
         L.rtb_dev_download.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.rtb_dev_download_async.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.rtb_dev_download_wait.argtypes = [C.c_void_p]
         L.rtb_ipc_export.argtypes = [C.c_void_p, C.c_void_p]
         L.rtb_ipc_open.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
         L.rtb_ipc_close.argtypes = [C.c_void_p]
