@@ -312,7 +312,7 @@ int rtb_dev_download(void *dst_host, const void *src_dev, size_t bytes);
 /* Double-buffered frames: start the download of a finished frame on the device's copy stream (page-locked
  * dst_host, e.g. rtb_host_alloc) and go on rendering into the other buffer; rtb_dev_download_wait returns
  * when every download started from that device has arrived.  The caller orders copy after frame
- * (rtb_scene_sync, a barrier between ranks).  (gpu/raytracer.cu:239-243 is the reference's one cudaMemcpy.) */
+ * (rtb_scene_sync, a barrier between ranks).  (gpu/raytracer.cu:244-247 is the reference's one cudaMemcpy2D.) */
 int rtb_dev_download_async(void *dst_host, const void *src_dev, size_t bytes);
 int rtb_dev_download_wait(const void *src_dev);
 int rtb_ipc_export(void *d_ptr, unsigned char handle_out[64]);
