@@ -10,6 +10,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <algorithm>
 #include <unordered_map>
 #include <vector>
 #include "rtb_internal.h"
@@ -271,7 +272,7 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   // camera change) records each item's cost; a 2-pass radix sort of the 16-bit costs on the
   // same stream gives the order the following frames use.  A one-shot render never gets here.
   const bool schedule = g_schedule && !fa.bounce_scratch && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
-                        S.frames_done >= 1;
+                        S.frames_done >= 1 && !S.tree_deferred;
   bool record = false;
   uint64_t *sk = nullptr, *sk2 = nullptr;
   uint32_t *sv = nullptr, *sv2 = nullptr, *ss = nullptr;
@@ -378,7 +379,27 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   RTB_CUDA(cudaEventRecord(S.ev0, st));
   if (S.profile && !S.kev[0])
     for (cudaEvent_t &e : S.kev) RTB_CUDA(cudaEventCreate(&e));
+  fa.need_tree = nullptr; fa.stray = nullptr; fa.stray_cap = 0; fa.stray_mode = 0; fa.only_items = 0;
+  if (S.tree_deferred) {
+    // only a frame of the per-sample tree tracer with the projection pass on can do without the nodes
+    if (!fa.prim || o.tracer != RTB_TRACER_TREE || o.count_rays || fa.bounce_scratch) return RTB_NEED_TREE;
+    fa.need_tree = fa.rast + 7;      // cleared with the other state words at the start of the frame
+    if (!S.d_stray) RTB_CUDA(cudaMallocAsync((void **)&S.d_stray, (size_t)STRAY_CAP * (sizeof(StrayQuery) + 4), st));
+    fa.stray = S.d_stray; fa.stray_cap = STRAY_CAP; fa.stray_mode = S.stray_pass == 2 ? 2 : 1;
+    if (S.stray_pass == 2) {
+      fa.item_order = reinterpret_cast<const unsigned *>(S.d_stray + STRAY_CAP);
+      fa.only_items = S.stray_items;
+      fa.item_cost = nullptr;
+    }
+  }
   TR("before launches");
+  if (S.stray_pass == 2) {
+    RTB_CUDA(cudaEventRecord(S.ev0, st));
+    rc = launch_frame_only(S.dev(), fa, S.sm_count, st);
+    if (rc) return rc;
+    RTB_CUDA(cudaEventRecord(S.ev1, st));
+    return RTB_OK;
+  }
   rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches, S.profile ? S.kev : nullptr);
   TR("after launches");
   if (rc) return rc;
@@ -616,7 +637,88 @@ int rtb_device_count(void) {
 static int scene_create_impl(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out, UploadGroup *grp, int member);
 
 int rtb_scene_create(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out) {
-  return scene_create_impl(scene, device, flags, out, nullptr, 0);
+  return scene_create_impl(scene, device, flags & 0xffffu, out, nullptr, 0);      // (the upper bits are internal)
+}
+
+// rtb_render / rtb_render_multi: may this scene's one frame be tried without the node array (build.cu `defer`)?  Only
+// when no object reflects (a bounce ray walks the tree; gpu/raytracer.cu:107-122 bounces while nr > 0.01); the size and
+// light-grid conditions are checked by the build itself.  RTB_DEFER_TREE=0 switches it off, =2 skips this check (tests:
+// the frame then finds out on the device and is rendered again).
+static unsigned defer_tree_flag(const struct scene *scene) {
+  static const int mode = [] { const char *e = getenv("RTB_DEFER_TREE"); return e ? atoi(e) : 1; }();
+  if (mode == 0 || !scene) return 0u;
+  if (mode != 2)
+    for (size_t o = 0; o < scene->object_count; ++o)
+      if (scene->objects && scene->objects[o].nr > 0.0f) return 0u;
+  return RTB_BUILD_DEFER_TREE;
+}
+
+// After the frame of a deferred-tree handle (build.cu `defer`): did a ray need the nodes?  Shadow rays that were merely
+// off their light's grid are listed (FrameArgs::stray): they are resolved against every triangle (k_stray_any) and the
+// warp tiles they belong to are rendered once more into d_out with the answers looked up.  *rebuild: anything else
+// needed the tree (or the list overflowed): the caller builds the scene again, with its tree.
+static int finish_deferred(rtb_scene_t *h, const rtb_frame_opts &o, unsigned char *d_out, ptrdiff_t pitch, int out_h, int out_w,
+                           bool *rebuild, bool *fixed) {
+  *rebuild = false;
+  *fixed = false;
+  SceneStore &S = h->store;
+  if (!S.tree_deferred || !S.d_rast) return RTB_OK;
+  unsigned w[15];
+  RTB_CUDA(cudaMemcpyAsync(w, S.d_rast + 7, sizeof w, cudaMemcpyDeviceToHost, S.stream));
+  RTB_CUDA(cudaStreamSynchronize(S.stream));
+  static const bool trace = [] { const char *tr = getenv("RTB_TRACE"); return tr && *tr == '1'; }();
+  const unsigned strays = w[14];
+  if (trace && (w[0] || strays))
+    fprintf(stderr, "[rtb200] rays that needed the tree: %u nearest-hit; shadow rays off their grid: %u (%u light without grid, %u origin outside "
+            "the scene's box, %u off the grid, %u outside a point light's projection)\n", w[9], strays, w[10], w[11], w[12], w[13]);
+  if (w[0] || strays > STRAY_CAP) { *rebuild = true; return RTB_OK; }
+  if (!strays) return RTB_OK;
+  int rc = launch_stray_any(S.dev(), S.d_stray, S.d_rast + 21, S.sm_count, S.stream);
+  if (rc) return rc;
+  std::vector<StrayQuery> q(strays);
+  RTB_CUDA(cudaMemcpyAsync(q.data(), S.d_stray, strays * sizeof(StrayQuery), cudaMemcpyDeviceToHost, S.stream));
+  RTB_CUDA(cudaStreamSynchronize(S.stream));
+  std::vector<unsigned> items;
+  for (const StrayQuery &e : q) items.push_back(e.item);
+  std::sort(items.begin(), items.end());
+  items.erase(std::unique(items.begin(), items.end()), items.end());
+  RTB_CUDA(cudaMemcpyAsync(S.d_stray + STRAY_CAP, items.data(), items.size() * 4, cudaMemcpyHostToDevice, S.stream));
+  rtb_frame_opts eff;
+  rc = check_frame(S, &o, out_h, out_w, &eff);
+  if (rc) return rc;
+  S.stray_pass = 2;
+  S.stray_items = (unsigned)items.size();
+  rc = render_async(S, eff, d_out, pitch, out_h, out_w, S.stream);
+  S.stray_pass = 0;
+  if (rc) return rc;
+  RTB_CUDA(cudaStreamSynchronize(S.stream));      // (items' host copy must outlive the upload)
+  *fixed = true;
+  return RTB_OK;
+}
+
+// the frame in S.d_frame to the caller's buffer (page-locked: direct; else through the pinned staging buffer)
+static int download_frame(SceneStore &S, unsigned char *rgba_out, ptrdiff_t stride, int out_h, int out_w) {
+  const size_t row = (size_t)out_w * 4, bytes = row * out_h;
+  cudaPointerAttributes attr;
+  const bool pinned = cudaPointerGetAttributes(&attr, rgba_out) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+  cudaGetLastError();
+  if (pinned) {
+    if ((size_t)stride == row) RTB_CUDA(cudaMemcpyAsync(rgba_out, S.d_frame, bytes, cudaMemcpyDeviceToHost, S.stream));
+    else RTB_CUDA(cudaMemcpy2DAsync(rgba_out, (size_t)stride, S.d_frame, row, row, out_h, cudaMemcpyDeviceToHost, S.stream));
+    RTB_CUDA(cudaStreamSynchronize(S.stream));
+    return RTB_OK;
+  }
+  if (S.h_frame_bytes < bytes) {
+    if (S.h_frame) cudaFreeHost(S.h_frame);
+    S.h_frame = nullptr;
+    S.h_frame_bytes = 0;
+    RTB_CUDA(cudaMallocHost((void **)&S.h_frame, bytes));
+    S.h_frame_bytes = bytes;
+  }
+  RTB_CUDA(cudaMemcpyAsync(S.h_frame, S.d_frame, bytes, cudaMemcpyDeviceToHost, S.stream));
+  RTB_CUDA(cudaStreamSynchronize(S.stream));
+  for (int y = 0; y < out_h; ++y) memcpy(rgba_out + (size_t)y * stride, S.h_frame + (size_t)y * row, row);
+  return RTB_OK;
 }
 
 static int scene_create_impl(const struct scene *scene, int device, unsigned flags, rtb_scene_t **out, UploadGroup *grp, int member) {
@@ -739,14 +841,47 @@ int rtb_render(const struct scene *scene, unsigned char *rgba_out, int aliasing,
   using clk = std::chrono::steady_clock;
   const auto t0 = clk::now();
   rtb_scene_t *h = nullptr;
-  int rc = rtb_scene_create(scene, 0, RTB_BUILD_ONE_FRAME, &h);
+  int rc = scene_create_impl(scene, 0, RTB_BUILD_ONE_FRAME | defer_tree_flag(scene), &h, nullptr, 0);
   if (rc) return rc;
-  const auto t1 = clk::now();
+  auto t1 = clk::now();
   rtb_frame_opts o;
   memset(&o, 0, sizeof o);
   o.aliasing = aliasing;
   o.nranks = 1;
-  rc = rtb_scene_render(h, &o, rgba_out, stride, out_h, out_w);
+  bool again = false, fixed = false;
+  if (h->store.tree_deferred) {
+    // frame, then the shadow rays it could not answer without the tree (finish_deferred), then one download
+    SceneStore &S = h->store;
+    rtb_frame_opts eff;
+    rc = check_frame(S, &o, out_h, out_w, &eff);
+    if (!rc && (!rgba_out || stride < (ptrdiff_t)out_w * 4)) { set_error(rgba_out ? "stride smaller than a row" : "NULL argument"); rc = RTB_ERR_ARG; }
+    const size_t bytes = (size_t)out_w * 4 * out_h;
+    if (!rc && S.d_frame_bytes < bytes) {
+      if (S.d_frame) cudaFree(S.d_frame);
+      S.d_frame = nullptr;
+      S.d_frame_bytes = 0;
+      RTB_CUDA(cudaMalloc((void **)&S.d_frame, bytes));
+      S.d_frame_bytes = bytes;
+    }
+    if (!rc) rc = render_async(S, eff, S.d_frame, (ptrdiff_t)out_w * 4, out_h, out_w, S.stream);
+    again = rc == RTB_NEED_TREE;
+    if (!rc) rc = finish_frame(S, S.stream);
+    if (!rc) rc = finish_deferred(h, eff, S.d_frame, (ptrdiff_t)out_w * 4, out_h, out_w, &again, &fixed);
+    if (!rc && !again) rc = download_frame(S, rgba_out, stride, out_h, out_w);
+    if (again) rc = RTB_OK;
+  } else
+    rc = rtb_scene_render(h, &o, rgba_out, stride, out_h, out_w);
+  if (again) {
+    // some ray of the frame needed the hierarchy after all (off a light's grid, a fall-back of the projection pass):
+    // the scene once more, with its tree
+    if (trace) fprintf(stderr, "rtb_render: the frame needed the tree; building it\n");
+    rtb_scene_destroy(h);
+    h = nullptr;
+    rc = scene_create_impl(scene, 0, RTB_BUILD_ONE_FRAME, &h, nullptr, 0);
+    if (rc) return rc;
+    t1 = clk::now();
+    rc = rtb_scene_render(h, &o, rgba_out, stride, out_h, out_w);
+  }
   const auto t2 = clk::now();
   rtb_stats st;
   memset(&st, 0, sizeof st);
@@ -830,7 +965,7 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
         if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) r = cuda_fail(e, "cudaDeviceEnablePeerAccess", __FILE__, __LINE__);
         cudaGetLastError();
       }
-      if (!r) r = scene_create_impl(scene, dev, RTB_BUILD_ONE_FRAME, &h, share_upload ? &grp : nullptr, dev);
+      if (!r) r = scene_create_impl(scene, dev, RTB_BUILD_ONE_FRAME | defer_tree_flag(scene), &h, share_upload ? &grp : nullptr, dev);
       if (r) grp.fail();
       const auto t1 = clk::now();
       const auto t2 = clk::now();
@@ -842,6 +977,17 @@ int rtb_render_multi(const struct scene *scene, unsigned char *rgba_out, int ali
         o.nranks = n_devices;
         r = rtb_scene_render_device(h, &o, d_frame, (ptrdiff_t)row, out_h, out_w, nullptr);
         if (!r) r = rtb_scene_sync(h);
+        bool again = r == RTB_NEED_TREE, fixed = false;
+        if (!r) r = finish_deferred(h, o, d_frame, (ptrdiff_t)row, out_h, out_w, &again, &fixed);
+        if (again) {
+          // this device's tiles met a ray that needs the hierarchy: its scene once more, with the tree (from the host:
+          // the shared upload was for the first build)
+          rtb_scene_destroy(h);
+          h = nullptr;
+          r = scene_create_impl(scene, dev, RTB_BUILD_ONE_FRAME, &h, nullptr, 0);
+          if (!r) r = rtb_scene_render_device(h, &o, d_frame, (ptrdiff_t)row, out_h, out_w, nullptr);
+          if (!r) r = rtb_scene_sync(h);
+        }
       }
       const auto t3 = clk::now();
       if (r) errs[(size_t)dev] = g_err;

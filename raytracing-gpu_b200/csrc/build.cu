@@ -796,13 +796,14 @@ SceneStore::~SceneStore() { release(); }
 void SceneStore::release() {
   if (device >= 0) cudaSetDevice(device);
   // (d_prim, d_rast_items, d_rast go back to the per-device cache with the stream: recycle_frame_ctx)
-  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, lgrids, d_fine_acc, d_fine_done};
+  void *ptrs[] = {v0, e1, e2, n0, n1, n2, nodes, materials, lights, order, up, inv_order, d_sched, lgrids, d_fine_acc, d_fine_done, d_stray};
   for (void *p : ptrs) if (p) block_free(p, stream);
   for (void *&p : lgrid_mem) { if (p) block_free(p, stream); p = nullptr; }
   lgrids = nullptr; n_lgrids = 0; lgrid_entries = lgrid_cells = 0;
   v0 = e1 = e2 = n0 = n1 = n2 = nodes = materials = lights = nullptr;
   order = nullptr; up = nullptr; inv_order = nullptr;
   d_fine_acc = nullptr; d_fine_done = nullptr; fine_pixels = fine_items = 0;
+  d_stray = nullptr; stray_pass = 0; stray_items = 0; tree_deferred = false;
   if (h_rast) { cudaFreeHost(h_rast); h_rast = nullptr; }
   if (xchg_block) { cudaStreamSynchronize(stream); cudaFree(xchg_block); xchg_block = nullptr; xchg_nranks = 0; xchg_rank = -1; }
   rast_pending = false; rast_useless = false;
@@ -1005,12 +1006,19 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGro
   const uint32_t cl_max =
       (flags & RTB_BUILD_RADIX_ONLY) || ((flags & RTB_BUILD_ONE_FRAME) && n > ONE_FRAME_SAH_MAX) ? 0u : SAH_CLUSTER_MAX;
   const bool sah_only = tree && cl_max && n <= SAH_WHOLE_MAX;    // the whole scene is one cluster: no sort, no radix tree
+  // Deferred tree (rtb_render on big scenes whose frame will take its first rays from the projection pass and its shadow
+  // rays from the light grids): everything the frame needs except the nodes -- keys, sort, slot order, permuted
+  // triangles, grids.  k_emit, k_live, the scan, k_compact, their 1.3 GB of scratch and two host round trips are left out.
+  const bool one_frame_grids = (unsigned long long)hs->camera.width * (unsigned long long)hs->camera.height >= 4ull * n &&
+                               !(flags & RTB_BUILD_NO_LIGHT_GRIDS);
+  const bool defer = tree && !sah_only && cl_max == 0 && (flags & RTB_BUILD_DEFER_TREE) && (flags & RTB_BUILD_ONE_FRAME) &&
+                     n >= (1u << 15) && one_frame_grids;
   Cluster *d_clusters = nullptr;
   uint32_t *d_n_clusters = nullptr;
   const uint32_t clusters_cap = cl_max ? 2u * (n / cl_max) + 2u : 1u;   // sibling clusters hold > cl_max triangles together
   S->builder = 0;
   if (tree) {
-    const uint32_t n_inner = n - 1;
+    const uint32_t n_inner = defer ? (n < MODE_SAMPLE_MAX + 1u ? n : MODE_SAMPLE_MAX + 1u) - 1u : n - 1;   // deferred: the sample trees only
     CK(tmp.alloc(&raw, n_inner)); CK(tmp.alloc(&visit, n_inner)); CK(tmp.alloc(&child_h, 2ull * n_inner));
     CK(tmp.alloc(&root_info, 4)); CK(tmp.alloc(&raw_parent, n_inner));
     CK(tmp.alloc(&d_mode, 8));
@@ -1071,7 +1079,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGro
   uint32_t *live = nullptr, *scan_scratch = nullptr;
   unsigned int *d_stats = nullptr;
   size_t ssw = 0;
-  if (tree) {
+  if (tree && !defer) {
     // ---- topology: radix tree over the sorted keys, clusters rebuilt with surface-area splits ----
     const uint32_t n_inner = n - 1;
     ssw = scan_scratch_words(n_inner + 1);
@@ -1124,7 +1132,18 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGro
                                                S->e2, S->n0, S->n1, S->n2);
     ++launches;
   }
-  if (tree) {
+  if (tree && defer) {
+    // no nodes: one dummy node keeps the pointers valid, the frame never reads it (FrameArgs::need_tree)
+    int h_mode[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    RTB_CUDA(cudaMemcpyAsync(h_mode, d_mode, sizeof h_mode, cudaMemcpyDeviceToHost, st));
+    CK(dev_alloc(&S->nodes, NODE_QUADS));
+    k_single_node<<<1, 1, 0, st>>>(0u, S->nodes);
+    ++launches;
+    RTB_CUDA(cudaStreamSynchronize(st));
+    S->key_mode = h_mode[0];
+    for (int k = 0; k < 4; ++k) S->mode_cost[k] = h_mode[1 + k];
+    S->n_nodes = 1; S->root = 0; S->height = 1; S->n_leaves = 0; S->max_leaf = 0;
+  } else if (tree) {
     const uint32_t n_inner = n - 1;
     k_live<<<(n_inner + BT - 1) / BT, BT, 0, st>>>(raw, n_inner, live);
     ++launches;
@@ -1172,6 +1191,7 @@ int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGro
   S->pad_unit = SLIVER_K * 1.1920929e-7f * (amax + S->origin_radius);     // as k_emit / k_sah_clusters compute it
   S->n_tris = n; S->n_objects = (uint32_t)n_obj; S->n_lights = (uint32_t)n_light;
   S->has_tree = tree;
+  S->tree_deferred = defer;
   S->camera = hs->camera;
   // shadow-ray grids: resident scenes, and single frames with enough samples per triangle to repay
   // them (C5: 1.9 ms of build per light per 10 M triangles against 80 ps saved per shadow ray, i.e.

@@ -240,8 +240,8 @@ __global__ void __launch_bounds__(256) k_lg_stats(const uint32_t *cell_start, si
 }
 
 // ---- the lookup ----
-// 1: some candidate on the ray, 0: none, -1: this ray has to walk the tree (its point is off the grid, or its
-// origin outside the box the regions were bounded for).
+// 1: some candidate on the ray, 0: none, < 0: this ray has to walk the tree (-2: its origin is outside the box the
+// regions were bounded for, -3: its point is off the grid, -4: a point light's projection is not usable for it).
 //
 // Three loops per chunk of 32 entries, because the lanes of a warp walk different lists in lockstep and a
 // single loop made the warp pay the most expensive branch in almost every iteration: (1) the entries'
@@ -252,14 +252,14 @@ __global__ void __launch_bounds__(256) k_lg_stats(const uint32_t *cell_start, si
 // on C5 -- a record test is ~35 instructions, the queue traffic around it costs more than the idle lanes
 // (profiles/r2_ncu_kframe_coop.txt).
 __device__ __forceinline__ int lg_any(const DevScene &sc, const LightGrid &g, const V3 o, const V3 d, int &hit) {
-  if (!(o.x >= g.bmin.x && o.x <= g.bmax.x && o.y >= g.bmin.y && o.y <= g.bmax.y && o.z >= g.bmin.z && o.z <= g.bmax.z)) return -1;
+  if (!(o.x >= g.bmin.x && o.x <= g.bmax.x && o.y >= g.bmin.y && o.y <= g.bmax.y && o.z >= g.bmin.z && o.z <= g.bmax.z)) return -2;
   float x, y, den;
   lg_project(g, o, x, y, den);
   const float fx = (x - g.x0) * g.inv_cell, fy = (y - g.y0) * g.inv_cell;
   const float fi = floorf(fx), fj = floorf(fy);
-  if (!(fi >= 0.0f && fj >= 0.0f && fi <= (float)(g.nx - 1) && fj <= (float)(g.ny - 1))) return -1;      // NaN too
+  if (!(fi >= 0.0f && fj >= 0.0f && fi <= (float)(g.nx - 1) && fj <= (float)(g.ny - 1))) return -3;      // NaN too
   if (g.kind == 2 && !(fabsf(den) > 1e-6f * (fabsf(o.x - g.org.x) + fabsf(o.y - g.org.y) + fabsf(o.z - g.org.z)) &&
-                       fabsf(x) <= LG_PERSP_LIMIT && fabsf(y) <= LG_PERSP_LIMIT)) return -1;
+                       fabsf(x) <= LG_PERSP_LIMIT && fabsf(y) <= LG_PERSP_LIMIT)) return -4;
   Best b;
   b.dist = INF; b.id = 0x7fffffff; b.slot = -1;
   for (uint32_t k = 0; k < g.n_large; ++k)

@@ -105,6 +105,16 @@ struct XchgView {
   const RastItem *in[XCHG_MAX_RANKS];   // this rank's inbox: the segment of source s (local memory)
 };
 
+struct StrayQuery {       // 48 bytes
+  float ox, oy, oz, dx, dy, dz;
+  unsigned sample;        // px | py << 16
+  unsigned light;
+  unsigned item;          // the warp tile (work item) the sample belongs to
+  unsigned occluded;      // written by k_stray_any
+  unsigned pad[2];
+};
+constexpr unsigned STRAY_CAP = 1024;
+
 struct FrameArgs {
   DevCamera cam;
   int aliasing;
@@ -123,6 +133,17 @@ struct FrameArgs {
   uint2 *fine_acc;
   unsigned int *fine_done;
   const unsigned int *fine_hot;
+  // deferred tree (SceneStore::tree_deferred): a ray that would have to walk the hierarchy sets *need_tree instead
+  // (its sample is then wrong: the caller builds the tree and renders again); nullptr: the scene has its tree
+  unsigned int *need_tree;
+  // ... except shadow rays that are merely off their light's grid (a hit point outside the scene's box: the rounded test
+  // accepts on noise far beside a triangle seen edge-on; C5: 26 of 125 M).  They are listed (stray_mode 1, count in
+  // need_tree[14] = rast[21]), resolved against every triangle by k_stray_any, and the warp tiles they belong to are
+  // rendered once more with the answers looked up (stray_mode 2, only_items tiles through item_order).
+  StrayQuery *stray;
+  unsigned stray_cap;
+  int stray_mode;
+  unsigned only_items;
   unsigned long long *counters;   // [8]: primary, shadow, bounce, node visits, tri tests
   // primary visibility by projection (raster.cuh); prim == nullptr: every ray walks the tree
   unsigned long long *prim;       // [H * W] new_dist bits << 32 | triangle id of the nearest primary candidate, ~0: none
@@ -166,6 +187,9 @@ void block_free(void *p, cudaStream_t st);
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
                  unsigned long long *launches, cudaEvent_t *marks = nullptr);
 unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
+// deferred tree: the listed shadow rays against every triangle; then the frame kernel alone (no projection pass) on fa.only_items tiles
+int launch_stray_any(const DevScene &sc, StrayQuery *q, const unsigned *count, int sm_count, cudaStream_t st);
+int launch_frame_only(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st);
 int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
                       uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
                       cudaStream_t st, int *result_in_alt, unsigned *d_hot, float per_share);

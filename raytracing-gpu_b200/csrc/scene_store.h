@@ -34,6 +34,12 @@ struct SceneStore {
   int key_mode = 0;                     // sort-key layout the build chose (build.cu morton_key)
   int mode_cost[4] = {0, 0, 0, 0};      // surface-area cost of the four sample trees (0: not evaluated)
   bool has_tree = false;
+  // RTB_BUILD_DEFER_TREE (rtb_render only): sort, slot order and light grids are built, the node array is not; a
+  // frame whose rays turn out to need it says so in rast[7] and rtb_render builds the scene again with the tree
+  bool tree_deferred = false;
+  StrayQuery *d_stray = nullptr;       // deferred tree: STRAY_CAP listed shadow rays, then STRAY_CAP work-item ids (rtb_internal.h)
+  int stray_pass = 0;                  // 2: the frame kernel alone on stray_items listed tiles, answers looked up
+  unsigned stray_items = 0;
   float abs_max = 0;
   float pad_unit = 0;                   // needle-padding unit of the leaf boxes (pad.cuh)
   float origin_radius = 0;              // ray-origin radius the sliver padding was built for (build.cu)
@@ -130,6 +136,8 @@ struct UploadGroup {
   }
 };
 
+constexpr unsigned RTB_BUILD_DEFER_TREE = 1u << 16;      // internal (rtb_render): see SceneStore::tree_deferred
+constexpr int RTB_NEED_TREE = -100;                       // internal return code: this frame cannot run on a deferred tree
 int build_scene(const struct scene *hs, unsigned flags, SceneStore *S, UploadGroup *grp = nullptr, int member = 0);
 // per-device cache of stream, events and frame buffers (api.cu)
 int acquire_frame_ctx(int device, SceneStore &S);

@@ -46,6 +46,7 @@ struct Counters {
   // shadow cache (-DRTB_SHADOW_CACHE, A/B only): the slot of the triangle that occluded this lane's last
   // shadow ray towards an even / odd light, tested first for the next sample.  Slower on C5.
   int occ0 = -1, occ1 = -1;
+  unsigned sample = 0, item = 0;      // the sample and work item being shaded (stray shadow rays are listed with them)
 };
 
 struct Best {
@@ -273,8 +274,36 @@ __device__ __noinline__ bool shadow_walk(const WalkArgs w, const V3 P, const V3 
 }
 
 // gpu/light.cu:50-127
+// Deferred tree (FrameArgs::need_tree): a shadow ray that is off its light's grid (code < 0 from lg_any, -1: the light has
+// no grid).  First pass: list it and answer "not occluded" for now; second pass (its tile rendered again): the answer
+// k_stray_any found.  No list, or a full one: the whole frame again.  Out of line: one ray in millions comes here.
+__device__ __noinline__ int stray_shadow_ray(const FrameArgs &fa, int code, const V3 P, const V3 dir, unsigned light, unsigned sample,
+                                             unsigned item) {
+  unsigned *nt = fa.need_tree;
+  atomicAdd(nt + 9 - code, 1u);      // rast[17]: no grid, [18] outside the box, [19] off the grid, [20] projection
+  if (fa.stray_mode == 2) {
+    const unsigned cnt = min(nt[14], fa.stray_cap);
+    int answer = 0;
+    for (unsigned k = 0; k < cnt; ++k)
+      if (fa.stray[k].sample == sample && fa.stray[k].light == light) answer = (int)fa.stray[k].occluded;
+    return answer;
+  }
+  if (fa.stray_mode == 1) {
+    const unsigned k = atomicAdd(nt + 14, 1u);
+    if (k < fa.stray_cap) {
+      StrayQuery q;
+      q.ox = P.x; q.oy = P.y; q.oz = P.z; q.dx = dir.x; q.dy = dir.y; q.dz = dir.z;
+      q.sample = sample; q.light = light; q.item = item; q.occluded = 0u; q.pad[0] = q.pad[1] = 0u;
+      fa.stray[k] = q;
+      return 0;
+    }
+  }
+  *nt = 1u;
+  return 0;
+}
+
 template <int TRACER, bool COUNT>
-__device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 P, const V3 Nrm, Counters &c) {
+__device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 P, const V3 Nrm, Counters &c, const FrameArgs *fa = nullptr) {
   const float4 m0 = __ldg(sc.materials + 2 * obj);
   const uint32_t ka = __float_as_uint(m0.x), kd = __float_as_uint(m0.y), ks = __float_as_uint(m0.z);
   const float ns = m0.w;
@@ -308,6 +337,7 @@ __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 
         occluded = lg_any(sc, sc.lgrids[i], P, dir, hit);
 #endif
       }
+      if (occluded < 0 && fa && fa->need_tree) occluded = stray_shadow_ray(*fa, occluded, P, dir, i, c.sample, c.item);
       if (occluded < 0) {
         if (COUNT) { Best b; occluded = trace<TRACER, true, true>(sc, P, dir, b, c) ? 1 : 0; }      // the counting frame: inline, counters live
         else {
@@ -372,13 +402,14 @@ __device__ uint32_t shade_sample(const DevScene &sc, const FrameArgs &fa, bool u
     uint32_t tc;
     bool hit;
     if (use_prim) { hit = prim_lookup(sc, fa, px, py, o, d, b); use_prim = false; }
+    else if (fa.need_tree) { *fa.need_tree = 1u; atomicAdd(fa.need_tree + 9, 1u); hit = false; }      // rast[16]: nearest-hit rays without a tree
     else hit = trace<TRACER, false, COUNT>(sc, o, d, b, c);
     hit = rejoin(hit);
     if (hit) {
       V3 P, N;
       hit_record(sc, o, d, b.slot, P, N);
       const int obj = __float_as_int(__ldg(sc.e1 + b.slot).w);
-      tc = apply_light<TRACER, COUNT>(sc, obj, b.slot, P, N, c);
+      tc = apply_light<TRACER, COUNT>(sc, obj, b.slot, P, N, c, &fa);
       r = __ldg(sc.materials + 2 * obj + 1).x;
       if (r > 0) {
         d = vsub(d, vscale(N, 2 * vdot(N, d)));
@@ -444,8 +475,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int a = fa.aliasing, aa = a * a;
   uint2 *acc = s_acc[warp];
-  const unsigned n_items = frame_items(fa);
-  const unsigned hot = FINE && fa.item_order ? min(__ldg(fa.fine_hot), n_items) : 0u;
+  const unsigned n_items = fa.only_items ? fa.only_items : frame_items(fa);      // only_items: the tiles of item_order, nothing else
+  const unsigned hot = FINE && fa.item_order && !fa.only_items ? min(__ldg(fa.fine_hot), n_items) : 0u;
   const unsigned n_fine = hot * (unsigned)aa, total = n_items + hot * (unsigned)(aa - 1);
   const bool use_prim = TRACER == RTB_TRACER_TREE && !COUNT && rast_active(fa);
   Counters c = {0, 0, 0, 0, 0};
@@ -472,6 +503,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
       const int px = a * lx0 + sx, py = a * ly0 + sy;
       if (px < fa.cam.W && py < fa.cam.H) {
+        c.sample = (unsigned)px | ((unsigned)py << 16); c.item = item;
         const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
         uint2 *dst = fine ? fa.fine_acc + (size_t)(ly0 + sy / a) * fa.out_w + (lx0 + sx / a) : acc + (sy / a) * 8 + sx / a;
         atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
@@ -852,6 +884,42 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
   if (count) return launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st);
   if (fa.fine_acc) return launch_frame_t<RTB_TRACER_TREE, false, true>(sc, fa, sm_count, st);
   return launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
+}
+
+// ---- deferred tree: the few shadow rays that are off their light's grid, against every triangle ----
+// (the definition of has_direct_hit, gpu/light.cu:29-36 + gpu/hit.cu:241-253, with no cull at all; a thread per triangle
+// slot, the rays from shared memory; 26 rays x 10 M triangles on C5: 0.2 ms)
+__global__ void __launch_bounds__(256) k_stray_any(const DevScene sc, StrayQuery *q, const unsigned *count) {
+  __shared__ float s_ray[STRAY_CAP][6];
+  __shared__ unsigned s_hit[STRAY_CAP];
+  const unsigned n = min(*count, STRAY_CAP);
+  for (unsigned k = threadIdx.x; k < n; k += 256) {
+    s_ray[k][0] = q[k].ox; s_ray[k][1] = q[k].oy; s_ray[k][2] = q[k].oz;
+    s_ray[k][3] = q[k].dx; s_ray[k][4] = q[k].dy; s_ray[k][5] = q[k].dz;
+    s_hit[k] = 0u;
+  }
+  __syncthreads();
+  for (uint32_t s = blockIdx.x * 256 + threadIdx.x; s < sc.n_tris; s += gridDim.x * 256) {
+    const float4 a4 = __ldg(sc.v0 + s), b4 = __ldg(sc.e1 + s), c4 = __ldg(sc.e2 + s);
+    for (unsigned k = 0; k < n; ++k) {
+      float dist;
+      if (tri_candidate(mk(s_ray[k][0], s_ray[k][1], s_ray[k][2]), mk(s_ray[k][3], s_ray[k][4], s_ray[k][5]), a4, b4, c4, dist)) s_hit[k] = 1u;
+    }
+  }
+  __syncthreads();
+  for (unsigned k = threadIdx.x; k < n; k += 256)
+    if (s_hit[k]) q[k].occluded = 1u;
+}
+
+int launch_stray_any(const DevScene &sc, StrayQuery *q, const unsigned *count, int sm_count, cudaStream_t st) {
+  k_stray_any<<<sm_count * 4, 256, 0, st>>>(sc, q, count);
+  RTB_CUDA(cudaGetLastError());
+  return RTB_OK;
+}
+
+int launch_frame_only(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
+  RTB_CUDA(cudaMemsetAsync(fa.tile_counter, 0, sizeof(unsigned int), st));
+  return launch_frame_kernel(sc, fa, RTB_TRACER_TREE, false, sm_count, st);
 }
 
 // ---- longest-first item order from the costs the previous frame left (api.cu) ----

@@ -168,3 +168,32 @@ def test_c5_samples_against_exhaustive_search_and_the_oracle(gpu):
         assert (d > 1).sum() == 0, int((d > 1).sum())
     finally:
         ds.close()
+
+
+def test_one_shot_render_without_the_tree_and_with_it(gpu, monkeypatch):
+    """rtb_render on a scene above 2^18 triangles first tries the frame without the node array (projection pass + light
+    grids need only the sorted slot order); the frame must be the resident scene's, byte for byte.  With a mirror in
+    the scene the host check keeps the tree; with the check skipped (RTB_DEFER_TREE=2 is read once per process, so
+    this runs in a child process) the frame finds out on the device and is rendered again -- same bytes."""
+    import subprocess, sys, os
+    hs = pyrtb.HostScene.terrain(364, 640, 360)
+    assert hs.triangle_count > 1 << 18
+    ds = pyrtb.DeviceScene(hs, 3)
+    try:
+        want = ds.render()
+    finally:
+        ds.close()
+    got = pyrtb.render_oneshot(hs, 3)
+    assert np.array_equal(got, want)
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import pyrtb\n"
+            "hs = pyrtb.HostScene.terrain(364, 640, 360)\n"
+            "hs.s.objects[0].nr = 0.5\n"
+            "ds = pyrtb.DeviceScene(hs, 3); want = ds.render(); ds.close()\n"
+            "got = pyrtb.render_oneshot(hs, 3)\n"
+            "assert (want != pyrtb.render_oneshot(pyrtb.HostScene.terrain(364, 640, 360), 3)).any(), 'the mirror must show'\n"
+            "print('SAME' if np.array_equal(got, want) else 'DIFFERENT')\n") % os.path.dirname(pyrtb.__file__)
+    for mode in ("1", "2"):
+        env = dict(os.environ, RTB_DEFER_TREE=mode, RTB_TRACE="1")
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
+        assert r.returncode == 0 and "SAME" in r.stdout, (mode, r.stdout[-500:], r.stderr[-2000:])
+        assert ("the frame needed the tree" in r.stderr) == (mode == "2"), (mode, r.stderr[-2000:])
