@@ -437,6 +437,7 @@ def run_ours(args):
             pyrtb.render_oneshot(hs, ALIASING, out=host_img)
             per_call.append(1e3 * (time.perf_counter() - t1))
         mean_s = (time.perf_counter() - t0) / e2e_steps
+        oneshot_img = host_img.copy()
         # The call makes ~400 driver calls and ~12 host round trips; on a shared host one call in ten is held up for
         # tens to hundreds of ms somewhere among them (80 calls in a row: 52-53 ms typical, excursions to 450).
         # value = the MEDIAN call; the mean and every call are beside it.
@@ -538,6 +539,11 @@ def run_ours(args):
             oneshot_diff = int((single != multi_img).any(axis=-1).sum())
             if oneshot_diff > 100:
                 raise SystemExit("rtb_render_multi frame differs from the single-GPU frame in %d pixels" % oneshot_diff)
+        else:
+            # the one-shot call renders without the node array (deferred tree, stray shadow rays by brute force): same pixels?
+            oneshot_diff = int((composed != oneshot_img).any(axis=-1).sum())
+            if oneshot_diff > 100:
+                raise SystemExit("rtb_render frame differs from the resident scene's frame in %d pixels" % oneshot_diff)
         checksum = int(composed.astype(np.uint64).sum())
 
     if rank == 0:

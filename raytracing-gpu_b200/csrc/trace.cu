@@ -302,7 +302,7 @@ __device__ __noinline__ int stray_shadow_ray(const FrameArgs &fa, int code, cons
   return 0;
 }
 
-template <int TRACER, bool COUNT>
+template <int TRACER, bool COUNT, bool DEFER = false>
 __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 P, const V3 Nrm, Counters &c, const FrameArgs *fa = nullptr) {
   const float4 m0 = __ldg(sc.materials + 2 * obj);
   const uint32_t ka = __float_as_uint(m0.x), kd = __float_as_uint(m0.y), ks = __float_as_uint(m0.z);
@@ -337,7 +337,7 @@ __device__ uint32_t apply_light(const DevScene &sc, int obj, int slot, const V3 
         occluded = lg_any(sc, sc.lgrids[i], P, dir, hit);
 #endif
       }
-      if (occluded < 0 && fa && fa->need_tree) occluded = stray_shadow_ray(*fa, occluded, P, dir, i, c.sample, c.item);
+      if (DEFER && occluded < 0) occluded = stray_shadow_ray(*fa, occluded, P, dir, i, c.sample, c.item);
       if (occluded < 0) {
         if (COUNT) { Best b; occluded = trace<TRACER, true, true>(sc, P, dir, b, c) ? 1 : 0; }      // the counting frame: inline, counters live
         else {
@@ -386,7 +386,7 @@ namespace {
 
 // raytrace kernel body (gpu/raytracer.cu:87-129) for one sample
 // use_prim: the first ray's winner comes from the projection pass (raster.cuh prim_lookup)
-template <int TRACER, bool COUNT>
+template <int TRACER, bool COUNT, bool DEFER = false>
 __device__ uint32_t shade_sample(const DevScene &sc, const FrameArgs &fa, bool use_prim, int px, int py, Counters &c) {
   const DevCamera &cam = fa.cam;
   V3 o, d;
@@ -402,14 +402,14 @@ __device__ uint32_t shade_sample(const DevScene &sc, const FrameArgs &fa, bool u
     uint32_t tc;
     bool hit;
     if (use_prim) { hit = prim_lookup(sc, fa, px, py, o, d, b); use_prim = false; }
-    else if (fa.need_tree) { *fa.need_tree = 1u; atomicAdd(fa.need_tree + 9, 1u); hit = false; }      // rast[16]: nearest-hit rays without a tree
+    else if (DEFER) { *fa.need_tree = 1u; atomicAdd(fa.need_tree + 9, 1u); hit = false; }      // rast[16]: nearest-hit rays without a tree
     else hit = trace<TRACER, false, COUNT>(sc, o, d, b, c);
     hit = rejoin(hit);
     if (hit) {
       V3 P, N;
       hit_record(sc, o, d, b.slot, P, N);
       const int obj = __float_as_int(__ldg(sc.e1 + b.slot).w);
-      tc = apply_light<TRACER, COUNT>(sc, obj, b.slot, P, N, c, &fa);
+      tc = apply_light<TRACER, COUNT, DEFER>(sc, obj, b.slot, P, N, c, DEFER ? &fa : nullptr);
       r = __ldg(sc.materials + 2 * obj + 1).x;
       if (r > 0) {
         d = vsub(d, vscale(N, 2 * vdot(N, d)));
@@ -465,7 +465,7 @@ __device__ __forceinline__ bool frame_item(const FrameArgs &fa, unsigned item, i
 // the tiles per rank the slowest tile sets the frame's tail (a tile over a cell of a light grid that hundreds
 // of line regions cross takes milliseconds); cut into rounds taken by different warps it no longer does.
 // Every other tile stays whole: its rounds share one SM's L1 (all tiles as rounds cost 19 % at any N).
-template <int TRACER, bool COUNT, bool FINE>
+template <int TRACER, bool COUNT, bool FINE, bool DEFER = false>
 __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(const DevScene sc, const FrameArgs fa) {
   // Per output pixel of the warp tile: the channel sums of its a x a samples (x: r | g << 16,
   // y: b).  The reference sums the u8 channels as floats (gpu/raytracer.cu:62-70); sums of at
@@ -503,8 +503,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, RTB_FRAME_MINBLOCKS) k_frame(co
       const int sx = 8 * (q % a) + (lane & 7), sy = 4 * (q / a) + (lane >> 3);
       const int px = a * lx0 + sx, py = a * ly0 + sy;
       if (px < fa.cam.W && py < fa.cam.H) {
-        c.sample = (unsigned)px | ((unsigned)py << 16); c.item = item;
-        const uint32_t col = shade_sample<TRACER, COUNT>(sc, fa, use_prim, px, py, c);
+        if (DEFER) { c.sample = (unsigned)px | ((unsigned)py << 16); c.item = item; }
+        const uint32_t col = shade_sample<TRACER, COUNT, DEFER>(sc, fa, use_prim, px, py, c);
         uint2 *dst = fine ? fa.fine_acc + (size_t)(ly0 + sy / a) * fa.out_w + (lx0 + sx / a) : acc + (sy / a) * 8 + sx / a;
         atomicAdd(&dst->x, ch_r(col) | (ch_g(col) << 16));
         atomicAdd(&dst->y, ch_b(col));
@@ -801,10 +801,10 @@ int build_light_grids(SceneStore &S, const struct light *lights, size_t n_lights
   return RTB_OK;
 }
 
-template <int TRACER, bool COUNT, bool FINE = false>
+template <int TRACER, bool COUNT, bool FINE = false, bool DEFER = false>
 static int launch_frame_t(const DevScene &sc, const FrameArgs &fa, int sm_count, cudaStream_t st) {
   const size_t smem = 0;
-  auto kern = k_frame<TRACER, COUNT, FINE>;
+  auto kern = k_frame<TRACER, COUNT, FINE, DEFER>;
 #ifdef RTB_CARVEOUT   /* A/B only: shared-memory share of the unified L1, percent */
   RTB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, RTB_CARVEOUT));
 #endif
@@ -882,6 +882,7 @@ static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int trac
     return count ? launch_frame_t<RTB_TRACER_BRUTE, true>(sc, fa, sm_count, st)
                  : launch_frame_t<RTB_TRACER_BRUTE, false>(sc, fa, sm_count, st);
   if (count) return launch_frame_t<RTB_TRACER_TREE, true>(sc, fa, sm_count, st);
+  if (fa.need_tree) return launch_frame_t<RTB_TRACER_TREE, false, false, true>(sc, fa, sm_count, st);      // deferred tree (one-shot)
   if (fa.fine_acc) return launch_frame_t<RTB_TRACER_TREE, false, true>(sc, fa, sm_count, st);
   return launch_frame_t<RTB_TRACER_TREE, false>(sc, fa, sm_count, st);
 }
