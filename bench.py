@@ -256,9 +256,19 @@ def run_ours(args):
         raise SystemExit("bench.py needs a GPU per rank: librtb200 has no CPU fallback")
     L = pyrtb.lib()
 
+    host_pg = dist.new_group(backend="gloo") if dist is not None else None
+
     def barrier():
         if dist is not None:
             dist.barrier()
+
+    def host_barrier():
+        """the waiting ranks sleep on the host: an NCCL barrier is a kernel that spins on every waiting rank's GPU, and
+        rank 0's N-device render() would share the devices with it"""
+        if dist is not None:
+            import torch
+            torch.cuda.synchronize()
+            dist.barrier(group=host_pg)
 
     def max_over_ranks(x):
         if dist is None:
@@ -459,7 +469,7 @@ def run_ours(args):
         # (rtb_render_multi: every device uploads the scene and builds its hierarchy, renders its tiles
         # into device 0's frame over NVLink; rank 0 downloads).  The other ranks wait.
         e2e_steps = max(2, min(args.steps, args.e2e_steps))
-        barrier()
+        host_barrier()
         e2e_s, mean_s, per_call = 0.0, 0.0, []
         if rank == 0:
             for _ in range(2):                                        # warm-up: contexts, peer access, pools
@@ -472,7 +482,7 @@ def run_ours(args):
             mean_s = (time.perf_counter() - t0) / e2e_steps
             e2e_s = float(np.median(per_call)) / 1e3          # as at N = 1: the median call, mean and every call beside it
             multi_img = host_img.copy()
-        barrier()
+        host_barrier()
         h2d = hs.triangle_count * 72 + 72 * hs.s.object_count + 28 * hs.s.light_count + 48
         e2e = {"value": rays / e2e_s / 1e6 if rank == 0 else None, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d) * world,
                "d2h_bytes_per_step": frame_bytes, "ms_per_step": 1e3 * e2e_s, "statistic": "median of %d calls" % e2e_steps,
