@@ -166,6 +166,10 @@ def test_c5_samples_against_exhaustive_search_and_the_oracle(gpu):
         assert (want >= 0).mean() > 0.5
         d, o = _colours_against_the_oracle(hs, ds, 40, 0xC5)
         assert (d > 1).sum() == 0, int((d > 1).sum())
+        # the drop-in call on this scene renders without the node array and resolves the ~26 shadow rays that leave
+        # their light's grid against all 10 M triangles (k_stray_any): the resident scene's frame, byte for byte
+        want = ds.render()
+        assert np.array_equal(pyrtb.render_oneshot(hs, 3), want)
     finally:
         ds.close()
 
