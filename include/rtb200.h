@@ -141,10 +141,12 @@ int rtb_scene_set_camera(rtb_scene_t *h, const struct camera *cam);
 #define RTB_KERNEL_PER_SAMPLE  0
 #define RTB_KERNEL_WAVEFRONT   1
 
-/* Primary rays all pass through the camera position, so their candidates per triangle are a
- * screen rectangle: the projected culling box.  RASTER tests exactly those (same per-ray test,
- * same winner as the tree walk) and falls back to the tree by itself when a box straddles the
- * camera plane too often or the rectangles cover too much; AUTO = RASTER from 2^15 triangles. */
+/* Primary rays all pass through the camera position, so the rays the reference's rounded ray/triangle test
+ * can accept for one triangle are a region of the screen bounded by three offset lines (csrc/region.cuh: a
+ * bound derived from the operation sequence of gpu/hit.cu:20-37, not a padded box).  RASTER runs the per-ray
+ * test on exactly those samples (same test, same winner as the exhaustive search of gpu/hit.cu:84-114) and
+ * falls back to the tree by itself when the regions cover too much or the item list overflows;
+ * AUTO = RASTER for every scene, except for a camera whose last frame fell back. */
 #define RTB_PRIMARY_AUTO    0
 #define RTB_PRIMARY_TREE    1
 #define RTB_PRIMARY_RASTER  2

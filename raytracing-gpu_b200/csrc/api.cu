@@ -226,8 +226,8 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
   const bool want_raster = o.primary == RTB_PRIMARY_RASTER || (o.primary == RTB_PRIMARY_AUTO && S.n_tris >= RASTER_AUTO_MIN_TRIS);
   if (want_raster && (S.inv_order || !S.has_tree) && o.tracer == RTB_TRACER_TREE && !o.count_rays &&
       o.frame_kernel == RTB_KERNEL_PER_SAMPLE && fa.cam.W <= 65535 && fa.cam.H <= 65535) {      // items hold 16-bit sample corners
-    // a frame of this camera that ran the pass and still walked the tree (boxes across the camera
-    // plane, rectangles covering too much) says the next one will too: AUTO does not try again
+    // a frame of this camera that ran the pass and still walked the tree (regions covering too much, the item
+    // list full) says the next one will too: AUTO does not try again
     const unsigned long long key[4] = {S.camera_gen, (unsigned long long)fa.cam.W << 32 | (unsigned)fa.cam.H,
                                        (unsigned long long)o.rank << 32 | (unsigned)o.nranks, 0ull};
     const bool same = memcmp(key, S.rast_key, sizeof key) == 0;

@@ -402,7 +402,7 @@ class DeviceScene:
         return {k: getattr(st, k) for k, _ in Stats._fields_}
 
     def raster_state(self):
-        """rtb_scene_raster_state: items, gave-up flag, rectangle area, boxes across the camera plane"""
+        """rtb_scene_raster_state: items, gave-up flag, samples the items cover, triangles with two-part regions, light grids"""
         out = (C.c_uint * 8)()
         fn = lib().rtb_scene_raster_state
         fn.argtypes = [C.c_void_p, C.c_void_p]
