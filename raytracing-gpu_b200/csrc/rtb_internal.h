@@ -165,7 +165,7 @@ size_t wave_scratch_floats(int aliasing, int sm_count);   // size of FrameArgs::
 // ---- device-side build (build.cu / sort.cu) ----
 int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_keys_alt, uint32_t *d_vals_alt,
                              size_t n, int key_bits, uint32_t *d_scratch, size_t scratch_words,
-                             cudaStream_t st, int *result_in_alt, unsigned long long *launches);
+                             cudaStream_t st, int *result_in_alt, unsigned long long *launches, int low_bit = 0);
 size_t radix_sort_scratch_words(size_t n);
 int dev_exclusive_scan_u32(uint32_t *d_data, size_t n, uint32_t *d_scratch, size_t scratch_words, bool inclusive,
                            cudaStream_t st, unsigned long long *launches);

@@ -248,11 +248,11 @@ size_t radix_sort_scratch_words(size_t n) {
   return counts + scan_scratch_words(counts);
 }
 
-// Sorts (key, value) pairs by the low `key_bits` bits of the key, stable.  Ping-pongs
+// Sorts (key, value) pairs by bits [low_bit, key_bits) of the key, stable (keys equal in those bits keep their order).  Ping-pongs
 // between the primary and the alternate buffers; *result_in_alt tells where the result is.
 int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_keys_alt, uint32_t *d_vals_alt,
                              size_t n, int key_bits, uint32_t *d_scratch, size_t scratch_words, cudaStream_t st,
-                             int *result_in_alt, unsigned long long *launches) {
+                             int *result_in_alt, unsigned long long *launches, int low_bit) {
   *result_in_alt = 0;
   if (n == 0) return RTB_OK;
   if (n >= (1ull << 32)) { set_error("radix sort: more than 2^32-1 keys"); return RTB_ERR_LIMIT; }
@@ -263,11 +263,12 @@ int dev_radix_sort_pairs_u64(uint64_t *d_keys, uint32_t *d_vals, uint64_t *d_key
   const size_t counts = (size_t)tiles * RS_RADIX;
   uint32_t *d_counts = d_scratch;
   uint32_t *d_scan_scratch = d_scratch + counts;
-  const int passes = (key_bits + 7) / 8;
+  if (low_bit < 0 || low_bit >= key_bits) low_bit = 0;
+  const int passes = (key_bits - low_bit + 7) / 8;
   uint64_t *kin = d_keys, *kout = d_keys_alt;
   uint32_t *vin = d_vals, *vout = d_vals_alt;
   for (int p = 0; p < passes; ++p) {
-    const int shift = 8 * p;
+    const int shift = low_bit + 8 * p;
     k_rs_histogram<<<tiles, RS_THREADS, 0, st>>>(kin, n, shift, d_counts, tiles);
     if (launches) ++*launches;
     int rc = dev_exclusive_scan_u32(d_counts, counts, d_scan_scratch, scratch_words - counts, false, st, launches);
