@@ -400,7 +400,29 @@ static int render_async(SceneStore &S, const rtb_frame_opts &o, unsigned char *d
     RTB_CUDA(cudaEventRecord(S.ev1, st));
     return RTB_OK;
   }
-  rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches, S.profile ? S.kev : nullptr);
+  // one-shot frames (deferred tree: rtb_render) have no previous frame to order their items by: an estimate instead
+  ItemEstimate est_args, *est = nullptr;
+  if (S.tree_deferred && g_schedule && fa.prim && !fa.item_order) {
+    const unsigned n_est = frame_item_count(out_w, out_h, o.nranks);
+    const size_t cap = ((size_t)n_est + 255) & ~(size_t)255;
+    if (S.sched_items < cap) {
+      if (S.d_sched) cudaFreeAsync(S.d_sched, st);
+      S.d_sched = nullptr; S.d_item_order = nullptr; S.sched_items = 0;
+      const size_t bytes = cap * (4 + 8 + 8 + 4 + 4) + radix_sort_scratch_words(cap) * 4 + 1024;
+      RTB_CUDA(cudaMallocAsync((void **)&S.d_sched, bytes, st));
+      S.sched_items = cap;
+    }
+    const size_t c = S.sched_items;
+    est_args.sk = (uint64_t *)S.d_sched; est_args.sk2 = est_args.sk + c;
+    est_args.sv = (uint32_t *)(est_args.sk2 + c); est_args.sv2 = est_args.sv + c;
+    est_args.ss = est_args.sv2 + c;
+    est_args.ssw = radix_sort_scratch_words(c);
+    est_args.cost = (unsigned *)(est_args.ss + est_args.ssw + 64);
+    est_args.hot = (unsigned *)(((uintptr_t)(est_args.cost + c) + 15u) & ~(uintptr_t)15u);
+    est_args.n_items = n_est;
+    est = &est_args;
+  }
+  rc = launch_frame(S.dev(), fa, o.tracer, o.count_rays != 0, S.sm_count, st, &S.frame_launches, S.profile ? S.kev : nullptr, est);
   TR("after launches");
   if (rc) return rc;
   RTB_CUDA(cudaEventRecord(S.ev1, st));

@@ -184,8 +184,16 @@ void block_free(void *p, cudaStream_t st);
 // ---- frame kernels (trace.cu) ----
 // marks: nullptr, or 6 events recorded before the frame's first operation, after k_rast_setup, after k_rast_big,
 // after k_xchg_sync, after k_rast_items and after the frame kernel (rtb_scene_profile)
+// est (one-shot frames: there is no previous frame whose costs could order the work items): scratch for an
+// ESTIMATED cost per item -- the lengths of the light-grid lists at the hit points of the item's pixel centres, known as
+// soon as the projection pass has run -- and for the sort that turns it into the item order of this very frame
+struct ItemEstimate {
+  unsigned *cost; unsigned n_items;
+  uint64_t *sk, *sk2; uint32_t *sv, *sv2, *ss; size_t ssw;
+  unsigned *hot;
+};
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
-                 unsigned long long *launches, cudaEvent_t *marks = nullptr);
+                 unsigned long long *launches, cudaEvent_t *marks = nullptr, const ItemEstimate *est = nullptr);
 unsigned frame_item_count(int out_w, int out_h, int nranks);   // work items of one rank's frame
 // deferred tree: the listed shadow rays against every triangle; then the frame kernel alone (no projection pass) on fa.only_items tiles
 int launch_stray_any(const DevScene &sc, StrayQuery *q, const unsigned *count, int sm_count, cudaStream_t st);

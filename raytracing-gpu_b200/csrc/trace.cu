@@ -839,8 +839,49 @@ static int launch_wave_t(const DevScene &sc, const FrameArgs &fa, int sm_count, 
 
 static int launch_frame_kernel(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st);
 
+// ItemEstimate (rtb_internal.h): one warp per work item, one lane per pixel of the 8x4 tile, the pixel's centre sample
+__global__ void __launch_bounds__(256) k_item_estimate(const DevScene sc, const FrameArgs fa, unsigned *cost, unsigned n_items) {
+  const int lane = threadIdx.x & 31;
+  const unsigned warps = gridDim.x * 8;
+  for (unsigned item = blockIdx.x * 8 + (threadIdx.x >> 5); item < n_items; item += warps) {
+    int lx0, ly0;
+    unsigned est = 0;
+    if (frame_item(fa, item, lx0, ly0)) {
+      const int a = fa.aliasing;
+      const int px = a * (lx0 + (lane & 7)) + a / 2, py = a * (ly0 + (lane >> 3)) + a / 2;
+      if (px < fa.cam.W && py < fa.cam.H) {
+        est = 2;                                   // a sample that hits nothing
+        const unsigned long long key = fa.prim[(size_t)py * fa.cam.W + px];
+        if (key != ~0ull) {
+          est = 8;
+          V3 o, d;
+          primary_ray(fa.cam, px, py, o, d);
+          const V3 P = vadd(o, vscale(d, __uint_as_float((unsigned)(key >> 32))));
+          for (uint32_t i = 0; i < sc.n_lights && sc.lgrids; ++i) {
+            const LightGrid &g = sc.lgrids[i];
+            if (!g.kind) continue;
+            float x, y, den;
+            lg_project(g, P, x, y, den);
+            const float fi = floorf((x - g.x0) * g.inv_cell), fj = floorf((y - g.y0) * g.inv_cell);
+            if (fi >= 0.0f && fj >= 0.0f && fi <= (float)(g.nx - 1) && fj <= (float)(g.ny - 1)) {
+              const size_t c = (size_t)(int)fj * g.nx + (int)fi;
+              est += 4u + (__ldg(g.cell_start + c + 1) - __ldg(g.cell_start + c));
+            }
+          }
+        }
+      }
+    }
+    est = __reduce_add_sync(0xffffffffu, est);
+    if (lane == 0) cost[item] = est;
+  }
+}
+
+int launch_item_order(const unsigned int *d_cost, unsigned n, uint64_t *d_keys, uint32_t *d_vals,
+                      uint64_t *d_keys_alt, uint32_t *d_vals_alt, uint32_t *d_scratch, size_t scratch_words,
+                      cudaStream_t st, int *result_in_alt, unsigned *d_hot, float per_share);
+
 int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count, int sm_count, cudaStream_t st,
-                 unsigned long long *launches, cudaEvent_t *marks) {
+                 unsigned long long *launches, cudaEvent_t *marks, const ItemEstimate *est) {
   if (fa.aliasing < 1 || fa.aliasing > 16) { set_error("aliasing must be in 1..16"); return RTB_ERR_ARG; }
   if (marks) RTB_CUDA(cudaEventRecord(marks[0], st));
   RTB_CUDA(cudaMemsetAsync(fa.tile_counter, 0, sizeof(unsigned int), st));
@@ -868,6 +909,17 @@ int launch_frame(const DevScene &sc, const FrameArgs &fa, int tracer, bool count
   } else if (marks)
     for (int k = 1; k <= 3; ++k) RTB_CUDA(cudaEventRecord(marks[k], st));
   if (marks) RTB_CUDA(cudaEventRecord(marks[4], st));
+  if (est && fa.prim && tracer == RTB_TRACER_TREE && !count && !fa.item_order && est->n_items) {
+    k_item_estimate<<<sm_count * 8, 256, 0, st>>>(sc, fa, est->cost, est->n_items);
+    int in_alt = 0;
+    const int rc2 = launch_item_order(est->cost, est->n_items, est->sk, est->sv, est->sk2, est->sv2, est->ss, est->ssw, st, &in_alt, est->hot, 0.0f);
+    if (rc2) return rc2;
+    FrameArgs fb = fa;
+    fb.item_order = in_alt ? est->sv2 : est->sv;
+    const int rc3 = launch_frame_kernel(sc, fb, tracer, count, sm_count, st);
+    if (!rc3 && marks) RTB_CUDA(cudaEventRecord(marks[5], st));
+    return rc3;
+  }
   const int rc = launch_frame_kernel(sc, fa, tracer, count, sm_count, st);
   if (!rc && marks) RTB_CUDA(cudaEventRecord(marks[5], st));
   return rc;
