@@ -59,3 +59,19 @@ def test_handle_broadcast_world_size_2_gloo(tmp_path):
                        text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stderr[-2000:]
     assert r.stdout.count("ok") == 2
+
+
+def test_upload_group_barrier_and_failure_release(tmp_path):
+    """rtb_render_multi's device threads meet at UploadGroup::barrier (csrc/scene_store.h) while device 0 uploads the
+    scene for all of them; a thread that fails must release the others.  Host-only: compiled with g++ against the CUDA
+    headers, no device call."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cuda_inc = "/usr/local/cuda/include"
+    if not os.path.exists(os.path.join(cuda_inc, "cuda_runtime_api.h")):
+        pytest.skip("CUDA headers not found")
+    exe = str(tmp_path / "upload_group_host")
+    subprocess.run(["g++", "-std=c++17", "-O1", "-pthread", "-I" + cuda_inc, "-I" + os.path.join(root, "include"),
+                    "-I" + os.path.join(root, "raytracing-gpu_b200", "csrc"), "-o", exe,
+                    os.path.join(root, "tests", "native", "upload_group_host.cpp")], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout + r.stderr
